@@ -1,0 +1,371 @@
+#!/usr/bin/env python
+"""bench.py -- MSDeformAttn forward+backward throughput on B200 (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                  [--workload ENC|DEC|CPU] [--dtype f32|bf16] [--dist model|uniform]
+
+A "step" is one pass of the hot path (msda_forward, then zero-fill + msda_backward)
+over one batch of synthetic input of the named workload (default ENC = BASELINE.json
+configs[1]: N=16, S=Lq=1500 tokens, M=8, D=64, L=4, P=4, fp32).
+
+  value     queries/s (N*Lq per step, summed over ranks) with inputs resident in HBM,
+            kernels launched through the C ABI; CUDA events, max over ranks.
+  e2e       same metric through the public API (MSDeformAttnFunction.apply + autograd
+            backward) from pinned HOST buffers: H2D of value/loc/aw/grad_out and D2H
+            of out + the three gradients inside the timed region.
+  roofline  dominant kernel = the backward kernel; achieved = algorithmic bytes
+             / its CUDA-event duration averaged over the timed steps.
+  cpu_baseline  the oracle port of the reference's pure-PyTorch CPU path
+            (oracle/core_pytorch.py, fwd + autograd bwd) on a bounded sample, rank 0, N=1 only.
+
+Multi-GPU (torchrun): batch-sharded, weak scaling (per-GPU batch fixed), no data-path
+collective; barrier + synchronize around the timed region.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "msdeformattn_fwd_bwd_queries_per_sec"
+UNIT = "queries/s"
+CPU_SAMPLE_BATCH = 16     # batch items of the workload the CPU legs process per step
+RING = 4                  # distinct input sets rotated so a step never finds its inputs in L2
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="ENC", choices=["ENC", "DEC", "CPU"])
+    ap.add_argument("--dtype", default="f32", choices=["f32", "bf16"])
+    ap.add_argument("--dist", default="model", choices=["model", "uniform"])
+    ap.add_argument("--padding", default="zeros", choices=["zeros", "border"])
+    ap.add_argument("--qtile", type=int, default=0, help="tuning: queries-per-tile multiplier (0=auto)")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--extra", action="store_true", help="also print per-phase and alt-distribution lines to stderr")
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return None
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = [r for t, r in self.rows if t0 - 0.05 <= t <= t1 + 0.15 and len(r) >= 6] or \
+               [r for _, r in self.rows if len(r) >= 6]
+        if not rows:
+            return None
+        sm = sorted(int(float(r[0])) for r in rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": int(float(rows[0][1])), "reasons": reasons,
+                "samples": len(rows)}
+
+
+# ----------------------------------------------------------------------------- CPU legs (oracle port)
+def cpu_leg(workload, steps, warmup, dist):
+    """Times the oracle port of the reference's ms_deform_attn_core_pytorch (fwd + autograd
+    bwd, fp32, all host threads) on a bounded sample: CPU_SAMPLE_BATCH batch items of the
+    workload per step.  Returns (queries/s, ms_per_step, cores, sample description)."""
+    import torch
+    from mfl_b200 import synthetic
+    from oracle.core_pytorch import ms_deform_attn_core_pytorch
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    nb = min(CPU_SAMPLE_BATCH, synthetic.WORKLOADS[workload]["N"])
+    inp = synthetic.make_workload(workload, torch.float32, "cpu", seed=1234, dist=dist, value="normal", N=nb)
+    v, loc, aw = (inp[k].requires_grad_(True) for k in ("value", "loc", "aw"))
+    Lq = inp["loc"].shape[1]
+
+    def step():
+        out = ms_deform_attn_core_pytorch(v, inp["shapes"], loc, aw, "border")
+        out.backward(inp["grad_out"])
+        v.grad = loc.grad = aw.grad = None
+
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = (time.perf_counter() - t0) / steps
+    sample = "%s workload cut to batch %d (Lq=%d), fwd+autograd bwd, fp32, %d threads, %d steps" % (
+        workload, nb, Lq, cores, steps)
+    return nb * Lq / dt, dt * 1e3, cores, sample
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps, warmup = min(args.steps, 20), min(args.warmup, 3)
+    qps, ms, cores, sample = cpu_leg(args.workload, steps, warmup, args.dist)
+    from mfl_b200 import synthetic
+    w = synthetic.WORKLOADS[args.workload]
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": qps, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": steps, "warmup": warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "%s: MSDeformAttn fwd+bwd, T=%s, M=8, D=64, L=4, P=4 (CPU sample: batch %d)" % (
+            args.workload, w["T"], min(CPU_SAMPLE_BATCH, w["N"])), "locations": args.dist,
+            "impl_detail": "oracle port of reference ms_deform_attn_core_pytorch (grid_sample border) on host cores"},
+        "cpu_baseline": {"value": qps, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": qps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# ----------------------------------------------------------------------------- GPU arm
+class OpBuffers:
+    """One input set + preallocated outputs; launches the hot path through the C ABI."""
+
+    def __init__(self, inp, padding, qtile):
+        import torch
+        from mfl_b200 import _lib
+        self.lib = _lib.load()
+        self.inp = inp
+        v, loc, aw = inp["value"], inp["loc"], inp["aw"]
+        self.N, self.S, self.M, self.D = v.shape
+        self.L, self.Lq, self.P = inp["shapes"].shape[0], loc.shape[1], loc.shape[4]
+        self.dt = {torch.float32: 0, torch.float64: 1, torch.bfloat16: 2}[v.dtype]
+        self.pad = _lib.PADDING_MODES[padding]
+        self.flags = _lib.flag_qtile(qtile)
+        self.skip = _lib.MSDA_FLAG_SKIP_ZERO_FILL
+        self.out = torch.empty(self.N, self.Lq, self.M * self.D, dtype=v.dtype, device=v.device)
+        self.gv, self.gl, self.ga = torch.empty_like(v), torch.empty_like(loc), torch.empty_like(aw)
+        self.ws_bytes = self.lib.msda_backward_workspace_bytes(self.N, self.S, self.M, self.D, self.L,
+                                                               self.Lq, self.P, self.dt)
+        self.ws = torch.empty(max(self.ws_bytes // 4, 1), dtype=torch.float32, device=v.device)
+        self.dims = (self.N, self.S, self.M, self.D, self.L, self.Lq, self.P)
+        self.check = _lib.check
+
+    def fwd(self, stream):
+        i = self.inp
+        self.check(self.lib.msda_forward(i["value"].data_ptr(), i["shapes"].data_ptr(), i["lsi"].data_ptr(),
+                                         i["loc"].data_ptr(), i["aw"].data_ptr(), self.out.data_ptr(),
+                                         *self.dims, self.dt, self.pad, self.flags, stream))
+
+    def zero(self):
+        (self.ws if self.ws_bytes else self.gv).zero_()
+
+    def bwd(self, stream):
+        i = self.inp
+        self.check(self.lib.msda_backward(
+            i["value"].data_ptr(), i["shapes"].data_ptr(), i["lsi"].data_ptr(), i["loc"].data_ptr(),
+            i["aw"].data_ptr(), i["grad_out"].data_ptr(), self.gv.data_ptr(), self.gl.data_ptr(),
+            self.ga.data_ptr(), *self.dims, self.dt, self.pad, self.flags | self.skip,
+            self.ws.data_ptr() if self.ws_bytes else None, self.ws_bytes, stream))
+
+
+def time_device(bufs, steps, warmup, dist_sync):
+    """Timed region: `steps` x (fwd, zero-fill, bwd) rotating over the input ring.
+    Returns (total_ms, fwd_ms_avg, zero_ms_avg, bwd_ms_avg)."""
+    import torch
+    st = torch.cuda.current_stream().cuda_stream
+    for i in range(warmup):
+        b = bufs[i % len(bufs)]
+        b.fwd(st); b.zero(); b.bwd(st)
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(steps)]
+    dist_sync()
+    for i in range(steps):
+        b = bufs[i % len(bufs)]
+        ev[i][0].record(); b.fwd(st)
+        ev[i][1].record(); b.zero()
+        ev[i][2].record(); b.bwd(st)
+        ev[i][3].record()
+    torch.cuda.synchronize()
+    dist_sync()
+    total = ev[0][0].elapsed_time(ev[-1][3])
+    seg = [sum(e[k].elapsed_time(e[k + 1]) for e in ev) / steps for k in range(3)]
+    return total, seg[0], seg[1], seg[2]
+
+
+def time_e2e(host, dev_meta, padding, steps, warmup, dist_sync):
+    """Public-API path from pinned host buffers: H2D inputs, apply + backward, D2H results."""
+    import torch
+    from mfl_b200.functions.ms_deform_attn_func import ms_deform_attn
+    dev = dev_meta["shapes"].device
+    res_host = None
+
+    def step():
+        nonlocal res_host
+        v = host["value"].to(dev, non_blocking=True).requires_grad_(True)
+        loc = host["loc"].to(dev, non_blocking=True).requires_grad_(True)
+        aw = host["aw"].to(dev, non_blocking=True).requires_grad_(True)
+        go = host["grad_out"].to(dev, non_blocking=True)
+        out = ms_deform_attn(v, dev_meta["shapes"], dev_meta["lsi"], loc, aw, 64, padding)
+        out.backward(go)
+        if res_host is None:
+            res_host = [torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+                        for t in (out, v.grad, loc.grad, aw.grad)]
+        for h, t in zip(res_host, (out.detach(), v.grad, loc.grad, aw.grad)):
+            h.copy_(t, non_blocking=True)
+        return res_host
+
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize()
+    dist_sync()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    dist_sync()
+    h2d = sum(host[k].numel() * host[k].element_size() for k in ("value", "loc", "aw", "grad_out"))
+    d2h = sum(t.numel() * t.element_size() for t in res_host)
+    return e0.elapsed_time(e1), h2d, d2h
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from mfl_b200 import synthetic
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU fallback "
+                         "(use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def dist_sync():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    dtype = {"f32": torch.float32, "bf16": torch.bfloat16}[args.dtype]
+    w = synthetic.WORKLOADS[args.workload]
+    ring = [synthetic.make_workload(args.workload, dtype, dev, seed=1234 + 17 * rank + r, dist=args.dist,
+                                    value="normal") for r in range(RING)]
+    bufs = [OpBuffers(i, args.padding, args.qtile) for i in ring]
+    b0 = bufs[0]
+    N, S, Lq, M, D, L, P = b0.N, b0.S, b0.Lq, b0.M, b0.D, b0.L, b0.P
+    esz = ring[0]["value"].element_size()
+    bytes_fwd, bytes_bwd = synthetic.algorithmic_bytes(N, S, Lq, M, D, L, P, esz)
+    ring_bytes = sum(sum(t.numel() * t.element_size() for t in (i["value"], i["loc"], i["aw"], i["grad_out"]))
+                     for i in ring)
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    t0 = time.time()
+    total_ms, fwd_ms, zero_ms, bwd_ms = time_device(bufs, args.steps, args.warmup, dist_sync)
+    t1 = time.time()
+    clocks = sampler.stop(t0, t1) if rank == 0 else None
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    total_ms = max_over_ranks(total_ms)
+    ms_per_step = total_ms / args.steps
+    value = world * N * Lq / (ms_per_step * 1e-3)
+
+    e2e = None
+    if not args.no_e2e:
+        host = {k: ring[0][k].detach().cpu().pin_memory() for k in ("value", "loc", "aw", "grad_out")}
+        e_steps = max(3, min(args.steps, 20))
+        e_ms, h2d, d2h = time_e2e(host, ring[0], args.padding, e_steps, 3, dist_sync)
+        e_ms = max_over_ranks(e_ms) / e_steps
+        e2e = {"value": world * N * Lq / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": d2h, "ms_per_step": e_ms, "steps": e_steps}
+
+    peaks, peak_src = None, "fallback"
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        peak_src = "measured"
+    except Exception:
+        pass
+    hbm_peak = float(peaks["hbm_gbs"]) if peaks else 6650.0
+    achieved = bytes_bwd / (bwd_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "msda_bwd_fast_kernel", "achieved": achieved, "peak": hbm_peak,
+                "peak_source": peak_src + " (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s",
+                "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+                "algorithmic_bytes_per_launch": bytes_bwd, "kernel_ms": bwd_ms,
+                "fwd_kernel": {"achieved": bytes_fwd / (fwd_ms * 1e-3) / 1e9,
+                               "frac": bytes_fwd / (fwd_ms * 1e-3) / 1e9 / hbm_peak, "kernel_ms": fwd_ms,
+                               "algorithmic_bytes_per_launch": bytes_fwd},
+                "zero_fill_ms": zero_ms,
+                "step": {"achieved": (bytes_fwd + bytes_bwd) / (ms_per_step * 1e-3) / 1e9,
+                         "frac": (bytes_fwd + bytes_bwd) / (ms_per_step * 1e-3) / 1e9 / hbm_peak}}
+    traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(traffic_file):
+        try:
+            roofline["traffic"] = json.load(open(traffic_file)).get("%s_%s_%s_bwd" % (args.workload, args.dtype, args.dist))
+        except Exception:
+            pass
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        qps, ms, cores, sample = cpu_leg(args.workload, 3, 1, args.dist)
+        cpu = {"value": qps, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample, "ms_per_step": ms}
+
+    if rank == 0:
+        print(json.dumps({
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+            "config": {"workload": "%s: MSDeformAttn fwd+bwd, per-GPU batch %d, Lq=%d, S=%d (T=%s), M=%d, D=%d, L=%d, P=%d" % (
+                args.workload, N, Lq, S, w["T"], M, D, L, P),
+                "locations": args.dist, "padding": args.padding, "parallelism": "batch-sharded x%d, no data-path collective" % world,
+                "l2": "inputs rotate over %d distinct sets (%.0f MB) > 126 MB L2" % (RING, ring_bytes / 1e6)},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+            "gpu_launches": 2 * args.steps, "clocks": clocks,
+        }))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,132 @@
+/*
+ * msda_b200.h -- C ABI of libmsda_b200.so: multi-scale deformable attention
+ * (forward + backward) for NVIDIA B200 (sm_100a).
+ *
+ * This is the drop-in boundary for the reference's native module
+ * `MultiScaleDeformableAttention` (pybind, models/ops/src/vision.cpp:13-16):
+ *
+ *   ms_deform_attn_forward (models/ops/src/ms_deform_attn.h:20-39,
+ *                           models/ops/src/cuda/ms_deform_attn_cuda.cu:20-80)
+ *       -> msda_forward
+ *   ms_deform_attn_backward(models/ops/src/ms_deform_attn.h:41-61,
+ *                           models/ops/src/cuda/ms_deform_attn_cuda.cu:83-153)
+ *       -> msda_backward (+ msda_backward_workspace_bytes)
+ *
+ * Conventions
+ *   - plain pointers and sizes; no torch / pybind types.
+ *   - every data pointer is a DEVICE pointer; the library borrows it for the
+ *     duration of the enqueue only and never allocates or retains memory.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *   - work is enqueued asynchronously; no host synchronisation is performed.
+ *   - return value: MSDA_OK (0) or a negative msda_status; never throws/exits.
+ *     (The reference only printf()s launch errors, .cuh:949-953 -- this ABI is
+ *     intentionally stricter.)
+ *   - no static mutable state: re-entrant, callable from several host threads
+ *     on different streams.
+ *
+ * Tensor layouts (row-major contiguous, identical to the reference):
+ *   value              [N, S, M, D]          S = sum_l H_l*W_l
+ *   spatial_shapes     [L, 2] int64 (H_l, W_l)          -- device memory
+ *   level_start_index  [L]    int64                     -- device memory
+ *   sampling_loc       [N, Lq, M, L, P, 2]   normalised (x -> W, y -> H)
+ *   attn_weight        [N, Lq, M, L, P]
+ *   output/grad_output [N, Lq, M*D]
+ */
+#ifndef MSDA_B200_H_
+#define MSDA_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MSDA_B200_ABI_VERSION 1
+
+/* element type of value / sampling_loc / attn_weight / output / all grads */
+typedef enum {
+  MSDA_F32 = 0,  /* reference: AT_DISPATCH_FLOATING_TYPES (cuda.cu:64) */
+  MSDA_F64 = 1,  /* reference: same macro; needed by gradcheck (test.py:76) */
+  MSDA_BF16 = 2  /* new capability (fp32 accumulate) */
+} msda_dtype;
+
+/* handling of taps outside the feature map */
+typedef enum {
+  MSDA_PAD_ZEROS = 0, /* reference CUDA op (.cuh:56-79, gate at :289) */
+  MSDA_PAD_BORDER = 1 /* reference PyTorch path (grid_sample border,
+                         functions/ms_deform_attn_func.py:61-62) */
+} msda_padding;
+
+typedef enum {
+  MSDA_OK = 0,
+  MSDA_ERR_NULL_POINTER = -1,
+  MSDA_ERR_BAD_SHAPE = -2,      /* a dimension <= 0 (N, Lq, S may be 0) */
+  MSDA_ERR_BAD_DTYPE = -3,
+  MSDA_ERR_BAD_PADDING = -4,
+  MSDA_ERR_TOO_LARGE = -5,      /* exceeds the 2^31 row / group index range */
+  MSDA_ERR_WORKSPACE = -6,      /* workspace missing or too small */
+  MSDA_ERR_CUDA = -7,           /* CUDA runtime error (see msda_last_cuda_error) */
+  MSDA_ERR_MISALIGNED = -8      /* a data pointer is not 16-byte aligned */
+} msda_status;
+
+/* flags for msda_forward / msda_backward (bitwise or) */
+#define MSDA_FLAG_FORCE_GENERIC 1u /* use the any-D scalar kernels even when the
+                                      vectorised path applies (testing aid) */
+#define MSDA_FLAG_SKIP_ZERO_FILL 2u /* msda_backward: the caller has already
+                                      zeroed the accumulation target (grad_value
+                                      for f32/f64, the workspace for bf16) */
+/* bits 8..19: queries-per-tile multiplier override for the vectorised kernels
+ * (0 = heuristic); a tuning knob, results do not depend on it. */
+#define MSDA_FLAG_QTILE(k) (((unsigned)(k) & 0xfffu) << 8)
+
+/* Library / ABI identification. */
+int msda_abi_version(void);
+const char* msda_error_string(int status);
+/* Name of the kernel family msda_forward/backward would pick:
+ * "fast" (vectorised, warp-cooperative) or "generic". */
+const char* msda_kernel_family(int64_t D, int dtype, unsigned flags);
+
+/*
+ * out[b,q,m,:] = sum_{l,p} aw[b,q,m,l,p] * bilinear(value_l[b,:,m,:], loc[b,q,m,l,p])
+ * Replaces ms_deform_attn_cuda_forward (cuda.cu:20-80) + the im2col kernel
+ * (.cuh:238-300).  `output` is fully written (no pre-zeroing needed).
+ * The reference's im2col_step batch chunking is a host-side knob validated by
+ * the Python shim; results do not depend on it, so it is not part of the ABI.
+ */
+int msda_forward(const void* value, const int64_t* spatial_shapes,
+                 const int64_t* level_start_index, const void* sampling_loc,
+                 const void* attn_weight, void* output,
+                 int64_t N, int64_t S, int64_t M, int64_t D, int64_t L,
+                 int64_t Lq, int64_t P,
+                 int dtype, int padding, unsigned flags, void* stream);
+
+/* Bytes of scratch msda_backward needs (0 for f32/f64; an fp32 accumulation
+ * image of grad_value for bf16). */
+size_t msda_backward_workspace_bytes(int64_t N, int64_t S, int64_t M, int64_t D,
+                                     int64_t L, int64_t Lq, int64_t P, int dtype);
+
+/*
+ * Replaces ms_deform_attn_cuda_backward (cuda.cu:83-153) + the col2im kernels
+ * (.cuh:302-921).  All three gradient buffers are fully defined on return
+ * (grad_value is zero-filled inside the call on `stream`; callers need not
+ * pre-zero anything).
+ */
+int msda_backward(const void* value, const int64_t* spatial_shapes,
+                  const int64_t* level_start_index, const void* sampling_loc,
+                  const void* attn_weight, const void* grad_output,
+                  void* grad_value, void* grad_sampling_loc, void* grad_attn_weight,
+                  int64_t N, int64_t S, int64_t M, int64_t D, int64_t L,
+                  int64_t Lq, int64_t P,
+                  int dtype, int padding, unsigned flags,
+                  void* workspace, size_t workspace_bytes, void* stream);
+
+/* Last CUDA runtime error code seen by the calling thread inside this library
+ * (cudaError_t as int) and its string. */
+int msda_last_cuda_error(void);
+const char* msda_last_cuda_error_string(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MSDA_B200_H_ */

@@ -1,0 +1,105 @@
+"""Drop-in for the reference's pybind module ``MultiScaleDeformableAttention``
+(models/ops/src/vision.cpp:13-16, built by models/ops/setup.py:53).
+
+Exports the same two functions with the same positional arguments and the same
+error behaviour (asserts -> RuntimeError), but the work is done by the sm_100a
+kernels in libmsda_b200.so through its C ABI (include/msda_b200.h).  The extra
+keyword arguments (padding_mode, flags) are optional extensions.
+"""
+import torch
+
+from . import _lib
+
+_DTYPES = {torch.float32: _lib.MSDA_F32, torch.float64: _lib.MSDA_F64,
+           torch.bfloat16: _lib.MSDA_BF16}
+
+
+def _check_inputs(named, im2col_step):
+    # models/ops/src/cuda/ms_deform_attn_cuda.cu:28-38 / :93-105
+    value = named[0][1]
+    if not value.is_cuda:
+        # models/ops/src/ms_deform_attn.h:38,60
+        raise RuntimeError("Not implemented on the CPU")
+    for name, t in named:
+        if not t.is_contiguous():
+            raise RuntimeError("%s tensor has to be contiguous" % name)
+        if not t.is_cuda:
+            raise RuntimeError("%s must be a CUDA tensor" % name)
+        if t.device != value.device:
+            raise RuntimeError("%s must be on the same device as value" % name)
+    value, shapes, lsi, loc, aw = (t for _, t in named[:5])
+    if value.dtype not in _DTYPES:
+        raise RuntimeError("msda_b200: unsupported dtype %s (float32, float64, bfloat16)" % value.dtype)
+    for name, t in named[3:]:
+        if t.dtype != value.dtype:
+            raise RuntimeError("%s must have the dtype of value (%s), got %s" % (name, value.dtype, t.dtype))
+    if shapes.dtype != torch.int64 or lsi.dtype != torch.int64:
+        raise RuntimeError("spatial_shapes and level_start_index must be int64 tensors")
+    if value.dim() != 4 or loc.dim() != 6 or aw.dim() != 5 or shapes.dim() != 2:
+        raise RuntimeError("msda_b200: expected value[N,S,M,D], spatial_shapes[L,2], "
+                           "sampling_loc[N,Lq,M,L,P,2], attn_weight[N,Lq,M,L,P]")
+    N, S, M, D = value.shape
+    L = shapes.shape[0]
+    Lq, P = loc.shape[1], loc.shape[4]
+    if (shapes.shape[1] != 2 or lsi.numel() != L or tuple(loc.shape) != (N, Lq, M, L, P, 2)
+            or tuple(aw.shape) != (N, Lq, M, L, P)):
+        raise RuntimeError("msda_b200: inconsistent shapes value=%s shapes=%s lsi=%s loc=%s aw=%s" % (
+            tuple(value.shape), tuple(shapes.shape), tuple(lsi.shape), tuple(loc.shape), tuple(aw.shape)))
+    # cuda.cu:50-52: im2col_step_ = min(batch, im2col_step); batch % im2col_step_ == 0
+    if N > 0:
+        step = min(N, int(im2col_step))
+        if step <= 0 or N % step != 0:
+            raise RuntimeError("batch(%d) must divide im2col_step(%d)" % (N, step))
+    return N, S, M, D, L, Lq, P
+
+
+def _stream(t):
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def ms_deform_attn_forward(value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
+                           im2col_step, padding_mode="zeros", flags=0):
+    """value[N,S,M,D] ... -> output[N,Lq,M*D]  (cuda.cu:20-80)."""
+    N, S, M, D, L, Lq, P = _check_inputs(
+        [("value", value), ("spatial_shapes", spatial_shapes),
+         ("level_start_index", level_start_index), ("sampling_loc", sampling_loc),
+         ("attn_weight", attn_weight)], im2col_step)
+    lib = _lib.load()
+    with torch.cuda.device_of(value):
+        out = torch.empty((N, Lq, M * D), dtype=value.dtype, device=value.device)
+        _lib.check(lib.msda_forward(
+            value.data_ptr(), spatial_shapes.data_ptr(), level_start_index.data_ptr(),
+            sampling_loc.data_ptr(), attn_weight.data_ptr(), out.data_ptr(),
+            N, S, M, D, L, Lq, P, _DTYPES[value.dtype], _lib.PADDING_MODES[padding_mode],
+            flags, _stream(value)))
+    return out
+
+
+def ms_deform_attn_backward(value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
+                            grad_output, im2col_step, padding_mode="zeros", flags=0):
+    """-> [grad_value, grad_sampling_loc, grad_attn_weight]  (cuda.cu:83-153)."""
+    N, S, M, D, L, Lq, P = _check_inputs(
+        [("value", value), ("spatial_shapes", spatial_shapes),
+         ("level_start_index", level_start_index), ("sampling_loc", sampling_loc),
+         ("attn_weight", attn_weight), ("grad_output", grad_output)], im2col_step)
+    if grad_output.numel() != N * Lq * M * D:
+        raise RuntimeError("grad_output must have N*Lq*M*D elements")
+    lib = _lib.load()
+    dt = _DTYPES[value.dtype]
+    with torch.cuda.device_of(value):
+        grad_value = torch.empty_like(value)
+        grad_loc = torch.empty_like(sampling_loc)
+        grad_aw = torch.empty_like(attn_weight)
+        ws_bytes = lib.msda_backward_workspace_bytes(N, S, M, D, L, Lq, P, dt)
+        ws = None
+        if ws_bytes:
+            ws = torch.empty(ws_bytes // 4, dtype=torch.float32, device=value.device)
+        _lib.check(lib.msda_backward(
+            value.data_ptr(), spatial_shapes.data_ptr(), level_start_index.data_ptr(),
+            sampling_loc.data_ptr(), attn_weight.data_ptr(), grad_output.data_ptr(),
+            grad_value.data_ptr(), grad_loc.data_ptr(), grad_aw.data_ptr(),
+            N, S, M, D, L, Lq, P, dt, _lib.PADDING_MODES[padding_mode], flags,
+            ws.data_ptr() if ws is not None else None, ws_bytes, _stream(value)))
+        if ws is not None:
+            ws.record_stream(torch.cuda.current_stream(value.device))
+    return [grad_value, grad_loc, grad_aw]

@@ -1,0 +1,96 @@
+"""ctypes binding of libmsda_b200.so (the C ABI in include/msda_b200.h).
+
+There is deliberately NO fallback: if the shared library is missing or a
+non-CUDA tensor reaches the op, callers get an exception (the reference raises
+"Not implemented on the CPU", models/ops/src/ms_deform_attn.h:38,60).
+"""
+import ctypes
+import os
+import subprocess
+import threading
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmsda_b200.so")
+BUILD_SCRIPT = os.path.join(_HERE, "build.sh")
+
+MSDA_F32, MSDA_F64, MSDA_BF16 = 0, 1, 2
+MSDA_PAD_ZEROS, MSDA_PAD_BORDER = 0, 1
+MSDA_FLAG_FORCE_GENERIC = 1
+MSDA_FLAG_SKIP_ZERO_FILL = 2
+
+
+def flag_qtile(k):
+    return (int(k) & 0xFFF) << 8
+
+PADDING_MODES = {"zeros": MSDA_PAD_ZEROS, "border": MSDA_PAD_BORDER}
+
+# every symbol include/msda_b200.h declares (checked by tests/test_abi.py)
+EXPORTED_SYMBOLS = (
+    "msda_abi_version",
+    "msda_error_string",
+    "msda_kernel_family",
+    "msda_forward",
+    "msda_backward_workspace_bytes",
+    "msda_backward",
+    "msda_last_cuda_error",
+    "msda_last_cuda_error_string",
+)
+
+_lock = threading.Lock()
+_lib = None
+
+
+def build(extra_flags=()):
+    """Compile libmsda_b200.so for sm_100a with nvcc (works without a GPU)."""
+    subprocess.run(["bash", BUILD_SCRIPT, *extra_flags], check=True)
+    return LIB_PATH
+
+
+def _declare(lib):
+    c = ctypes
+    i64, vp, u32 = c.c_int64, c.c_void_p, c.c_uint
+    lib.msda_abi_version.restype = c.c_int
+    lib.msda_abi_version.argtypes = []
+    lib.msda_error_string.restype = c.c_char_p
+    lib.msda_error_string.argtypes = [c.c_int]
+    lib.msda_kernel_family.restype = c.c_char_p
+    lib.msda_kernel_family.argtypes = [i64, c.c_int, u32]
+    lib.msda_last_cuda_error.restype = c.c_int
+    lib.msda_last_cuda_error.argtypes = []
+    lib.msda_last_cuda_error_string.restype = c.c_char_p
+    lib.msda_last_cuda_error_string.argtypes = []
+    lib.msda_forward.restype = c.c_int
+    lib.msda_forward.argtypes = [vp, vp, vp, vp, vp, vp] + [i64] * 7 + [c.c_int, c.c_int, u32, vp]
+    lib.msda_backward_workspace_bytes.restype = c.c_size_t
+    lib.msda_backward_workspace_bytes.argtypes = [i64] * 7 + [c.c_int]
+    lib.msda_backward.restype = c.c_int
+    lib.msda_backward.argtypes = (
+        [vp] * 9 + [i64] * 7 + [c.c_int, c.c_int, u32, vp, c.c_size_t, vp]
+    )
+    return lib
+
+
+def load():
+    """Return the loaded library; raise if it has not been built."""
+    global _lib
+    if _lib is None:
+        with _lock:
+            if _lib is None:
+                if not os.path.exists(LIB_PATH):
+                    raise RuntimeError(
+                        "libmsda_b200.so is not built (%s). Run `python -c 'import "
+                        "__graft_entry__ as g; g.build()'` or %s. There is no CPU/PyTorch "
+                        "fallback for MSDeformAttn in this package." % (LIB_PATH, BUILD_SCRIPT)
+                    )
+                _lib = _declare(ctypes.CDLL(LIB_PATH))
+    return _lib
+
+
+def check(status):
+    """Turn a non-zero msda_status into a RuntimeError (c10::Error analogue)."""
+    if status != 0:
+        lib = load()
+        msg = lib.msda_error_string(status).decode()
+        if status == -7:
+            msg += ": " + lib.msda_last_cuda_error_string().decode()
+        raise RuntimeError("msda_b200: " + msg)

@@ -1,0 +1,287 @@
+// msda_capi.cu -- host side of libmsda_b200.so: argument validation, kernel
+// selection and launches behind the C ABI declared in include/msda_b200.h.
+// Replaces the reference host launchers ms_deform_attn_cuda_forward/backward
+// (models/ops/src/cuda/ms_deform_attn_cuda.cu:20-153) and the D-dispatch table
+// ms_deformable_col2im_cuda (ms_deform_im2col_cuda.cuh:957-1328).
+#include "../../include/msda_b200.h"
+#include "msda_fast.cuh"
+#include "msda_generic.cuh"
+
+using namespace msda;
+
+namespace {
+
+thread_local int t_last_cuda_error = 0;
+
+inline int cuda_fail(cudaError_t e) {
+  t_last_cuda_error = (int)e;
+  return MSDA_ERR_CUDA;
+}
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+inline int log2_exact(int64_t g) {  // -1 unless g in {1,2,4,8,16,32}
+  for (int s = 0; s <= 5; ++s)
+    if (g == (int64_t(1) << s)) return s;
+  return -1;
+}
+
+inline int vec_of(int dtype) { return dtype == MSDA_F32 ? 4 : dtype == MSDA_BF16 ? 8 : 0; }
+
+inline bool fast_applies(int64_t D, int64_t L, int dtype, unsigned flags) {
+  if (flags & MSDA_FLAG_FORCE_GENERIC) return false;
+  const int vec = vec_of(dtype);
+  if (!vec || D % vec || L > kMaxLevelsFast) return false;
+  return log2_exact(D / vec) >= 0;
+}
+
+int check_common(int64_t N, int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq, int64_t P,
+                 int dtype, int padding) {
+  if (dtype != MSDA_F32 && dtype != MSDA_F64 && dtype != MSDA_BF16) return MSDA_ERR_BAD_DTYPE;
+  if (padding != MSDA_PAD_ZEROS && padding != MSDA_PAD_BORDER) return MSDA_ERR_BAD_PADDING;
+  if (N < 0 || S < 0 || Lq < 0 || M <= 0 || D <= 0 || L <= 0 || P <= 0) return MSDA_ERR_BAD_SHAPE;
+  const int64_t lim = (int64_t(1) << 31) - 1;
+  if (S > lim || N * Lq * M > lim || L * P > lim || M * D > lim) return MSDA_ERR_TOO_LARGE;
+  return MSDA_OK;
+}
+
+inline Dims make_dims(int64_t N, int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq, int64_t P,
+                      int padding) {
+  Dims d;
+  d.N = (int)N; d.S = (int)S; d.M = (int)M; d.D = (int)D; d.L = (int)L; d.Lq = (int)Lq; d.P = (int)P;
+  d.border = padding == MSDA_PAD_BORDER;
+  return d;
+}
+
+// Queries per tile: a multiple k of the groups per CTA.  Larger tiles reuse
+// tapped rows from L1; smaller ones fill the 148 SMs when N*M*Lq is small.
+inline int pick_qtile(const Dims& d, int G, unsigned flags) {
+  const int ng = kFastThreads / G;
+  int k = (int)((flags >> 8) & 0xfffu);
+  if (k == 0) {
+    k = 4;
+    while (k > 1 && (int64_t)d.N * d.M * ((d.Lq + ng * k - 1) / (ng * k)) < 148 * 8) k >>= 1;
+  }
+  return ng * k;
+}
+
+template <typename T, int VEC, int G>
+int launch_fwd_fast(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
+                    const void* aw, void* out, const Dims& d, unsigned flags, cudaStream_t st) {
+  const int qtile = pick_qtile(d, G, flags);
+  const int nqc = (d.Lq + qtile - 1) / qtile;
+  const int64_t tiles = (int64_t)d.N * d.M * nqc;
+  msda_fwd_fast_kernel<T, VEC, G><<<(unsigned)tiles, kFastThreads, 0, st>>>(
+      (const T*)value, shapes, lsi, (const T*)loc, (const T*)aw, (T*)out, d, qtile, nqc);
+  const cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
+}
+
+template <typename T, int VEC, int G>
+int launch_bwd_fast(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
+                    const void* aw, const void* gout, float* gvalue, void* gloc, void* gaw,
+                    const Dims& d, unsigned flags, cudaStream_t st) {
+  const int qtile = pick_qtile(d, G, flags);
+  const int nqc = (d.Lq + qtile - 1) / qtile;
+  const int64_t tiles = (int64_t)d.N * d.M * nqc;
+  msda_bwd_fast_kernel<T, VEC, G><<<(unsigned)tiles, kFastThreads, 0, st>>>(
+      (const T*)value, shapes, lsi, (const T*)loc, (const T*)aw, (const T*)gout, gvalue, (T*)gloc,
+      (T*)gaw, d, qtile, nqc);
+  const cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
+}
+
+#define MSDA_DISPATCH_G(LOG2G, CALL)                    \
+  switch (LOG2G) {                                      \
+    case 0: { constexpr int G = 1; CALL; } break;       \
+    case 1: { constexpr int G = 2; CALL; } break;       \
+    case 2: { constexpr int G = 4; CALL; } break;       \
+    case 3: { constexpr int G = 8; CALL; } break;       \
+    case 4: { constexpr int G = 16; CALL; } break;      \
+    default: { constexpr int G = 32; CALL; } break;     \
+  }
+
+template <typename T>
+int launch_fwd_generic(const void* value, const int64_t* shapes, const int64_t* lsi,
+                       const void* loc, const void* aw, void* out, const Dims& d, cudaStream_t st) {
+  const size_t total = (size_t)d.N * d.Lq * d.M * d.D;
+  size_t blocks = (total + 255) / 256;
+  if (blocks > 148u * 64u) blocks = 148u * 64u;
+  msda_fwd_generic_kernel<T><<<(unsigned)blocks, 256, 0, st>>>(
+      (const T*)value, shapes, lsi, (const T*)loc, (const T*)aw, (T*)out, d, total);
+  const cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
+}
+
+template <typename T, typename GV>
+int launch_bwd_generic(const void* value, const int64_t* shapes, const int64_t* lsi,
+                       const void* loc, const void* aw, const void* gout, GV* gvalue, void* gloc,
+                       void* gaw, const Dims& d, cudaStream_t st) {
+  const int64_t groups = (int64_t)d.N * d.Lq * d.M;
+  msda_bwd_generic_kernel<T, GV><<<(unsigned)groups, 128, 0, st>>>(
+      (const T*)value, shapes, lsi, (const T*)loc, (const T*)aw, (const T*)gout, gvalue, (T*)gloc,
+      (T*)gaw, d);
+  const cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
+}
+
+}  // namespace
+
+extern "C" {
+
+int msda_abi_version(void) { return MSDA_B200_ABI_VERSION; }
+
+const char* msda_error_string(int status) {
+  switch (status) {
+    case MSDA_OK: return "ok";
+    case MSDA_ERR_NULL_POINTER: return "null pointer argument";
+    case MSDA_ERR_BAD_SHAPE: return "invalid shape (M, D, L, P must be > 0; N, S, Lq >= 0)";
+    case MSDA_ERR_BAD_DTYPE: return "unsupported dtype (expected f32, f64 or bf16)";
+    case MSDA_ERR_BAD_PADDING: return "unsupported padding mode (expected zeros or border)";
+    case MSDA_ERR_TOO_LARGE: return "problem exceeds the 2^31-1 row/group index range";
+    case MSDA_ERR_WORKSPACE: return "workspace missing or smaller than msda_backward_workspace_bytes()";
+    case MSDA_ERR_CUDA: return "CUDA runtime error (see msda_last_cuda_error_string)";
+    case MSDA_ERR_MISALIGNED: return "data pointer not aligned to its element size";
+    default: return "unknown msda status";
+  }
+}
+
+const char* msda_kernel_family(int64_t D, int dtype, unsigned flags) {
+  return fast_applies(D, 1, dtype, flags) ? "fast" : "generic";
+}
+
+int msda_last_cuda_error(void) { return t_last_cuda_error; }
+const char* msda_last_cuda_error_string(void) {
+  return cudaGetErrorString((cudaError_t)t_last_cuda_error);
+}
+
+int msda_forward(const void* value, const int64_t* spatial_shapes, const int64_t* level_start_index,
+                 const void* sampling_loc, const void* attn_weight, void* output, int64_t N,
+                 int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq, int64_t P, int dtype,
+                 int padding, unsigned flags, void* stream) {
+  const int rc = check_common(N, S, M, D, L, Lq, P, dtype, padding);
+  if (rc != MSDA_OK) return rc;
+  if (N == 0 || Lq == 0) return MSDA_OK;  // empty output
+  if (!spatial_shapes || !level_start_index || !sampling_loc || !attn_weight || !output)
+    return MSDA_ERR_NULL_POINTER;
+  if (S > 0 && !value) return MSDA_ERR_NULL_POINTER;
+  const Dims d = make_dims(N, S, M, D, L, Lq, P, padding);
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool fast = fast_applies(D, L, dtype, flags) && aligned16(value) && aligned16(output) &&
+                    aligned16(sampling_loc) && aligned16(attn_weight);
+  if (fast) {
+    const int lg = log2_exact(D / vec_of(dtype));
+    int r = MSDA_OK;
+    if (dtype == MSDA_F32) {
+      MSDA_DISPATCH_G(lg, (r = launch_fwd_fast<float, 4, G>(value, spatial_shapes, level_start_index,
+                                                            sampling_loc, attn_weight, output, d,
+                                                            flags, st)));
+    } else {
+      MSDA_DISPATCH_G(lg, (r = launch_fwd_fast<__nv_bfloat16, 8, G>(
+                               value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
+                               output, d, flags, st)));
+    }
+    return r;
+  }
+  switch (dtype) {
+    case MSDA_F32:
+      return launch_fwd_generic<float>(value, spatial_shapes, level_start_index, sampling_loc,
+                                       attn_weight, output, d, st);
+    case MSDA_F64:
+      return launch_fwd_generic<double>(value, spatial_shapes, level_start_index, sampling_loc,
+                                        attn_weight, output, d, st);
+    default:
+      return launch_fwd_generic<__nv_bfloat16>(value, spatial_shapes, level_start_index,
+                                               sampling_loc, attn_weight, output, d, st);
+  }
+}
+
+size_t msda_backward_workspace_bytes(int64_t N, int64_t S, int64_t M, int64_t D, int64_t L,
+                                     int64_t Lq, int64_t P, int dtype) {
+  (void)L; (void)Lq; (void)P;
+  if (dtype != MSDA_BF16 || N <= 0 || S <= 0 || M <= 0 || D <= 0) return 0;
+  return (size_t)N * S * M * D * sizeof(float);
+}
+
+int msda_backward(const void* value, const int64_t* spatial_shapes, const int64_t* level_start_index,
+                  const void* sampling_loc, const void* attn_weight, const void* grad_output,
+                  void* grad_value, void* grad_sampling_loc, void* grad_attn_weight, int64_t N,
+                  int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq, int64_t P, int dtype,
+                  int padding, unsigned flags, void* workspace, size_t workspace_bytes,
+                  void* stream) {
+  const int rc = check_common(N, S, M, D, L, Lq, P, dtype, padding);
+  if (rc != MSDA_OK) return rc;
+  const Dims d = make_dims(N, S, M, D, L, Lq, P, padding);
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t esz = dtype == MSDA_F64 ? 8 : dtype == MSDA_F32 ? 4 : 2;
+  const size_t nvalue = (size_t)N * S * M * D;
+  const size_t ws_need = msda_backward_workspace_bytes(N, S, M, D, L, Lq, P, dtype);
+  if (nvalue > 0 && (!grad_value || !value)) return MSDA_ERR_NULL_POINTER;
+  if (ws_need > 0 && (!workspace || workspace_bytes < ws_need)) return MSDA_ERR_WORKSPACE;
+  if (ws_need > 0 && !aligned16(workspace)) return MSDA_ERR_MISALIGNED;
+
+  // zero the accumulation target (the reference does this with zeros_like,
+  // cuda.cu:121-123; grad_loc / grad_aw are fully written by the kernels)
+  void* acc = ws_need ? workspace : grad_value;
+  if (nvalue > 0 && !(flags & MSDA_FLAG_SKIP_ZERO_FILL)) {
+    const cudaError_t e = cudaMemsetAsync(acc, 0, ws_need ? ws_need : nvalue * esz, st);
+    if (e != cudaSuccess) return cuda_fail(e);
+  }
+  if (N == 0 || Lq == 0) return MSDA_OK;
+  if (!spatial_shapes || !level_start_index || !sampling_loc || !attn_weight || !grad_output ||
+      !grad_sampling_loc || !grad_attn_weight)
+    return MSDA_ERR_NULL_POINTER;
+
+  const bool fast = fast_applies(D, L, dtype, flags) && aligned16(value) && aligned16(grad_output) &&
+                    aligned16(grad_value) && aligned16(sampling_loc) && aligned16(attn_weight) &&
+                    aligned16(grad_sampling_loc) && aligned16(grad_attn_weight);
+  int r = MSDA_OK;
+  if (fast) {
+    const int lg = log2_exact(D / vec_of(dtype));
+    if (dtype == MSDA_F32) {
+      MSDA_DISPATCH_G(lg, (r = launch_bwd_fast<float, 4, G>(
+                               value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
+                               grad_output, (float*)acc, grad_sampling_loc, grad_attn_weight, d,
+                               flags, st)));
+    } else {
+      MSDA_DISPATCH_G(lg, (r = launch_bwd_fast<__nv_bfloat16, 8, G>(
+                               value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
+                               grad_output, (float*)acc, grad_sampling_loc, grad_attn_weight, d,
+                               flags, st)));
+    }
+  } else if (dtype == MSDA_F32) {
+    r = launch_bwd_generic<float, float>(value, spatial_shapes, level_start_index, sampling_loc,
+                                         attn_weight, grad_output, (float*)acc, grad_sampling_loc,
+                                         grad_attn_weight, d, st);
+  } else if (dtype == MSDA_F64) {
+    r = launch_bwd_generic<double, double>(value, spatial_shapes, level_start_index, sampling_loc,
+                                           attn_weight, grad_output, (double*)acc,
+                                           grad_sampling_loc, grad_attn_weight, d, st);
+  } else {
+    r = launch_bwd_generic<__nv_bfloat16, float>(value, spatial_shapes, level_start_index,
+                                                 sampling_loc, attn_weight, grad_output,
+                                                 (float*)acc, grad_sampling_loc, grad_attn_weight,
+                                                 d, st);
+  }
+  if (r != MSDA_OK) return r;
+
+  if (dtype == MSDA_BF16 && nvalue > 0) {
+    if ((nvalue % 8) == 0 && aligned16(grad_value)) {
+      const size_t n8 = nvalue / 8;
+      size_t blocks = (n8 + 255) / 256;
+      if (blocks > 148u * 16u) blocks = 148u * 16u;
+      msda_round_bf16_kernel<<<(unsigned)blocks, 256, 0, st>>>((const float*)acc,
+                                                               (__nv_bfloat16*)grad_value, n8);
+    } else {
+      size_t blocks = (nvalue + 255) / 256;
+      if (blocks > 148u * 16u) blocks = 148u * 16u;
+      msda_round_bf16_scalar_kernel<<<(unsigned)blocks, 256, 0, st>>>(
+          (const float*)acc, (__nv_bfloat16*)grad_value, nvalue);
+    }
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e);
+  }
+  return MSDA_OK;
+}
+
+}  // extern "C"

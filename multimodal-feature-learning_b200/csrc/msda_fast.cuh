@@ -1,0 +1,330 @@
+// msda_fast.cuh -- vectorised, warp-cooperative MSDeformAttn kernels (sm_100a).
+//
+// Work decomposition (forward and backward):
+//   * a GROUP of G lanes owns one (batch b, query q, head m); lane j of the
+//     group owns channels [j*VEC, (j+1)*VEC) -> every tap of the head row is
+//     ONE coalesced 128-bit load per lane (G*16 bytes contiguous).
+//   * a CTA (256 threads = 256/G groups) owns a TILE = (b, m, chunk of
+//     consecutive queries), so the rows tapped by neighbouring queries are
+//     re-served from the SM's L1 instead of L2.
+//   * the scalar geometry of a sampling point (floor, weights, gate) is
+//     computed ONCE, by lane j for point j of the current chunk of G points,
+//     and published to the group through shared memory (broadcast LDS.128)
+//     -- the reference recomputes it in each of the D channel threads
+//     (ms_deform_im2col_cuda.cuh:282-297).
+//   * when every level has H == 1 (the temporal use of the op in this
+//     reference, models/ops/modules/ms_deform_attn.py:114-117) only the two
+//     taps of the single row are ever live; the kernels branch (uniformly)
+//     to a 2-tap body.
+#pragma once
+#include "msda_common.cuh"
+
+namespace msda {
+
+constexpr int kFastThreads = 256;
+
+template <int NT> struct TapMeta;            // what a group needs per point
+template <> struct __align__(16) TapMeta<2> { int off[2]; float w[2]; };
+template <> struct __align__(16) TapMeta<4> { int off[4]; float w[4]; };
+
+template <int G> __device__ __forceinline__ unsigned group_mask(int lane) {
+  if constexpr (G == 32) {
+    return 0xffffffffu;
+  } else {
+    return ((1u << G) - 1u) << (lane & ~(G - 1));
+  }
+}
+
+// x[i] holds this lane's partial for point i (i < G).  On return lane j holds
+// the sum over the group's lanes of x[j].  G-1 shuffles instead of G*log2(G).
+template <int G>
+__device__ __forceinline__ float transpose_reduce(float (&x)[G], int j, unsigned mask) {
+#pragma unroll
+  for (int s = G / 2; s >= 1; s >>= 1) {
+    const bool up = (j & s) != 0;
+#pragma unroll
+    for (int i = 0; i < s; ++i) {
+      const float send = up ? x[i] : x[i + s];
+      const float keep = up ? x[i + s] : x[i];
+      x[i] = keep + __shfl_xor_sync(mask, send, s);
+    }
+  }
+  return x[0];
+}
+
+// Stage (H, W, start) per level and the "all H == 1" flag.
+__device__ __forceinline__ void stage_levels(const int64_t* __restrict__ shapes,
+                                             const int64_t* __restrict__ lsi, int L, int* s_lvl,
+                                             int* s_one_d) {
+  if (threadIdx.x == 0) *s_one_d = 1;
+  __syncthreads();
+  for (int l = threadIdx.x; l < L; l += blockDim.x) {
+    const int H = (int)shapes[2 * l], W = (int)shapes[2 * l + 1];
+    s_lvl[3 * l] = H;
+    s_lvl[3 * l + 1] = W;
+    s_lvl[3 * l + 2] = (int)lsi[l];
+    if (H != 1) *s_one_d = 0;
+  }
+  __syncthreads();
+}
+
+template <typename T> struct LocLoad;
+template <> struct LocLoad<float> {
+  static __device__ __forceinline__ void ld(const float* loc2, const float* aw, float& x, float& y,
+                                            float& a) {
+    const float2 t = __ldcs(reinterpret_cast<const float2*>(loc2));
+    x = t.x; y = t.y; a = __ldcs(aw);
+  }
+  static __device__ __forceinline__ void st(float* gloc2, float* gaw, float gx, float gy, float ga) {
+    __stcs(reinterpret_cast<float2*>(gloc2), make_float2(gx, gy));
+    __stcs(gaw, ga);
+  }
+};
+template <> struct LocLoad<__nv_bfloat16> {
+  static __device__ __forceinline__ void ld(const __nv_bfloat16* loc2, const __nv_bfloat16* aw,
+                                            float& x, float& y, float& a) {
+    const uint32_t t = __ldcs(reinterpret_cast<const unsigned int*>(loc2));
+    x = __uint_as_float(t << 16); y = __uint_as_float(t & 0xffff0000u);
+    a = __bfloat162float(*aw);
+  }
+  static __device__ __forceinline__ void st(__nv_bfloat16* gloc2, __nv_bfloat16* gaw, float gx,
+                                            float gy, float ga) {
+    *reinterpret_cast<__nv_bfloat162*>(gloc2) = __floats2bfloat162_rn(gx, gy);
+    *gaw = __float2bfloat16_rn(ga);
+  }
+};
+
+// Which taps a 2-tap (H == 1) body uses: the top pair (0,1) when row h_low is
+// the map's single row, else the bottom pair (2,3).
+template <int NT> __device__ __forceinline__ int tap_select(const PointGeom<float>& g) {
+  if (NT == 4) return 0;
+  return (g.off[0] >= 0 || g.off[1] >= 0) ? 0 : 2;
+}
+
+// ------------------------------- forward ------------------------------------
+template <typename T, int VEC, int G, int NT>
+__device__ __forceinline__ void fwd_body(const T* __restrict__ value, const T* __restrict__ loc,
+                                         const T* __restrict__ aw, T* __restrict__ out,
+                                         const Dims& d, int b, int m, int q_begin, int q_end,
+                                         const int* s_lvl, TapMeta<NT>* s_meta_cta) {
+  constexpr int NG = kFastThreads / G;
+  const int lane = threadIdx.x & 31;
+  const int gi = threadIdx.x / G;
+  const int j = threadIdx.x % G;
+  const unsigned mask = group_mask<G>(lane);
+  TapMeta<NT>* s_meta = s_meta_cta + gi * G;
+  const int LP = d.L * d.P;
+  const size_t MD = (size_t)d.M * d.D;
+  const T* vbase = value + ((size_t)b * d.S * d.M + m) * d.D + j * VEC;
+
+  for (int q = q_begin + gi; q < q_end; q += NG) {
+    const size_t grp = ((size_t)b * d.Lq + q) * d.M + m;
+    const T* loc_g = loc + grp * LP * 2;
+    const T* aw_g = aw + grp * LP;
+    float acc[VEC];
+#pragma unroll
+    for (int c = 0; c < VEC; ++c) acc[c] = 0.f;
+
+    for (int base = 0; base < LP; base += G) {
+      const int pt = base + j;
+      if (pt < LP) {
+        float lx, ly, a;
+        LocLoad<T>::ld(loc_g + 2 * pt, aw_g + pt, lx, ly, a);
+        const int l = pt / d.P;
+        PointGeom<float> g;
+        point_geom<float>(lx, ly, s_lvl[3 * l], s_lvl[3 * l + 1], s_lvl[3 * l + 2], d.border != 0, g);
+        const bool bot = tap_select<NT>(g) != 0;
+        TapMeta<NT> tm;
+#pragma unroll
+        for (int k = 0; k < NT; ++k) {
+          tm.off[k] = (NT == 2 && bot) ? g.off[(k + 2) & 3] : g.off[k];
+          tm.w[k] = ((NT == 2 && bot) ? g.w[(k + 2) & 3] : g.w[k]) * a;
+        }
+        s_meta[j] = tm;
+      }
+      __syncwarp(mask);
+#pragma unroll
+      for (int i = 0; i < G; ++i) {
+        if (base + i < LP) {
+          const TapMeta<NT> tm = s_meta[i];
+#pragma unroll
+          for (int k = 0; k < NT; ++k) {
+            if (tm.off[k] >= 0) {
+              float v[VEC];
+              VecIO<T, VEC>::ldg(vbase + (size_t)tm.off[k] * MD, v);
+#pragma unroll
+              for (int c = 0; c < VEC; ++c) acc[c] = fmaf(tm.w[k], v[c], acc[c]);
+            }
+          }
+        }
+      }
+      __syncwarp(mask);
+    }
+    VecIO<T, VEC>::st_stream(out + grp * d.D + j * VEC, acc);
+  }
+}
+
+template <typename T, int VEC, int G>
+__global__ void __launch_bounds__(kFastThreads)
+msda_fwd_fast_kernel(const T* __restrict__ value, const int64_t* __restrict__ shapes,
+                     const int64_t* __restrict__ lsi, const T* __restrict__ loc,
+                     const T* __restrict__ aw, T* __restrict__ out, Dims d, int qtile, int nqc) {
+  __shared__ int s_lvl[3 * kMaxLevelsFast];
+  __shared__ int s_one_d;
+  __shared__ TapMeta<4> s_meta[kFastThreads];
+  stage_levels(shapes, lsi, d.L, s_lvl, &s_one_d);
+
+  const int tile = blockIdx.x;
+  const int m = tile % d.M;
+  const int qc = (tile / d.M) % nqc;
+  const int b = tile / (d.M * nqc);
+  const int q_begin = qc * qtile;
+  const int q_end = min(q_begin + qtile, d.Lq);
+  if (s_one_d)
+    fwd_body<T, VEC, G, 2>(value, loc, aw, out, d, b, m, q_begin, q_end, s_lvl,
+                           reinterpret_cast<TapMeta<2>*>(s_meta));
+  else
+    fwd_body<T, VEC, G, 4>(value, loc, aw, out, d, b, m, q_begin, q_end, s_lvl, s_meta);
+}
+
+// ------------------------------- backward -----------------------------------
+// grad_value is accumulated in fp32 with 128-bit `red.global.add.v4.f32`
+// (for bf16 storage into an fp32 workspace image that a second kernel rounds).
+// grad_sampling_loc / grad_attn_weight need, per point, the dot products
+// <grad_out, v_k> over the head's D channels: each lane keeps its partial for
+// the G points of the chunk and one transpose-reduce hands point j's totals to
+// lane j, which owns that point's geometry and writes its three gradients
+// (.cuh:115-159 for the math).
+template <typename T, int VEC, int G, int NT>
+__device__ __forceinline__ void bwd_body(const T* __restrict__ value, const T* __restrict__ loc,
+                                         const T* __restrict__ aw, const T* __restrict__ gout,
+                                         float* __restrict__ gvalue, T* __restrict__ gloc,
+                                         T* __restrict__ gaw, const Dims& d, int b, int m,
+                                         int q_begin, int q_end, const int* s_lvl,
+                                         TapMeta<NT>* s_meta_cta) {
+  constexpr int NG = kFastThreads / G;
+  const int lane = threadIdx.x & 31;
+  const int gi = threadIdx.x / G;
+  const int j = threadIdx.x % G;
+  const unsigned mask = group_mask<G>(lane);
+  TapMeta<NT>* s_meta = s_meta_cta + gi * G;
+  const int LP = d.L * d.P;
+  const size_t MD = (size_t)d.M * d.D;
+  const size_t voff = ((size_t)b * d.S * d.M + m) * d.D + j * VEC;
+  const T* vbase = value + voff;
+  float* gvbase = gvalue + voff;
+
+  for (int q = q_begin + gi; q < q_end; q += NG) {
+    const size_t grp = ((size_t)b * d.Lq + q) * d.M + m;
+    const T* loc_g = loc + grp * LP * 2;
+    const T* aw_g = aw + grp * LP;
+    float go[VEC];
+    VecIO<T, VEC>::ld_stream(gout + grp * d.D + j * VEC, go);
+
+    for (int base = 0; base < LP; base += G) {
+      const int pt = base + j;
+      float cw[NT], cx[NT], cy[NT];
+#pragma unroll
+      for (int k = 0; k < NT; ++k) cw[k] = cx[k] = cy[k] = 0.f;
+      if (pt < LP) {
+        float lx, ly, a;
+        LocLoad<T>::ld(loc_g + 2 * pt, aw_g + pt, lx, ly, a);
+        const int l = pt / d.P;
+        PointGeom<float> g;
+        point_geom<float>(lx, ly, s_lvl[3 * l], s_lvl[3 * l + 1], s_lvl[3 * l + 2], d.border != 0, g);
+        const bool bot = tap_select<NT>(g) != 0;
+        const float hh = 1.f - g.lh, hw = 1.f - g.lw;
+        const float dx[4] = {-hh, hh, -g.lh, g.lh};
+        const float dy[4] = {-hw, -g.lw, hw, g.lw};
+        TapMeta<NT> tm;
+#pragma unroll
+        for (int k = 0; k < NT; ++k) {
+          const bool alt = (NT == 2) && bot;
+          const int k2 = (k + 2) & 3;
+          tm.off[k] = alt ? g.off[k2] : g.off[k];
+          cw[k] = alt ? g.w[k2] : g.w[k];
+          tm.w[k] = cw[k] * a;
+          cx[k] = (alt ? dx[k2] : dx[k]) * g.sx * a;
+          cy[k] = (alt ? dy[k2] : dy[k]) * g.sy * a;
+        }
+        s_meta[j] = tm;
+      }
+      __syncwarp(mask);
+      float dot[NT][G];
+#pragma unroll
+      for (int i = 0; i < G; ++i) {
+#pragma unroll
+        for (int k = 0; k < NT; ++k) dot[k][i] = 0.f;
+        if (base + i < LP) {
+          const TapMeta<NT> tm = s_meta[i];
+#pragma unroll
+          for (int k = 0; k < NT; ++k) {
+            if (tm.off[k] >= 0) {
+              const size_t ro = (size_t)tm.off[k] * MD;
+              float v[VEC];
+              VecIO<T, VEC>::ldg(vbase + ro, v);
+              float s = 0.f;
+#pragma unroll
+              for (int c = 0; c < VEC; ++c) s = fmaf(go[c], v[c], s);
+              dot[k][i] = s;
+#pragma unroll
+              for (int c = 0; c < VEC; c += 4)
+                red_add_f32x4(gvbase + ro + c, tm.w[k] * go[c], tm.w[k] * go[c + 1],
+                              tm.w[k] * go[c + 2], tm.w[k] * go[c + 3]);
+            }
+          }
+        }
+      }
+      float ga = 0.f, gx = 0.f, gy = 0.f;
+#pragma unroll
+      for (int k = 0; k < NT; ++k) {
+        const float r = transpose_reduce<G>(dot[k], j, mask);
+        ga = fmaf(cw[k], r, ga);
+        gx = fmaf(cx[k], r, gx);
+        gy = fmaf(cy[k], r, gy);
+      }
+      if (pt < LP) LocLoad<T>::st(gloc + (grp * LP + pt) * 2, gaw + grp * LP + pt, gx, gy, ga);
+      __syncwarp(mask);
+    }
+  }
+}
+
+template <typename T, int VEC, int G>
+__global__ void __launch_bounds__(kFastThreads)
+msda_bwd_fast_kernel(const T* __restrict__ value, const int64_t* __restrict__ shapes,
+                     const int64_t* __restrict__ lsi, const T* __restrict__ loc,
+                     const T* __restrict__ aw, const T* __restrict__ gout,
+                     float* __restrict__ gvalue, T* __restrict__ gloc, T* __restrict__ gaw, Dims d,
+                     int qtile, int nqc) {
+  __shared__ int s_lvl[3 * kMaxLevelsFast];
+  __shared__ int s_one_d;
+  __shared__ TapMeta<4> s_meta[kFastThreads];
+  stage_levels(shapes, lsi, d.L, s_lvl, &s_one_d);
+
+  const int tile = blockIdx.x;
+  const int m = tile % d.M;
+  const int qc = (tile / d.M) % nqc;
+  const int b = tile / (d.M * nqc);
+  const int q_begin = qc * qtile;
+  const int q_end = min(q_begin + qtile, d.Lq);
+  if (s_one_d)
+    bwd_body<T, VEC, G, 2>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q_begin, q_end, s_lvl,
+                           reinterpret_cast<TapMeta<2>*>(s_meta));
+  else
+    bwd_body<T, VEC, G, 4>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q_begin, q_end, s_lvl,
+                           s_meta);
+}
+
+// fp32 accumulation image -> bf16 grad_value
+__global__ void __launch_bounds__(256)
+msda_round_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, size_t n8) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const float4 a = __ldcs(reinterpret_cast<const float4*>(src) + 2 * i);
+    const float4 b = __ldcs(reinterpret_cast<const float4*>(src) + 2 * i + 1);
+    const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    VecIO<__nv_bfloat16, 8>::st_stream(dst + 8 * i, v);
+  }
+}
+
+}  // namespace msda

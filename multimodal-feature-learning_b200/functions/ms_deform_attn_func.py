@@ -1,0 +1,85 @@
+"""Autograd surface of the op -- drop-in for
+models/ops/functions/ms_deform_attn_func.py:23-41 (twin: models/modules/attention.py:311-328).
+
+``MSDeformAttnFunction.apply(value, value_spatial_shapes, value_level_start_index,
+sampling_locations, attention_weights, im2col_step)`` keeps the reference's
+positional signature, output shape [N, Lq, M*D] and backward return pattern
+``(grad_value, None, None, grad_sampling_loc, grad_attn_weight, None)``.
+"""
+import torch
+from torch.autograd import Function
+from torch.autograd.function import once_differentiable
+
+from .. import MultiScaleDeformableAttention as MSDA
+
+
+class _MSDeformAttnBase(Function):
+    """Shared forward/backward; subclasses fix the padding mode so that
+    ``apply`` keeps exactly six positional arguments."""
+
+    padding_mode = "zeros"
+
+    @classmethod
+    def _fwd(cls, ctx, value, value_spatial_shapes, value_level_start_index,
+             sampling_locations, attention_weights, im2col_step):
+        ctx.im2col_step = im2col_step
+        output = MSDA.ms_deform_attn_forward(
+            value, value_spatial_shapes, value_level_start_index, sampling_locations,
+            attention_weights, ctx.im2col_step, padding_mode=cls.padding_mode)
+        ctx.save_for_backward(value, value_spatial_shapes, value_level_start_index,
+                              sampling_locations, attention_weights)
+        return output
+
+    @classmethod
+    def _bwd(cls, ctx, grad_output):
+        value, shapes, lsi, loc, aw = ctx.saved_tensors
+        grad_value, grad_loc, grad_aw = MSDA.ms_deform_attn_backward(
+            value, shapes, lsi, loc, aw, grad_output, ctx.im2col_step,
+            padding_mode=cls.padding_mode)
+        return grad_value, None, None, grad_loc, grad_aw, None
+
+
+class MSDeformAttnFunction(_MSDeformAttnBase):
+    """Zero padding outside the map == the reference CUDA op
+    (ms_deform_im2col_cuda.cuh:56-79, :289)."""
+
+    padding_mode = "zeros"
+
+    @staticmethod
+    def forward(ctx, value, value_spatial_shapes, value_level_start_index, sampling_locations,
+                attention_weights, im2col_step):
+        return MSDeformAttnFunction._fwd(ctx, value, value_spatial_shapes, value_level_start_index,
+                                         sampling_locations, attention_weights, im2col_step)
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, grad_output):
+        return MSDeformAttnFunction._bwd(ctx, grad_output)
+
+
+class MSDeformAttnBorderFunction(_MSDeformAttnBase):
+    """Border padding == the reference's PyTorch path, which every transformer
+    in the reference actually runs (grid_sample padding_mode='border',
+    ms_deform_attn_func.py:61-62 / models/modules/attention.py:367-368)."""
+
+    padding_mode = "border"
+
+    @staticmethod
+    def forward(ctx, value, value_spatial_shapes, value_level_start_index, sampling_locations,
+                attention_weights, im2col_step):
+        return MSDeformAttnBorderFunction._fwd(ctx, value, value_spatial_shapes,
+                                               value_level_start_index, sampling_locations,
+                                               attention_weights, im2col_step)
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, grad_output):
+        return MSDeformAttnBorderFunction._bwd(ctx, grad_output)
+
+
+def ms_deform_attn(value, value_spatial_shapes, value_level_start_index, sampling_locations,
+                   attention_weights, im2col_step=64, padding_mode="zeros"):
+    """Functional form with a selectable padding mode."""
+    fn = {"zeros": MSDeformAttnFunction, "border": MSDeformAttnBorderFunction}[padding_mode]
+    return fn.apply(value, value_spatial_shapes, value_level_start_index, sampling_locations,
+                    attention_weights, im2col_step)

@@ -1,0 +1,33 @@
+"""TEST INFRASTRUCTURE -- port of the reference's pure-PyTorch core.
+
+Restates ms_deform_attn_core_pytorch
+(models/ops/functions/ms_deform_attn_func.py:44-71; 1-D twin at
+models/modules/attention.py:331-383): per level, view the value slab as an
+image batch (N*M, D, H, W), bilinearly sample it with F.grid_sample at
+2*loc-1 (align_corners=False), weight by the attention weights and sum over
+levels*points.  The reference hard-codes padding_mode='border'; here it is a
+parameter so the same code also yields the zero-padded variant (= what the
+reference CUDA kernel computes).  This is the CPU baseline bench.py times
+(cpu_baseline.kind = "port") and one of the oracles the tests use.
+"""
+import torch
+import torch.nn.functional as F
+
+
+def ms_deform_attn_core_pytorch(value, value_spatial_shapes, sampling_locations, attention_weights,
+                                padding_mode="border"):
+    n, _, m, d = value.shape
+    _, lq, _, n_lvl, n_pt, _ = sampling_locations.shape
+    sizes = [(int(h), int(w)) for h, w in value_spatial_shapes.tolist()]
+    slabs = value.split([h * w for h, w in sizes], dim=1)
+    grid = sampling_locations * 2 - 1
+    sampled = []
+    for lvl, (h, w) in enumerate(sizes):
+        img = slabs[lvl].permute(0, 2, 3, 1).reshape(n * m, d, h, w)
+        g = grid[:, :, :, lvl].permute(0, 2, 1, 3, 4).reshape(n * m, lq, n_pt, 2)
+        sampled.append(F.grid_sample(img, g, mode="bilinear", padding_mode=padding_mode,
+                                     align_corners=False))          # (N*M, D, Lq, P)
+    stacked = torch.cat(sampled, dim=-1)                             # (N*M, D, Lq, L*P)
+    w = attention_weights.permute(0, 2, 1, 3, 4).reshape(n * m, 1, lq, n_lvl * n_pt)
+    out = (stacked * w).sum(-1)                                      # (N*M, D, Lq)
+    return out.view(n, m * d, lq).permute(0, 2, 1).contiguous()

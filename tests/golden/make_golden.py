@@ -1,0 +1,128 @@
+"""Generate the golden fixtures in tests/golden/*.npz FROM THE REFERENCE ITSELF.
+
+Run in the build container only (needs /root/reference, which does not exist
+on the GPU box):      python tests/golden/make_golden.py
+
+It imports, by file path and unmodified,
+  * models/ops/functions/ms_deform_attn_func.py  (ms_deform_attn_core_pytorch, 2-D form, :44-71)
+  * models/modules/attention.py                  (ms_deform_attn_core_pytorch, 1-D live twin, :331-383)
+runs them on seeded inputs (the tiny case reproduces models/ops/test.py:23-44:
+N=1, M=2, D=2, Lq=2, L=2, P=2, shapes (6,4),(3,2), torch.manual_seed(3)) and
+stores inputs, outputs and autograd gradients.
+
+Two padding variants are stored per case:
+  border : the reference function exactly as written (padding_mode='border').
+  zeros  : the SAME reference function executed with F.grid_sample's
+           padding_mode argument overridden to 'zeros' -- the CPU-available
+           stand-in for the reference CUDA kernel's zero padding
+           (ms_deform_im2col_cuda.cuh:56-79, :289); SURVEY.md section 8(c) oracle (3).
+"""
+import importlib.util
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+REF = "/root/reference"
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _load(path, name):
+    spec = importlib.util.spec_from_file_location(name, path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+ref_ops = _load(os.path.join(REF, "models/ops/functions/ms_deform_attn_func.py"), "ref_ops_func")
+ref_live = _load(os.path.join(REF, "models/modules/attention.py"), "ref_live_attention")
+
+_real_grid_sample = F.grid_sample
+
+
+class _force_padding:
+    """Run the reference with grid_sample(padding_mode=<mode>) -- one argument differs."""
+
+    def __init__(self, mode):
+        self.mode = mode
+
+    def __enter__(self):
+        def patched(inp, grid, mode="bilinear", padding_mode="zeros", align_corners=None):
+            return _real_grid_sample(inp, grid, mode=mode, padding_mode=self.mode,
+                                     align_corners=align_corners)
+        F.grid_sample = patched
+
+    def __exit__(self, *a):
+        F.grid_sample = _real_grid_sample
+
+
+def run_ref(fn, value, shapes_arg, loc_arg, aw, grad_out, padding):
+    value = value.clone().requires_grad_(True)
+    loc_arg = loc_arg.clone().requires_grad_(True)
+    aw = aw.clone().requires_grad_(True)
+    if padding == "border":
+        out = fn(value, shapes_arg, loc_arg, aw)
+    else:
+        with _force_padding(padding):
+            out = fn(value, shapes_arg, loc_arg, aw)
+    out.backward(grad_out)
+    return out.detach(), value.grad, loc_arg.grad, aw.grad
+
+
+def make_case(name, seed, N, M, D, Lq, P, shapes_hw, dtype, loc_range=(0.0, 1.0), interior=False,
+              one_d_twin=False, value_scale=0.01):
+    torch.manual_seed(seed)
+    shapes = torch.as_tensor(shapes_hw, dtype=torch.long)
+    L = shapes.shape[0]
+    lsi = torch.cat((shapes.new_zeros((1,)), shapes.prod(1).cumsum(0)[:-1]))
+    S = int(shapes.prod(1).sum())
+    value = (torch.rand(N, S, M, D) * value_scale).to(dtype)
+    lo, hi = loc_range
+    loc = (torch.rand(N, Lq, M, L, P, 2) * (hi - lo) + lo).to(dtype)
+    if interior:  # keep every tap inside the map so zeros == border
+        wh = torch.stack((shapes[:, 1], shapes[:, 0]), -1).to(dtype)[None, None, None, :, None, :]
+        loc = (0.5 + loc * (wh - 1)) / wh
+    if one_d_twin:
+        assert all(h == 1 for h, _ in shapes_hw)
+        loc[..., 1] = 0.5
+    aw = torch.rand(N, Lq, M, L, P) + 1e-5
+    aw = (aw / aw.sum(-1, keepdim=True).sum(-2, keepdim=True)).to(dtype)
+    grad_out = torch.randn(N, Lq, M * D).to(dtype)
+    rec = dict(value=value, shapes=shapes, lsi=lsi, loc=loc, aw=aw, grad_out=grad_out)
+    for padding in ("border", "zeros"):
+        o, gv, gl, ga = run_ref(ref_ops.ms_deform_attn_core_pytorch, value, shapes, loc, aw, grad_out,
+                                padding)
+        rec.update({"out_" + padding: o, "gvalue_" + padding: gv, "gloc_" + padding: gl,
+                    "gaw_" + padding: ga})
+    if one_d_twin:
+        # the live 1-D twin takes shapes [L,1] (T_l) and loc [...,1]; must agree with the 2-D form
+        o, gv, gl, ga = run_ref(ref_live.ms_deform_attn_core_pytorch, value, shapes[:, 1:].contiguous(),
+                                loc[..., :1].contiguous(), aw, grad_out, "border")
+        rec.update(dict(out_live=o, gvalue_live=gv, gloc_live=gl, gaw_live=ga))
+    np.savez_compressed(os.path.join(HERE, name + ".npz"),
+                        **{k: v.numpy() for k, v in rec.items()})
+    print(name, {k: tuple(v.shape) for k, v in rec.items() if k.startswith(("value", "loc"))})
+
+
+def main():
+    # models/ops/test.py:17-44 (the only shapes/seeds the reference's tests fix)
+    make_case("testpy_tiny_f64", 3, 1, 2, 2, 2, 2, [(6, 4), (3, 2)], torch.float64)
+    make_case("testpy_tiny_f32", 3, 1, 2, 2, 2, 2, [(6, 4), (3, 2)], torch.float32)
+    # 2-D, odd channel count, locations spilling outside the map (gate / clamping edge cases)
+    make_case("edge2d_f64", 11, 2, 3, 5, 7, 3, [(5, 7), (3, 4), (1, 2)], torch.float64,
+              loc_range=(-0.3, 1.3))
+    # temporal (H == 1) use of the op, as every transformer in the reference calls it
+    make_case("temporal_f64", 21, 2, 4, 8, 12, 4, [(1, 16), (1, 8), (1, 4), (1, 2)], torch.float64,
+              loc_range=(-0.1, 1.1), one_d_twin=True)
+    make_case("temporal_f32", 22, 2, 8, 16, 20, 4, [(1, 38), (1, 19), (1, 10), (1, 5)], torch.float32,
+              loc_range=(-0.1, 1.1), one_d_twin=True)
+    # interior-only locations: zeros and border coincide
+    make_case("interior2d_f32", 31, 2, 2, 8, 9, 4, [(6, 5), (3, 3)], torch.float32, interior=True)
+
+
+if __name__ == "__main__":
+    if not os.path.isdir(REF):
+        sys.exit("needs %s (build container only)" % REF)
+    main()

@@ -1,0 +1,101 @@
+"""CPU suite: the C-ABI library builds, loads and exports every symbol
+include/msda_b200.h declares; argument validation that needs no GPU."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+import mfl_b200
+from mfl_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    if not os.path.exists(_lib.LIB_PATH):
+        _lib.build()
+    return _lib.load()
+
+
+def test_header_symbols_exported(lib):
+    header = open(os.path.join(ROOT, "include", "msda_b200.h")).read()
+    declared = set(re.findall(r"\b(msda_[a-z_0-9]+)\s*\(", header))
+    assert declared == set(_lib.EXPORTED_SYMBOLS)
+    for name in declared:
+        assert hasattr(lib, name), name
+
+
+def test_abi_version_and_strings(lib):
+    assert lib.msda_abi_version() == 1
+    assert lib.msda_error_string(0) == b"ok"
+    assert b"dtype" in lib.msda_error_string(-3)
+    assert lib.msda_kernel_family(64, _lib.MSDA_F32, 0) == b"fast"
+    assert lib.msda_kernel_family(64, _lib.MSDA_BF16, 0) == b"fast"
+    assert lib.msda_kernel_family(64, _lib.MSDA_F64, 0) == b"generic"
+    assert lib.msda_kernel_family(30, _lib.MSDA_F32, 0) == b"generic"
+    assert lib.msda_kernel_family(64, _lib.MSDA_F32, _lib.MSDA_FLAG_FORCE_GENERIC) == b"generic"
+
+
+def test_argument_validation_without_gpu(lib):
+    # rejected before anything touches CUDA
+    z = ctypes.c_void_p(0)
+    assert lib.msda_forward(z, z, z, z, z, z, 1, 1, 0, 4, 1, 1, 1, 0, 0, 0, z) == -2   # M = 0
+    assert lib.msda_forward(z, z, z, z, z, z, 1, 1, 1, 4, 1, 1, 1, 7, 0, 0, z) == -3   # dtype
+    assert lib.msda_forward(z, z, z, z, z, z, 1, 1, 1, 4, 1, 1, 1, 0, 5, 0, z) == -4   # padding
+    assert lib.msda_forward(z, z, z, z, z, z, 1, 1, 1, 4, 1, 1, 1, 0, 0, 0, z) == -1   # null ptrs
+    assert lib.msda_forward(z, z, z, z, z, z, 1, 2 ** 31, 1, 4, 1, 1, 1, 0, 0, 0, z) == -5
+    assert lib.msda_forward(z, z, z, z, z, z, 0, 1, 1, 4, 1, 1, 1, 0, 0, 0, z) == 0    # empty batch
+    assert lib.msda_backward_workspace_bytes(2, 3, 4, 8, 1, 1, 1, _lib.MSDA_F32) == 0
+    assert lib.msda_backward_workspace_bytes(2, 3, 4, 8, 1, 1, 1, _lib.MSDA_BF16) == 2 * 3 * 4 * 8 * 4
+
+
+def _cpu_inputs():
+    value = torch.rand(2, 6, 2, 4)
+    shapes = torch.tensor([[1, 4], [1, 2]])
+    lsi = torch.tensor([0, 4])
+    loc = torch.rand(2, 3, 2, 2, 2, 2)
+    aw = torch.rand(2, 3, 2, 2, 2)
+    return value, shapes, lsi, loc, aw
+
+
+def test_cpu_tensors_raise_like_reference():
+    # models/ops/src/ms_deform_attn.h:38 -- AT_ERROR("Not implemented on the CPU")
+    with pytest.raises(RuntimeError, match="Not implemented on the CPU"):
+        mfl_b200.MSDeformAttnFunction.apply(*_cpu_inputs(), 64)
+    m = mfl_b200.MSDeformAttn(d_model=32, n_levels=2, n_heads=4, n_points=2)
+    with pytest.raises(RuntimeError, match="Not implemented on the CPU"):
+        m(torch.rand(1, 3, 32), torch.rand(1, 3, 2, 1), torch.rand(1, 6, 32),
+          torch.tensor([4, 2]), torch.tensor([0, 4]))
+
+
+def test_module_surface_matches_reference():
+    # state-dict keys / shapes; ctor errors (ms_deform_attn.py:40-41)
+    m = mfl_b200.MSDeformAttn(d_model=512, n_levels=4, n_heads=8, n_points=4)
+    sd = {k: tuple(v.shape) for k, v in m.state_dict().items()}
+    assert sd == {
+        "sampling_offsets.weight": (128, 512), "sampling_offsets.bias": (128,),
+        "attention_weights.weight": (128, 512), "attention_weights.bias": (128,),
+        "value_proj.weight": (512, 512), "value_proj.bias": (512,),
+        "output_proj.weight": (512, 512), "output_proj.bias": (512,)}
+    assert m.im2col_step == 64
+    with pytest.raises(ValueError):
+        mfl_b200.MSDeformAttn(d_model=30, n_heads=8)
+    # bias grid: head direction cos(2*pi*m/M) sign-normalised, times (p+1)  (ms_deform_attn.py:64-71)
+    b = m.sampling_offsets.bias.detach().view(8, 4, 4)
+    assert torch.allclose(b[0, 0], torch.tensor([1., 2., 3., 4.]))
+    assert torch.allclose(b[4, 2], torch.tensor([-1., -2., -3., -4.]))
+    assert float(b[2].abs().max()) < 1e-6
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "multimodal-feature-learning_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".sh")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in text and "from oracle" not in text, f
+                if f.endswith(".py"):
+                    assert "F.grid_sample(" not in text, f

@@ -1,0 +1,150 @@
+"""GPU suite at BASELINE.json's full sizes (ENC / DEC): live comparison with the
+oracle port of the reference's PyTorch path run on the same GPU, with the
+reference's own CUDA op when oracle/_ref is present, and size-independent
+properties (linearity in value / weights, partition of unity, determinism of the
+forward, im2col_step independence)."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+import mfl_b200  # noqa: E402
+from mfl_b200 import MultiScaleDeformableAttention as MSDA  # noqa: E402
+from mfl_b200 import synthetic  # noqa: E402
+from mfl_b200.functions.ms_deform_attn_func import ms_deform_attn  # noqa: E402
+from oracle import ref_cuda  # noqa: E402
+from oracle.core_pytorch import ms_deform_attn_core_pytorch  # noqa: E402
+
+DEV = "cuda"
+
+
+def rel(a, b):
+    return float((a.double() - b.double()).abs().max() / b.double().abs().max().clamp_min(1e-30))
+
+
+def _grads(fn, inp):
+    v, loc, aw = (inp[k].detach().clone().requires_grad_(True) for k in ("value", "loc", "aw"))
+    out = fn(v, loc, aw)
+    out.backward(inp["grad_out"].view_as(out))
+    return out.detach(), v.grad, loc.grad, aw.grad
+
+
+@pytest.mark.parametrize("workload", ["ENC", "DEC"])
+@pytest.mark.parametrize("dist", ["model", "uniform"])
+@pytest.mark.parametrize("padding", ["zeros", "border"])
+def test_fullsize_fp32_vs_torch_port_on_gpu(workload, dist, padding):
+    inp = synthetic.make_workload(workload, torch.float32, DEV, seed=42, dist=dist, value="small")
+    got = _grads(lambda v, loc, aw: ms_deform_attn(v, inp["shapes"], inp["lsi"], loc, aw, 64, padding), inp)
+    want = _grads(lambda v, loc, aw: ms_deform_attn_core_pytorch(v, inp["shapes"], loc, aw, padding), inp)
+    assert float((got[0] - want[0]).abs().max()) <= 1e-5          # forward max-abs, value in [0, 0.01)
+    assert rel(got[1], want[1]) <= 1e-4                            # grad_value
+    assert rel(got[3], want[3]) <= 1e-4                            # grad_attn_weight
+    assert rel(got[2], want[2]) <= 1e-4                            # grad_sampling_loc (x and y)
+
+
+@pytest.mark.parametrize("workload", ["ENC", "DEC"])
+def test_fullsize_bf16_vs_fp32_kernel_on_rounded_inputs(workload):
+    inp = synthetic.make_workload(workload, torch.bfloat16, DEV, seed=43, dist="model", value="normal")
+    f32 = {k: (v.float() if v.is_floating_point() else v) for k, v in inp.items()}
+    got = _grads(lambda v, loc, aw: ms_deform_attn(v, inp["shapes"], inp["lsi"], loc, aw, 64), inp)
+    want = _grads(lambda v, loc, aw: ms_deform_attn(v, inp["shapes"], inp["lsi"], loc, aw, 64), f32)
+    assert rel(got[0].float(), want[0]) <= 2.0 ** -7
+    for g, w in zip(got[1:], want[1:]):
+        assert rel(g.float(), w) <= 2e-2
+
+
+@pytest.mark.skipif(not ref_cuda.available(), reason="oracle/_ref (reference CUDA op) not built")
+@pytest.mark.parametrize("workload", ["ENC", "DEC"])
+@pytest.mark.parametrize("dist", ["model", "uniform"])
+def test_fullsize_vs_reference_cuda_op(workload, dist):
+    """The reference's own kernels (zero padding), compiled unmodified for sm_100a."""
+    ref = ref_cuda.load()
+    inp = synthetic.make_workload(workload, torch.float32, DEV, seed=44, dist=dist, value="small")
+    a = [inp[k] for k in ("value", "shapes", "lsi", "loc", "aw")]
+    want_out = ref.ms_deform_attn_forward(*a, 64)
+    want_g = ref.ms_deform_attn_backward(*a, inp["grad_out"], 64)
+    got_out = MSDA.ms_deform_attn_forward(*a, 64)
+    got_g = MSDA.ms_deform_attn_backward(*a, inp["grad_out"], 64)
+    assert float((got_out - want_out).abs().max()) <= 1e-5
+    for g, w in zip(got_g, want_g):
+        assert rel(g, w) <= 1e-4
+
+
+@pytest.mark.skipif(not ref_cuda.available(), reason="oracle/_ref (reference CUDA op) not built")
+@pytest.mark.parametrize("channels", [30, 32, 64, 71, 1025, 2048, 3096])
+def test_sweep_vs_reference_cuda_op_fp64(channels):
+    """configs[2]: the reference's gradcheck channel sweep, fp64, 2-D shapes, im2col_step 64."""
+    ref = ref_cuda.load()
+    inp = synthetic.make_inputs(2, 5, 2, channels, 2, [(6, 4), (3, 2)], torch.float64, DEV, seed=channels,
+                                dist="spill")
+    a = [inp[k] for k in ("value", "shapes", "lsi", "loc", "aw")]
+    torch.testing.assert_close(MSDA.ms_deform_attn_forward(*a, 64), ref.ms_deform_attn_forward(*a, 64),
+                               rtol=1e-10, atol=1e-14)
+    for g, w in zip(MSDA.ms_deform_attn_backward(*a, inp["grad_out"], 64),
+                    ref.ms_deform_attn_backward(*a, inp["grad_out"], 64)):
+        torch.testing.assert_close(g, w, rtol=1e-10, atol=1e-14)
+
+
+def test_fullsize_properties():
+    inp = synthetic.make_workload("ENC", torch.float32, DEV, seed=45, dist="uniform", value="normal")
+    s, l, loc, aw, v = inp["shapes"], inp["lsi"], inp["loc"], inp["aw"], inp["value"]
+    f = lambda value, weights: MSDA.ms_deform_attn_forward(value, s, l, loc, weights, 64)  # noqa: E731
+    out = f(v, aw)
+    assert torch.equal(out, f(v, aw))                                   # forward is deterministic
+    assert torch.equal(out, MSDA.ms_deform_attn_forward(v, s, l, loc, aw, 16))   # im2col_step independent
+    v2 = torch.randn_like(v)
+    lin = f(v * 0.5 + v2 * 2.0, aw)
+    assert rel(lin, out * 0.5 + f(v2, aw) * 2.0) <= 1e-5                # linear in value
+    assert rel(f(v, aw * 3.0), out * 3.0) <= 1e-6                       # linear in the weights
+    # constant value + interior locations + softmaxed weights => partition of unity
+    inp2 = synthetic.make_workload("ENC", torch.float32, DEV, seed=46, dist="model", value="normal")
+    loc_in = inp2["loc"].clone()
+    W = s[:, 1].float()[None, None, None, :, None]
+    loc_in[..., 0] = torch.minimum(torch.maximum(loc_in[..., 0], 0.5 / W), 1 - 0.5 / W)
+    ones = torch.ones_like(v)
+    o = MSDA.ms_deform_attn_forward(ones, s, l, loc_in, inp2["aw"], 64)
+    assert float((o - 1).abs().max()) <= 1e-5
+    # grad_value conserves mass: sum_rows grad_value == sum_queries grad_out (same constant-1 argument)
+    gv, gl, ga = MSDA.ms_deform_attn_backward(ones, s, l, loc_in, inp2["aw"], inp2["grad_out"], 64)
+    want = inp2["grad_out"].view(16, -1, 8, 64).sum(1)
+    assert rel(gv.sum(1), want) <= 1e-4
+    assert float(gl[..., 0].abs().max()) <= 1e-3 * float(want.abs().max())   # constant field: no location gradient
+
+
+def test_module_matches_torch_composition():
+    """MSDeformAttn (drop-in module) == the reference module's arithmetic with the PyTorch core."""
+    torch.manual_seed(0)
+    T = [64, 32, 16, 8]
+    m = mfl_b200.MSDeformAttn(d_model=256, n_levels=4, n_heads=8, n_points=4, padding_mode="border",
+                              attn_weight_init="xavier").to(DEV)
+    with torch.no_grad():
+        m.sampling_offsets.weight.normal_(0, 0.02)
+    N, S, Lq = 3, sum(T), 50
+    shapes = torch.tensor(T, device=DEV)
+    lsi = torch.cat((shapes.new_zeros(1), shapes.cumsum(0)[:-1]))
+    q = torch.randn(N, Lq, 256, device=DEV, requires_grad=True)
+    x = torch.randn(N, S, 256, device=DEV, requires_grad=True)
+    ref_pts = torch.rand(N, Lq, 4, 1, device=DEV)
+    mask = torch.zeros(N, S, dtype=torch.bool, device=DEV)
+    mask[1, 100:] = True
+    out, loc, aw = m(q, ref_pts, x, shapes, lsi, mask, is_sparse=True)
+    out.sum().backward()
+    g_q, g_x = q.grad.clone(), x.grad.clone()
+    g_w = m.sampling_offsets.weight.grad.clone()
+    q.grad = x.grad = None
+    m.zero_grad()
+    # composition (ms_deform_attn.py:95-125) with the oracle core
+    value = m.value_proj(x).masked_fill(mask[..., None], 0.).view(N, S, 8, 32)
+    off = m.sampling_offsets(q).view(N, Lq, 8, 4, 4)
+    w = torch.softmax(m.attention_weights(q).view(N, Lq, 8, 16), -1).view(N, Lq, 8, 4, 4)
+    loc1 = ref_pts[:, :, None, :, None, 0] + off / shapes[None, None, None, :, None]
+    loc2 = torch.stack((loc1, torch.full_like(loc1, 0.5)), -1)
+    shapes2 = torch.stack((torch.ones_like(shapes), shapes), -1)
+    want = m.output_proj(ms_deform_attn_core_pytorch(value, shapes2, loc2, w, "border"))
+    want.sum().backward()
+    assert loc.shape == (N, Lq, 8, 4, 4, 1) and aw.shape == (N, Lq, 8, 4, 4)
+    torch.testing.assert_close(out, want, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(g_q, q.grad, rtol=1e-3, atol=1e-5)
+    torch.testing.assert_close(g_x, x.grad, rtol=1e-3, atol=1e-5)
+    torch.testing.assert_close(g_w, m.sampling_offsets.weight.grad, rtol=1e-3, atol=1e-4)
