@@ -293,12 +293,10 @@ def run_ours(args):
     t1 = time.time()
     clocks = sampler.stop(t0, t1) if rank == 0 else None
 
+    from mfl_b200 import sharding
+
     def max_over_ranks(x):
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+        return sharding.max_over_ranks(x, dev)
 
     total_ms = max_over_ranks(total_ms)
     ms_per_step = total_ms / args.steps
