@@ -76,9 +76,8 @@ typedef enum {
 #define MSDA_FLAG_SKIP_ZERO_FILL 2u /* msda_backward: the caller has already
                                       zeroed the accumulation target (grad_value
                                       for f32/f64, the workspace for bf16) */
-#define MSDA_FLAG_NO_BAND 4u        /* never use the band-window kernels */
-#define MSDA_FLAG_FORCE_BAND 8u     /* use them whenever they are instantiated for
-                                      the shape (experimental, opt-in) */
+#define MSDA_FLAG_NO_WINDOW 4u      /* never use the row-window kernels
+                                      (msda_win.cuh); per-tap kernels only */
 /* bits 8..19: queries-per-tile multiplier override for the vectorised kernels
  * (0 = heuristic); a tuning knob, results do not depend on it. */
 #define MSDA_FLAG_QTILE(k) (((unsigned)(k) & 0xfffu) << 8)

@@ -17,8 +17,7 @@ MSDA_F32, MSDA_F64, MSDA_BF16 = 0, 1, 2
 MSDA_PAD_ZEROS, MSDA_PAD_BORDER = 0, 1
 MSDA_FLAG_FORCE_GENERIC = 1
 MSDA_FLAG_SKIP_ZERO_FILL = 2
-MSDA_FLAG_NO_BAND = 4
-MSDA_FLAG_FORCE_BAND = 8
+MSDA_FLAG_NO_WINDOW = 4
 
 
 def flag_qtile(k):

@@ -4,9 +4,9 @@
 // (models/ops/src/cuda/ms_deform_attn_cuda.cu:20-153) and the D-dispatch table
 // ms_deformable_col2im_cuda (ms_deform_im2col_cuda.cuh:957-1328).
 #include "../../include/msda_b200.h"
-#include "msda_band.cuh"
 #include "msda_fast.cuh"
 #include "msda_generic.cuh"
+#include "msda_win.cuh"
 
 using namespace msda;
 
@@ -105,30 +105,41 @@ int launch_bwd_fast(const void* value, const int64_t* shapes, const int64_t* lsi
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
 }
 
-// Band-window kernels (msda_band.cuh): temporal maps + query locality.  They are
-// instantiated for the production head (D = 64, P = 4); the kernel itself checks
-// H == 1 on the device and falls back to the sparse body otherwise.
-inline bool band_applies(const Dims& d, int dtype, unsigned flags) {
-  if (flags & (MSDA_FLAG_NO_BAND | MSDA_FLAG_FORCE_GENERIC)) return false;
-  if (dtype != MSDA_F32 || d.D != 64 || d.P != 4 || d.L > kMaxLevelsFast) return false;
-  // experimental: correct (tests run it with MSDA_FLAG_FORCE_BAND) but not yet
-  // faster than the sparse kernels, so it is opt-in for now
-  return (flags & MSDA_FLAG_FORCE_BAND) != 0;
+// Row-window kernels (msda_win.cuh): temporal maps + query locality.  They are
+// instantiated for P = 4 points, L <= 4 levels and 8 lanes per head row
+// (f32: D = 64 or 32, bf16: D = 64); the kernels check H == 1 on the device and
+// decide per block of 4 queries between the window and the per-tap body.
+inline bool win_applies(const Dims& d, int dtype, unsigned flags) {
+  if (flags & (MSDA_FLAG_NO_WINDOW | MSDA_FLAG_FORCE_GENERIC)) return false;
+  if (d.P != kWinP || d.L > kWinMaxL) return false;
+  if (dtype == MSDA_F32) return d.D == 64 || d.D == 32;
+  if (dtype == MSDA_BF16) return d.D == 64;
+  return false;
 }
 
-template <typename T, int LG, int Q, int PP, int NU, int G>
-int launch_fwd_band(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
-                    const void* aw, void* out, const Dims& d, cudaStream_t st) {
-  constexpr int per_cta = (kFastThreads / LG) * Q;
+template <typename T, int NU, int G>
+int launch_fwd_win(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
+                   const void* aw, void* out, const Dims& d, cudaStream_t st) {
+  constexpr int per_cta = (kWinThreads / G) * kWinQ;
   const int nqc = (d.Lq + per_cta - 1) / per_cta;
   const int64_t ctas = (int64_t)d.N * d.M * nqc;
-  auto kern = msda_fwd_band_kernel<T, LG, Q, PP, NU, G>;
-  const size_t smem = band_smem_bytes<LG, Q>();
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e != cudaSuccess) return cuda_fail(e);
-  kern<<<(unsigned)ctas, kFastThreads, smem, st>>>((const T*)value, shapes, lsi, (const T*)loc,
-                                                   (const T*)aw, (T*)out, d, nqc);
-  e = cudaGetLastError();
+  msda_fwd_win_kernel<T, NU, G><<<(unsigned)ctas, kWinThreads, 0, st>>>(
+      (const T*)value, shapes, lsi, (const T*)loc, (const T*)aw, (T*)out, d, nqc);
+  const cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
+}
+
+template <typename T, int NU, int G>
+int launch_bwd_win(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
+                   const void* aw, const void* gout, float* gvalue, void* gloc, void* gaw,
+                   const Dims& d, cudaStream_t st) {
+  constexpr int per_cta = (kWinThreads / G) * kWinQ;
+  const int nqc = (d.Lq + per_cta - 1) / per_cta;
+  const int64_t ctas = (int64_t)d.N * d.M * nqc;
+  msda_bwd_win_kernel<T, NU, G><<<(unsigned)ctas, kWinThreads, 0, st>>>(
+      (const T*)value, shapes, lsi, (const T*)loc, (const T*)aw, (const T*)gout, gvalue, (T*)gloc,
+      (T*)gaw, d, nqc);
+  const cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
 }
 
@@ -225,9 +236,16 @@ int msda_forward(const void* value, const int64_t* spatial_shapes, const int64_t
   const bool fits32 = S * M * D < (int64_t(1) << 31);
   const bool fast = fits32 && fast_applies(D, L, dtype, flags) && aligned16(value) && aligned16(output) &&
                     aligned16(sampling_loc) && aligned16(attn_weight);
-  if (fast && band_applies(d, dtype, flags))
-    return launch_fwd_band<float, 16, 16, 4, 2, 8>(value, spatial_shapes, level_start_index,
-                                                   sampling_loc, attn_weight, output, d, st);
+  if (fast && win_applies(d, dtype, flags)) {
+    if (dtype == MSDA_BF16)
+      return launch_fwd_win<__nv_bfloat16, 1, 8>(value, spatial_shapes, level_start_index,
+                                                 sampling_loc, attn_weight, output, d, st);
+    if (D == 64)
+      return launch_fwd_win<float, 2, 8>(value, spatial_shapes, level_start_index, sampling_loc,
+                                         attn_weight, output, d, st);
+    return launch_fwd_win<float, 1, 8>(value, spatial_shapes, level_start_index, sampling_loc,
+                                       attn_weight, output, d, st);
+  }
   if (fast) {
     FastPlan plan;
     fast_plan(D, dtype, &plan);
@@ -288,7 +306,20 @@ int msda_backward(const void* value, const int64_t* spatial_shapes, const int64_
                     aligned16(grad_value) && aligned16(sampling_loc) && aligned16(attn_weight) &&
                     aligned16(grad_sampling_loc) && aligned16(grad_attn_weight);
   int r = MSDA_OK;
-  if (fast) {
+  if (fast && win_applies(d, dtype, flags)) {
+    if (dtype == MSDA_BF16)
+      r = launch_bwd_win<__nv_bfloat16, 1, 8>(value, spatial_shapes, level_start_index,
+                                              sampling_loc, attn_weight, grad_output, (float*)acc,
+                                              grad_sampling_loc, grad_attn_weight, d, st);
+    else if (D == 64)
+      r = launch_bwd_win<float, 2, 8>(value, spatial_shapes, level_start_index, sampling_loc,
+                                      attn_weight, grad_output, (float*)acc, grad_sampling_loc,
+                                      grad_attn_weight, d, st);
+    else
+      r = launch_bwd_win<float, 1, 8>(value, spatial_shapes, level_start_index, sampling_loc,
+                                      attn_weight, grad_output, (float*)acc, grad_sampling_loc,
+                                      grad_attn_weight, d, st);
+  } else if (fast) {
     r = [&]() -> int {
       FastPlan plan;
       fast_plan(D, dtype, &plan);

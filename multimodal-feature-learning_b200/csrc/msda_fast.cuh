@@ -200,20 +200,19 @@ __device__ __forceinline__ void owner_point(const T* __restrict__ loc_g, const T
 template <typename T, int NU, int G, int NT>
 __device__ __forceinline__ void fwd_body(const T* __restrict__ value, const T* __restrict__ loc,
                                          const T* __restrict__ aw, T* __restrict__ out,
-                                         const Dims& d, int b, int m, int q_begin, int q_end,
-                                         const int* s_lvl, TapMeta<NT>* s_meta_cta) {
+                                         const Dims& d, int b, int m, int q_first, int q_end,
+                                         int q_step, const int* s_lvl, TapMeta<NT>* s_meta) {
+  // the group handles queries q_first, q_first + q_step, ... < q_end of (b, m);
+  // s_meta = G entries private to the group
   constexpr int E = Unit<T>::E;
-  constexpr int NG = kFastThreads / G;
   const int lane = threadIdx.x & 31;
-  const int gi = threadIdx.x / G;
   const int j = threadIdx.x % G;
   const unsigned mask = group_mask<G>(lane);
-  TapMeta<NT>* s_meta = s_meta_cta + gi * G;
   const int LP = d.L * d.P;
   const int MD = d.M * d.D;
   const T* vb = value + ((size_t)b * d.S * d.M + m) * d.D + j * E;
 
-  for (int q = q_begin + gi; q < q_end; q += NG) {
+  for (int q = q_first; q < q_end; q += q_step) {
     const size_t grp = ((size_t)b * d.Lq + q) * d.M + m;
     const T* loc_g = loc + grp * LP * 2;
     const T* aw_g = aw + grp * LP;
@@ -276,11 +275,14 @@ msda_fwd_fast_kernel(const T* __restrict__ value, const int64_t* __restrict__ sh
   const int b = tile / (d.M * nqc);
   const int q_begin = qc * qtile;
   const int q_end = min(q_begin + qtile, d.Lq);
+  constexpr int NG = kFastThreads / G;
+  const int gi = threadIdx.x / G;
   if (s_one_d)
-    fwd_body<T, NU, G, 2>(value, loc, aw, out, d, b, m, q_begin, q_end, s_lvl,
-                          reinterpret_cast<TapMeta<2>*>(s_meta));
+    fwd_body<T, NU, G, 2>(value, loc, aw, out, d, b, m, q_begin + gi, q_end, NG, s_lvl,
+                          reinterpret_cast<TapMeta<2>*>(s_meta) + gi * G);
   else
-    fwd_body<T, NU, G, 4>(value, loc, aw, out, d, b, m, q_begin, q_end, s_lvl, s_meta);
+    fwd_body<T, NU, G, 4>(value, loc, aw, out, d, b, m, q_begin + gi, q_end, NG, s_lvl,
+                          s_meta + gi * G);
 }
 
 // ------------------------------- backward -----------------------------------
@@ -296,22 +298,19 @@ __device__ __forceinline__ void bwd_body(const T* __restrict__ value, const T* _
                                          const T* __restrict__ aw, const T* __restrict__ gout,
                                          float* __restrict__ gvalue, T* __restrict__ gloc,
                                          T* __restrict__ gaw, const Dims& d, int b, int m,
-                                         int q_begin, int q_end, const int* s_lvl,
-                                         TapMeta<NT>* s_meta_cta) {
+                                         int q_first, int q_end, int q_step, const int* s_lvl,
+                                         TapMeta<NT>* s_meta) {
   constexpr int E = Unit<T>::E;
-  constexpr int NG = kFastThreads / G;
   const int lane = threadIdx.x & 31;
-  const int gi = threadIdx.x / G;
   const int j = threadIdx.x % G;
   const unsigned mask = group_mask<G>(lane);
-  TapMeta<NT>* s_meta = s_meta_cta + gi * G;
   const int LP = d.L * d.P;
   const int MD = d.M * d.D;
   const size_t voff = ((size_t)b * d.S * d.M + m) * d.D + j * E;
   const T* vb = value + voff;
   float* gvb = gvalue + voff;
 
-  for (int q = q_begin + gi; q < q_end; q += NG) {
+  for (int q = q_first; q < q_end; q += q_step) {
     const size_t grp = ((size_t)b * d.Lq + q) * d.M + m;
     const T* loc_g = loc + grp * LP * 2;
     const T* aw_g = aw + grp * LP;
@@ -383,12 +382,14 @@ msda_bwd_fast_kernel(const T* __restrict__ value, const int64_t* __restrict__ sh
   const int b = tile / (d.M * nqc);
   const int q_begin = qc * qtile;
   const int q_end = min(q_begin + qtile, d.Lq);
+  constexpr int NG = kFastThreads / G;
+  const int gi = threadIdx.x / G;
   if (s_one_d)
-    bwd_body<T, NU, G, 2>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q_begin, q_end, s_lvl,
-                          reinterpret_cast<TapMeta<2>*>(s_meta));
+    bwd_body<T, NU, G, 2>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q_begin + gi, q_end, NG,
+                          s_lvl, reinterpret_cast<TapMeta<2>*>(s_meta) + gi * G);
   else
-    bwd_body<T, NU, G, 4>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q_begin, q_end, s_lvl,
-                          s_meta);
+    bwd_body<T, NU, G, 4>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q_begin + gi, q_end, NG,
+                          s_lvl, s_meta + gi * G);
 }
 
 // fp32 accumulation image -> bf16 grad_value
