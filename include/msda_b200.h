@@ -78,6 +78,9 @@ typedef enum {
                                       for f32/f64, the workspace for bf16) */
 #define MSDA_FLAG_NO_WINDOW 4u      /* never use the row-window kernels
                                       (msda_win.cuh); per-tap kernels only */
+#define MSDA_FLAG_FORCE_WINDOW 8u   /* use them whenever they are instantiated for
+                                      the shape, also for short query lists
+                                      (default: Lq >= 256) */
 /* bits 8..19: queries-per-tile multiplier override for the vectorised kernels
  * (0 = heuristic); a tuning knob, results do not depend on it. */
 #define MSDA_FLAG_QTILE(k) (((unsigned)(k) & 0xfffu) << 8)

@@ -18,6 +18,7 @@ MSDA_PAD_ZEROS, MSDA_PAD_BORDER = 0, 1
 MSDA_FLAG_FORCE_GENERIC = 1
 MSDA_FLAG_SKIP_ZERO_FILL = 2
 MSDA_FLAG_NO_WINDOW = 4
+MSDA_FLAG_FORCE_WINDOW = 8
 
 
 def flag_qtile(k):

@@ -64,6 +64,7 @@ inline Dims make_dims(int64_t N, int64_t S, int64_t M, int64_t D, int64_t L, int
   Dims d;
   d.N = (int)N; d.S = (int)S; d.M = (int)M; d.D = (int)D; d.L = (int)L; d.Lq = (int)Lq; d.P = (int)P;
   d.border = padding == MSDA_PAD_BORDER;
+  d.dbg = 0;
   return d;
 }
 
@@ -111,20 +112,52 @@ int launch_bwd_fast(const void* value, const int64_t* shapes, const int64_t* lsi
 // decide per block of 4 queries between the window and the per-tap body.
 inline bool win_applies(const Dims& d, int dtype, unsigned flags) {
   if (flags & (MSDA_FLAG_NO_WINDOW | MSDA_FLAG_FORCE_GENERIC)) return false;
-  if (d.P != kWinP || d.L > kWinMaxL) return false;
+  // Query lists shorter than this are decoder-style (a few learned queries per
+  // item, unrelated reference points): their 4-query blocks have no common window.
+  if (d.Lq < kWinMinQueries && !(flags & MSDA_FLAG_FORCE_WINDOW)) return false;
+  if (d.P != kWinP || d.L > kWinMaxL || d.S <= 0) return false;
+  // the points of a query are staged with 16-byte cp.async pieces
+  if ((d.L * d.P * (dtype == MSDA_BF16 ? 2 : 4)) % 16 != 0) return false;
+  if ((int64_t)d.N * d.M * ((d.Lq + 15) / 16) >= (int64_t(1) << 31)) return false;
+  // 32-bit BYTE offsets inside one batch item's slab (fp32 accumulation image included)
+  if ((int64_t)d.S * d.M * d.D * 4 >= (int64_t(1) << 32)) return false;
   if (dtype == MSDA_F32) return d.D == 64 || d.D == 32;
   if (dtype == MSDA_BF16) return d.D == 64;
   return false;
 }
 
+// Persistent launch: as many CTAs as fit on the device at once (the kernels
+// distribute 16-query units themselves).
+template <typename K>
+int win_grid(K kern, size_t smem, long long units, int* grid) {
+  int dev = 0, sms = 0, per_sm = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e == cudaSuccess)
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kWinThreads, smem);
+  if (e != cudaSuccess) return cuda_fail(e);
+  if (per_sm < 1) per_sm = 1;
+  const long long warps = kWinThreads / 32;
+  long long g = (long long)sms * per_sm;
+  if (g > (units + warps - 1) / warps) g = (units + warps - 1) / warps;
+  *grid = (int)(g < 1 ? 1 : g);
+  return MSDA_OK;
+}
+
 template <typename T, int NU, int G>
 int launch_fwd_win(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
                    const void* aw, void* out, const Dims& d, cudaStream_t st) {
-  constexpr int per_cta = (kWinThreads / G) * kWinQ;
-  const int nqc = (d.Lq + per_cta - 1) / per_cta;
-  const int64_t ctas = (int64_t)d.N * d.M * nqc;
-  msda_fwd_win_kernel<T, NU, G><<<(unsigned)ctas, kWinThreads, 0, st>>>(
-      (const T*)value, shapes, lsi, (const T*)loc, (const T*)aw, (T*)out, d, nqc);
+  const int nqc = (d.Lq + 4 * kWinQ - 1) / (4 * kWinQ);
+  const long long units = (long long)d.N * d.M * nqc;
+  constexpr size_t smem = (size_t)(kWinThreads / G) * WinSmem<T, 1, false, 0>::kGroupBytes;
+  auto kern = msda_fwd_win_kernel<T, NU, G>;
+  int grid = 1;
+  const int rc = win_grid(kern, smem, units, &grid);
+  if (rc != MSDA_OK) return rc;
+  kern<<<grid, kWinThreads, smem, st>>>((const T*)value, shapes, lsi, (const T*)loc, (const T*)aw,
+                                        (T*)out, d, nqc, (int)units);
   const cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
 }
@@ -133,12 +166,16 @@ template <typename T, int NU, int G>
 int launch_bwd_win(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
                    const void* aw, const void* gout, float* gvalue, void* gloc, void* gaw,
                    const Dims& d, cudaStream_t st) {
-  constexpr int per_cta = (kWinThreads / G) * kWinQ;
-  const int nqc = (d.Lq + per_cta - 1) / per_cta;
-  const int64_t ctas = (int64_t)d.N * d.M * nqc;
-  msda_bwd_win_kernel<T, NU, G><<<(unsigned)ctas, kWinThreads, 0, st>>>(
-      (const T*)value, shapes, lsi, (const T*)loc, (const T*)aw, (const T*)gout, gvalue, (T*)gloc,
-      (T*)gaw, d, nqc);
+  const int nqc = (d.Lq + 4 * kWinQ - 1) / (4 * kWinQ);
+  const long long units = (long long)d.N * d.M * nqc;
+  constexpr int DD = NU * G * (16 / (int)sizeof(T));
+  constexpr size_t smem = (size_t)(kWinThreads / G) * WinSmem<T, 2, true, DD>::kGroupBytes;
+  auto kern = msda_bwd_win_kernel<T, NU, G>;
+  int grid = 1;
+  const int rc = win_grid(kern, smem, units, &grid);
+  if (rc != MSDA_OK) return rc;
+  kern<<<grid, kWinThreads, smem, st>>>((const T*)value, shapes, lsi, (const T*)loc, (const T*)aw,
+                                        (const T*)gout, gvalue, (T*)gloc, (T*)gaw, d, nqc, (int)units);
   const cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
 }
@@ -231,7 +268,8 @@ int msda_forward(const void* value, const int64_t* spatial_shapes, const int64_t
   if (!spatial_shapes || !level_start_index || !sampling_loc || !attn_weight || !output)
     return MSDA_ERR_NULL_POINTER;
   if (S > 0 && !value) return MSDA_ERR_NULL_POINTER;
-  const Dims d = make_dims(N, S, M, D, L, Lq, P, padding);
+  Dims d = make_dims(N, S, M, D, L, Lq, P, padding);
+  d.dbg = (int)((flags >> 20) & 0xffu);
   cudaStream_t st = (cudaStream_t)stream;
   const bool fits32 = S * M * D < (int64_t(1) << 31);
   const bool fast = fits32 && fast_applies(D, L, dtype, flags) && aligned16(value) && aligned16(output) &&
@@ -280,7 +318,8 @@ int msda_backward(const void* value, const int64_t* spatial_shapes, const int64_
                   void* stream) {
   const int rc = check_common(N, S, M, D, L, Lq, P, dtype, padding);
   if (rc != MSDA_OK) return rc;
-  const Dims d = make_dims(N, S, M, D, L, Lq, P, padding);
+  Dims d = make_dims(N, S, M, D, L, Lq, P, padding);
+  d.dbg = (int)((flags >> 20) & 0xffu);
   cudaStream_t st = (cudaStream_t)stream;
   const size_t esz = dtype == MSDA_F64 ? 8 : dtype == MSDA_F32 ? 4 : 2;
   const size_t nvalue = (size_t)N * S * M * D;

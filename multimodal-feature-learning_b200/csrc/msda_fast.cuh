@@ -108,6 +108,22 @@ template <> struct Unit<float> {
         : "=&f"(v[0]), "=&f"(v[1]), "=&f"(v[2]), "=&f"(v[3])
         : "l"(p), "r"((int)pred));
   }
+  using Raw = float;
+  // predicated 128-bit load that KEEPS the old register contents when !pred
+  static __device__ __forceinline__ void ldg_keep(const char* p, bool pred, float (&v)[4]) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+                 "@p ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%4];\n\t}"
+                 : "+f"(v[0]), "+f"(v[1]), "+f"(v[2]), "+f"(v[3])
+                 : "l"(p), "r"((int)pred));
+  }
+  static __device__ __forceinline__ void unpack_raw(const float (&r)[4], float (&v)[4]) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = r[i];
+  }
+  static __device__ __forceinline__ void ldg_all(const float* p, float (&v)[4]) {
+    const float4 t = __ldg(reinterpret_cast<const float4*>(p));
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  }
   static __device__ __forceinline__ void ld_stream(const float* p, float (&v)[4]) {
     const float4 t = __ldcs(reinterpret_cast<const float4*>(p));
     v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
@@ -132,6 +148,21 @@ template <> struct Unit<__nv_bfloat16> {
         "@p ld.global.nc.v4.b32 {%0, %1, %2, %3}, [%4];\n\t}"
         : "=&r"(w[0]), "=&r"(w[1]), "=&r"(w[2]), "=&r"(w[3])
         : "l"(p), "r"((int)pred));
+    unpack(w, v);
+  }
+  using Raw = uint32_t;
+  static __device__ __forceinline__ void ldg_keep(const char* p, bool pred, uint32_t (&w)[4]) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+                 "@p ld.global.nc.v4.b32 {%0, %1, %2, %3}, [%4];\n\t}"
+                 : "+r"(w[0]), "+r"(w[1]), "+r"(w[2]), "+r"(w[3])
+                 : "l"(p), "r"((int)pred));
+  }
+  static __device__ __forceinline__ void unpack_raw(const uint32_t (&w)[4], float (&v)[8]) {
+    unpack(w, v);
+  }
+  static __device__ __forceinline__ void ldg_all(const __nv_bfloat16* p, float (&v)[8]) {
+    const uint4 t = __ldg(reinterpret_cast<const uint4*>(p));
+    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
     unpack(w, v);
   }
   static __device__ __forceinline__ void ld_stream(const __nv_bfloat16* p, float (&v)[8]) {

@@ -41,42 +41,41 @@ namespace msda {
 constexpr int kWinQ = 4;         // queries per block
 constexpr int kWinP = 4;         // points per level (template-free fast case)
 constexpr int kWinMaxL = 4;      // levels
-constexpr int kWinCap = 96;      // packed rows per block, multiple of 4
+constexpr int kWinCap = 88;      // packed rows per block, multiple of 4
+constexpr int kWinRows = kWinCap + 8;  // + padding rows read by the software pipeline
 constexpr int kWinThreads = 128;
-// per group: float4 Wt[kWinCap], int rowoff[kWinCap], + 4 floats so that the
-// groups of a warp start 4 banks apart
-constexpr int kWinGroupFloats = 5 * kWinCap + 4;
+constexpr int kWinMinQueries = 256;  // host heuristic: shorter query lists use the per-tap kernels
 
 struct WinCoef { float k0, k1, fx, cy0, cy1; };
 
-// One sampling point on a (1, W) map: slab row of the low tap, weights (already
-// times the attention weight and the vertical factor), which taps are read.
-// Same arithmetic as point_geom() with H == 1 (msda_common.cuh).
+// One sampling point on a (1, W) map: slab row of the low tap and the tap
+// weights (already times the attention weight and the vertical factor; 0 for a
+// tap that is not read).  Same arithmetic as point_geom() with H == 1
+// (msda_common.cuh): h_im = y - 0.5 in (-1, 1) -> the single row is the low
+// (weight 1 - h_im) or the high (weight h_im + 1) row of the vertical pair,
+// i.e. 1 - |h_im| either way.
 template <bool BWD>
 __device__ __forceinline__ void win_point(float x, float y, float a, int W, int start, bool border,
-                                          bool active, int& r0, float& w0, float& w1, bool& v0,
-                                          bool& v1, WinCoef& c) {
+                                          bool active, int& r0, float& w0, float& w1, bool& live,
+                                          bool& v0, bool& v1, WinCoef& c) {
   float h_im = y - 0.5f;
   float w_im = x * (float)W - 0.5f;
+  const float wlast = (float)(W - 1);
   float sx = (float)W, sy = 1.f;
-  bool live;
   if (border) {
-    const float wmax = (float)(W - 1);
     if (!(w_im > 0.f)) { w_im = 0.f; sx = 0.f; }
-    else if (w_im >= wmax) { w_im = wmax; sx = 0.f; }
+    else if (w_im >= wlast) { w_im = wlast; sx = 0.f; }
     h_im = 0.f; sy = 0.f;
     live = active;
   } else {
-    live = active && (h_im > -1.f) && (w_im > -1.f) && (h_im < 1.f) && (w_im < (float)W);
+    live = active && (fabsf(h_im) < 1.f) && (w_im > -1.f) && (w_im < (float)W);
   }
   const float wf = floorf(w_im);
-  const int w_low = (int)wf;
   const float lw = w_im - wf, hw = 1.f - lw;
-  const bool hl = h_im >= 0.f;                       // row 0 is the LOW row of the vertical pair
-  const float fy = hl ? 1.f - h_im : h_im + 1.f;     // hh or lh
-  v0 = live && w_low >= 0;
-  v1 = live && w_low + 1 <= W - 1;
-  r0 = start + w_low;
+  const float fy = 1.f - fabsf(h_im);
+  v0 = live && w_im >= 0.f;      // w_low >= 0
+  v1 = live && w_im < wlast;     // w_low + 1 <= W - 1
+  r0 = start + (int)wf;
   const float k0 = fy * hw, k1 = fy * lw;
   w0 = v0 ? k0 * a : 0.f;
   w1 = v1 ? k1 * a : 0.f;
@@ -84,9 +83,9 @@ __device__ __forceinline__ void win_point(float x, float y, float a, int W, int 
     c.k0 = v0 ? k0 : 0.f;
     c.k1 = v1 ? k1 : 0.f;
     c.fx = live ? sx * a * fy : 0.f;
-    const float sg = hl ? -sy : sy;
-    c.cy0 = live ? sg * a * hw : 0.f;
-    c.cy1 = live ? sg * a * lw : 0.f;
+    const float sg = live ? copysignf(sy, -h_im) * a : 0.f;   // h_im >= 0: -sy, else +sy
+    c.cy0 = sg * hw;
+    c.cy1 = sg * lw;
   }
 }
 
@@ -98,6 +97,15 @@ template <> struct WinPts<float> {
     const float4 l0 = __ldg(reinterpret_cast<const float4*>(loc2));
     const float4 l1 = __ldg(reinterpret_cast<const float4*>(loc2) + 1);
     const float4 w = __ldg(reinterpret_cast<const float4*>(awp));
+    x[0] = l0.x; y[0] = l0.y; x[1] = l0.z; y[1] = l0.w;
+    x[2] = l1.x; y[2] = l1.y; x[3] = l1.z; y[3] = l1.w;
+    a[0] = w.x; a[1] = w.y; a[2] = w.z; a[3] = w.w;
+  }
+  static __device__ __forceinline__ void ld_smem(const float* loc2, const float* awp, float (&x)[4],
+                                                 float (&y)[4], float (&a)[4]) {
+    const float4 l0 = *reinterpret_cast<const float4*>(loc2);
+    const float4 l1 = *(reinterpret_cast<const float4*>(loc2) + 1);
+    const float4 w = *reinterpret_cast<const float4*>(awp);
     x[0] = l0.x; y[0] = l0.y; x[1] = l0.z; y[1] = l0.w;
     x[2] = l1.x; y[2] = l1.y; x[3] = l1.z; y[3] = l1.w;
     a[0] = w.x; a[1] = w.y; a[2] = w.z; a[3] = w.w;
@@ -123,6 +131,19 @@ template <> struct WinPts<__nv_bfloat16> {
     a[0] = __uint_as_float(w.x << 16); a[1] = __uint_as_float(w.x & 0xffff0000u);
     a[2] = __uint_as_float(w.y << 16); a[3] = __uint_as_float(w.y & 0xffff0000u);
   }
+  static __device__ __forceinline__ void ld_smem(const __nv_bfloat16* loc2, const __nv_bfloat16* awp,
+                                                 float (&x)[4], float (&y)[4], float (&a)[4]) {
+    const uint4 l = *reinterpret_cast<const uint4*>(loc2);
+    const uint2 w = *reinterpret_cast<const uint2*>(awp);
+    const uint32_t lw[4] = {l.x, l.y, l.z, l.w};
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      x[p] = __uint_as_float(lw[p] << 16);
+      y[p] = __uint_as_float(lw[p] & 0xffff0000u);
+    }
+    a[0] = __uint_as_float(w.x << 16); a[1] = __uint_as_float(w.x & 0xffff0000u);
+    a[2] = __uint_as_float(w.y << 16); a[3] = __uint_as_float(w.y & 0xffff0000u);
+  }
   static __device__ __forceinline__ uint32_t pack(float lo, float hi) {
     const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<const uint32_t*>(&h);
@@ -136,379 +157,626 @@ template <> struct WinPts<__nv_bfloat16> {
   }
 };
 
-// What every lane of a block knows after the window agreement.
-struct WinPlan {
-  int lo[kWinMaxL];     // first slab row of level l's window
-  int off[kWinMaxL];    // packed position of that row
-  int rtot;             // packed rows over all levels
+// base + 32-bit byte offset in one IMAD.WIDE
+__device__ __forceinline__ const char* win_addr(const char* base, unsigned off) {
+  unsigned long long r;
+  asm("mad.wide.u32 %0, %1, 1, %2;" : "=l"(r) : "r"(off), "l"(base));
+  return reinterpret_cast<const char*>(r);
+}
+
+// 16-byte asynchronous global -> shared copy (LDGSTS), L2-only caching
+__device__ __forceinline__ void win_cp16(void* smem_dst, const void* gsrc) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void win_cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void win_cp_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// Stage (H, W, start) per level; returns (to every thread) whether all levels
+// have H == 1.  One barrier.
+__device__ __forceinline__ bool win_stage_levels(const int64_t* __restrict__ shapes,
+                                                 const int64_t* __restrict__ lsi, int L,
+                                                 int* s_lvl) {
+  bool one = true;
+  if ((int)threadIdx.x < L) {
+    const int l = threadIdx.x;
+    const int H = (int)shapes[2 * l];
+    one = H == 1;
+    s_lvl[3 * l] = H;
+    s_lvl[3 * l + 1] = (int)shapes[2 * l + 1];
+    s_lvl[3 * l + 2] = (int)lsi[l];
+  }
+  return __syncthreads_and(one) != 0;
+}
+
+// ---- work distribution ------------------------------------------------------
+// A UNIT = 16 consecutive queries (4 blocks, one per 8-lane group of a warp) of
+// one (batch, head).  Warp w of the (persistent) grid takes units w, w + W,
+// w + 2W, ... (W = warps in the grid), so at any moment the resident warps work
+// on neighbouring units -- the same few (b, m) slabs, which then stay in L2 --
+// exactly as a non-persistent launch would sweep them.
+struct WinUnit { int b, m, q0; };
+
+__device__ __forceinline__ WinUnit win_decode(int u, int nqc, int M) {
+  WinUnit w;
+  const int bm = u / nqc;
+  w.q0 = (u - bm * nqc) * (4 * kWinQ);
+  w.b = bm / M;
+  w.m = bm - w.b * M;
+  return w;
+}
+
+// Shared memory of one group (block of 4 queries):
+//   float4   Wt[kWinRows]            weights, later (backward) the dots G
+//   unsigned rowoff[kWinRows]        byte offset of the slab row behind packed row t
+//   T        pts[NPB][4][LP*3]       staged sampling points of the block (loc then aw per query)
+//   T        gout[4][D]              (backward) staged grad_out rows
+template <typename T, int NPB, bool BWD, int D>
+struct WinSmem {
+  static constexpr int kPtsBytes = 4 * (kWinMaxL * kWinP * 3) * (int)sizeof(T);   // per buffer
+  static constexpr int kGoutBytes = BWD ? 4 * D * (int)sizeof(T) : 0;
+  static constexpr int kPlanBytes = kWinRows * 20;
+  static constexpr int kGroupBytes = kPlanBytes + NPB * kPtsBytes + kGoutBytes + 16;  // +16: bank skew
 };
 
-// Steps 1 + 2 of the header comment.  Returns false when the block must use the
-// per-tap path (packed windows exceed kWinCap).  On success Wt / rowoff are
-// built and visible to the whole group.
+// cp.async the sampling points of block (b, q0.., m) into `dst` (loc of the 4
+// queries, then their attention weights); queries >= Lq are skipped.  The piece
+// a lane copies is the same for every block: (query, loc|aw, 16-byte index).
+template <typename T>
+struct WinFetch {
+  static constexpr int kMaxPieces = (4 * kWinMaxL * kWinP * 3 * (int)sizeof(T) / 16 + 7) / 8;
+  int n;                       // pieces of this lane
+  int qi[kMaxPieces];
+  unsigned src[kMaxPieces];    // byte offset from the block's loc (or aw) base
+  unsigned dst[kMaxPieces];    // byte offset in the staging buffer; bit 31: aw
+  __device__ __forceinline__ void init(const Dims& d, int j) {
+    const int LP = d.L * kWinP;
+    const int loc_chunks = LP * 2 * (int)sizeof(T) / 16;
+    const int aw_chunks = LP * (int)sizeof(T) / 16;
+    const int per_q = loc_chunks + aw_chunks;
+    n = 0;
+#pragma unroll
+    for (int i = 0; i < kMaxPieces; ++i) {
+      const int c = j + 8 * i;
+      qi[i] = 0; src[i] = 0; dst[i] = 0;
+      if (c < 4 * per_q) {
+        n = i + 1;
+        const int q = c / per_q, k = c - q * per_q;
+        qi[i] = q;
+        if (k < loc_chunks) {
+          src[i] = (unsigned)(q * d.M * LP * 2 * (int)sizeof(T) + k * 16);
+          dst[i] = (unsigned)((q * loc_chunks + k) * 16);
+        } else {
+          src[i] = (unsigned)(q * d.M * LP * (int)sizeof(T) + (k - loc_chunks) * 16);
+          dst[i] = (unsigned)((4 * loc_chunks + q * aw_chunks + (k - loc_chunks)) * 16) | 0x80000000u;
+        }
+      }
+    }
+  }
+  __device__ __forceinline__ void issue(const T* __restrict__ loc, const T* __restrict__ aw,
+                                        const Dims& d, int b, int m, int q0, char* buf) const {
+    const int LP = d.L * kWinP;
+    const size_t grp = ((size_t)b * d.Lq + q0) * d.M + m;
+    const char* lb = reinterpret_cast<const char*>(loc + grp * LP * 2);
+    const char* ab = reinterpret_cast<const char*>(aw + grp * LP);
+#pragma unroll
+    for (int i = 0; i < kMaxPieces; ++i) {
+      if (i < n && q0 + qi[i] < d.Lq) {
+        const bool is_aw = (dst[i] >> 31) != 0;
+        win_cp16(buf + (dst[i] & 0x7fffffffu), win_addr(is_aw ? ab : lb, src[i]));
+      }
+    }
+  }
+};
+template <typename T>
+__device__ __forceinline__ const T* win_pts_loc(const char* pts, int L, int qi, int l) {
+  return reinterpret_cast<const T*>(pts) + (qi * L * kWinP + l * kWinP) * 2;
+}
+template <typename T>
+__device__ __forceinline__ const T* win_pts_aw(const char* pts, int L, int qi, int l) {
+  return reinterpret_cast<const T*>(pts) + 4 * L * kWinP * 2 + qi * L * kWinP + l * kWinP;
+}
+
+// Steps 1 + 2 of the header comment, executed by all 32 lanes of the warp, with
+// the block's points already staged in shared memory (`pts`).
+// Returns ok = false when the block must use the per-tap path (its packed
+// windows exceed kWinCap); such a block, and one without queries, takes part
+// in the row loop with zero rows.  Outputs: tb[i] = packed position minus slab
+// row for the lane's i-th level, rt = this block's packed rows, wmax = the
+// largest rt of the warp's blocks (the warp-uniform trip count).  Wt is zero
+// and rowoff (BYTE offsets of the slab rows) repeats the last row up to
+// round4(wmax) + 4, so the row loops can run past rt.
 template <typename T, int G>
-__device__ __forceinline__ bool win_build(const T* __restrict__ loc, const T* __restrict__ aw,
-                                          const Dims& d, size_t grp_me, bool have_q,
-                                          const int* s_lvl, float* s_grp, int j, int gbase,
-                                          unsigned mask, WinPlan& pl) {
+__device__ __forceinline__ bool win_build(const char* pts, const Dims& d, bool have_q,
+                                          const int* s_lvl, char* s_grp, int j, int gbase,
+                                          int (&tb)[(kWinMaxL * 4 + G - 1) / G], int& rt,
+                                          int& wmax) {
+  constexpr unsigned FULL = 0xffffffffu;
   constexpr int NH = G / 4;                        // level classes
   constexpr int LPL = (kWinMaxL + NH - 1) / NH;    // levels owned per lane
   constexpr int BIG = 0x3fffffff;
   const int qi = j & 3, h = j >> 2;
-  const int MD = d.M * d.D;
-  const int LP = d.L * kWinP;
   float4* Wt = reinterpret_cast<float4*>(s_grp);
-  float* Wf = s_grp;
-  int* rowoff = reinterpret_cast<int*>(s_grp + 4 * kWinCap);
+  float* Wf = reinterpret_cast<float*>(s_grp);
+  unsigned* rowoff = reinterpret_cast<unsigned*>(s_grp + 16 * kWinRows);
 
   int r0[LPL][4];
   float w0[LPL][4], w1[LPL][4];
-  bool v0[LPL][4], v1[LPL][4];
   int lo[LPL], hi[LPL];
 #pragma unroll
   for (int i = 0; i < LPL; ++i) {
     const int l = h + i * NH;
     const bool active = have_q && l < d.L;
-    const int ls = active ? l : 0;
+    const int ls = l < d.L ? l : 0;
     float x[4], y[4], a[4];
-    WinPts<T>::ld(loc + (grp_me * LP + ls * kWinP) * 2, aw + grp_me * LP + ls * kWinP, x, y, a);
+    WinPts<T>::ld_smem(win_pts_loc<T>(pts, d.L, qi, ls), win_pts_aw<T>(pts, d.L, qi, ls), x, y, a);
     const int W = s_lvl[3 * ls + 1], start = s_lvl[3 * ls + 2];
     lo[i] = BIG; hi[i] = -BIG;
 #pragma unroll
     for (int p = 0; p < 4; ++p) {
       WinCoef c;
+      bool live, v0, v1;
       win_point<false>(x[p], y[p], a[p], W, start, d.border != 0, active, r0[i][p], w0[i][p],
-                       w1[i][p], v0[i][p], v1[i][p], c);
-      if (v0[i][p]) { lo[i] = min(lo[i], r0[i][p]); hi[i] = max(hi[i], r0[i][p]); }
-      if (v1[i][p]) { lo[i] = min(lo[i], r0[i][p] + 1); hi[i] = max(hi[i], r0[i][p] + 1); }
+                       w1[i][p], live, v0, v1, c);
+      lo[i] = min(lo[i], live ? r0[i][p] : BIG);
+      hi[i] = max(hi[i], live ? r0[i][p] + 1 : -BIG);
     }
+    // a live point has -1 <= w_low <= W - 1: clip the pair to the map
+    lo[i] = max(lo[i], start);
+    hi[i] = min(hi[i], start + W - 1);
   }
   // agree per level over the 4 lanes (qi = 0..3) of the class
 #pragma unroll
   for (int s = 1; s <= 2; s <<= 1)
 #pragma unroll
     for (int i = 0; i < LPL; ++i) {
-      lo[i] = min(lo[i], __shfl_xor_sync(mask, lo[i], s));
-      hi[i] = max(hi[i], __shfl_xor_sync(mask, hi[i], s));
+      lo[i] = min(lo[i], __shfl_xor_sync(FULL, lo[i], s));
+      hi[i] = max(hi[i], __shfl_xor_sync(FULL, hi[i], s));
     }
   // every lane learns all levels; pack them back to back
-  int rtot = 0;
+  int plo[kWinMaxL], poff[kWinMaxL];
+  int rtot = 0, last_row = 0;
 #pragma unroll
   for (int l = 0; l < kWinMaxL; ++l) {
     const int src = gbase + (l % NH) * 4;
-    const int llo = __shfl_sync(mask, lo[l / NH], src);
-    const int lhi = __shfl_sync(mask, hi[l / NH], src);
+    const int llo = __shfl_sync(FULL, lo[l / NH], src);
+    const int lhi = __shfl_sync(FULL, hi[l / NH], src);
     const int rows = max(lhi - llo + 1, 0);
-    pl.lo[l] = llo;
-    pl.off[l] = rtot;
+    plo[l] = llo;
+    poff[l] = rtot;
     rtot += rows;
+    if (rows > 0) last_row = lhi;
   }
-  pl.rtot = rtot;
-  if (rtot > kWinCap) return false;
+  const bool ok = rtot <= kWinCap;
+  rt = ok ? rtot : 0;
+  if (!ok) last_row = 0;
+  wmax = __reduce_max_sync(FULL, rt);
+  if (d.dbg & 1) wmax = 0;
 
-  // zero Wt, fill rowoff (padding rows up to a multiple of 4: weight 0, offset -1)
-  const int rpad = (rtot + 3) & ~3;
-  for (int t = j; t < rpad; t += G) {
+  const unsigned row_bytes = (unsigned)(d.M * d.D) * (unsigned)sizeof(T);
+  const int nfill = ((wmax + 3) & ~3) + 4;
+  for (int t = j; t < nfill; t += G) {
     Wt[t] = make_float4(0.f, 0.f, 0.f, 0.f);
-    int base = pl.lo[0] - pl.off[0];
+    int base = plo[0] - poff[0];
 #pragma unroll
     for (int l = 1; l < kWinMaxL; ++l)
-      if (t >= pl.off[l]) base = pl.lo[l] - pl.off[l];
-    rowoff[t] = t < rtot ? (base + t) * MD : -1;
+      if (t >= poff[l]) base = plo[l] - poff[l];
+    rowoff[t] = (unsigned)(t < rt ? base + t : last_row) * row_bytes;
   }
-  __syncwarp(mask);
-  // scatter: column (level, qi) belongs to this lane alone
-  int tb[LPL];
 #pragma unroll
   for (int i = 0; i < LPL; ++i) {
     const int l = h + i * NH;
-    int o = pl.off[0] - pl.lo[0];
+    int o = poff[0] - plo[0];
 #pragma unroll
     for (int ll = 1; ll < kWinMaxL; ++ll)
-      if (l == ll) o = pl.off[ll] - pl.lo[ll];
+      if (l == ll) o = poff[ll] - plo[ll];
     tb[i] = o;
   }
+  __syncwarp();
+  // scatter: column (level, qi) belongs to this lane alone.  A zero weight needs
+  // no store (and a tap outside the map has weight 0), so no validity flags.
+  if (ok) {
 #pragma unroll
-  for (int p = 0; p < 4; ++p) {
-    float c0[LPL], c1[LPL];
-    int t0[LPL];
+    for (int p = 0; p < 4; ++p) {
+      float c0[LPL], c1[LPL];
+      int t0[LPL];
 #pragma unroll
-    for (int i = 0; i < LPL; ++i) {
-      t0[i] = (v0[i][p] || v1[i][p]) ? (r0[i][p] + tb[i]) * 4 + qi : qi;
-      c0[i] = v0[i][p] ? Wf[t0[i]] : 0.f;
-      c1[i] = v1[i][p] ? Wf[t0[i] + 4] : 0.f;
-    }
+      for (int i = 0; i < LPL; ++i) {
+        t0[i] = (r0[i][p] + tb[i]) * 4 + qi;
+        c0[i] = w0[i][p] != 0.f ? Wf[t0[i]] : 0.f;
+        c1[i] = w1[i][p] != 0.f ? Wf[t0[i] + 4] : 0.f;
+      }
 #pragma unroll
-    for (int i = 0; i < LPL; ++i) {
-      if (v0[i][p]) Wf[t0[i]] = c0[i] + w0[i][p];
-      if (v1[i][p]) Wf[t0[i] + 4] = c1[i] + w1[i][p];
+      for (int i = 0; i < LPL; ++i) {
+        if (w0[i][p] != 0.f) Wf[t0[i]] = c0[i] + w0[i][p];
+        if (w1[i][p] != 0.f) Wf[t0[i] + 4] = c1[i] + w1[i][p];
+      }
     }
   }
-  __syncwarp(mask);
-  return true;
+  __syncwarp();
+  return ok;
 }
+
+// One value row (this lane's NU 16-byte units) as loaded: kept raw until used.
+// The load is predicated WITHOUT zero-fill: a skipped load leaves the previous
+// (finite) contents, which only ever meet zero weights.
+template <typename T, int NU, int G>
+__device__ __forceinline__ void win_load_row(const char* vbb, unsigned off, bool pred,
+                                             typename Unit<T>::Raw (&buf)[NU][4]) {
+  const char* p = win_addr(vbb, off);
+#pragma unroll
+  for (int u = 0; u < NU; ++u) Unit<T>::ldg_keep(p + u * (G * 16), pred, buf[u]);
+}
+
+constexpr int kWinStages = 4;   // value rows in flight per lane
 
 // ------------------------------- forward ------------------------------------
-template <typename T, int NU, int G>
-__device__ __forceinline__ void fwd_win_rows(const T* __restrict__ vb, T* __restrict__ out,
-                                             const Dims& d, int b, int m, int q0, int nq,
-                                             const float* s_grp, int j, int rtot) {
-  constexpr int E = Unit<T>::E;
-  constexpr int RB = 4;  // rows per step
-  const float4* Wt = reinterpret_cast<const float4*>(s_grp);
-  const int* rowoff = reinterpret_cast<const int*>(s_grp + 4 * kWinCap);
-  float2 acc[kWinQ][NU][E / 2];
-#pragma unroll
-  for (int q = 0; q < kWinQ; ++q)
-#pragma unroll
-    for (int u = 0; u < NU; ++u)
-#pragma unroll
-      for (int c = 0; c < E / 2; ++c) acc[q][u][c] = make_float2(0.f, 0.f);
-
-  for (int t = 0; t < rtot; t += RB) {
-    const int4 ro4 = *reinterpret_cast<const int4*>(rowoff + t);
-    const int ro[RB] = {ro4.x, ro4.y, ro4.z, ro4.w};
-    float v[RB][NU][E];
-#pragma unroll
-    for (int r = 0; r < RB; ++r)
-#pragma unroll
-      for (int u = 0; u < NU; ++u) Unit<T>::ldg(vb + ro[r] + u * (G * E), ro[r] >= 0, v[r][u]);
-    float4 w[RB];
-#pragma unroll
-    for (int r = 0; r < RB; ++r) w[r] = Wt[t + r];
-#pragma unroll
-    for (int r = 0; r < RB; ++r) {
-      const float wq[kWinQ] = {w[r].x, w[r].y, w[r].z, w[r].w};
-#pragma unroll
-      for (int q = 0; q < kWinQ; ++q) {
-        const float2 w2 = make_float2(wq[q], wq[q]);
-#pragma unroll
-        for (int u = 0; u < NU; ++u)
-#pragma unroll
-          for (int c = 0; c < E / 2; ++c)
-            acc[q][u][c] = __ffma2_rn(w2, make_float2(v[r][u][2 * c], v[r][u][2 * c + 1]), acc[q][u][c]);
-      }
-    }
-  }
-#pragma unroll
-  for (int q = 0; q < kWinQ; ++q) {
-    if (q < nq) {
-      T* og = out + (((size_t)b * d.Lq + q0 + q) * d.M + m) * d.D + j * E;
-#pragma unroll
-      for (int u = 0; u < NU; ++u) {
-        float o[E];
-#pragma unroll
-        for (int c = 0; c < E / 2; ++c) { o[2 * c] = acc[q][u][c].x; o[2 * c + 1] = acc[q][u][c].y; }
-        Unit<T>::st_stream(og + u * (G * E), o);
-      }
-    }
-  }
-}
-
-// CTA = kWinThreads threads = kWinThreads/G blocks of 4 consecutive queries of one (b, m).
+// Persistent CTAs of kWinThreads threads; each warp loops over units.  While a
+// block is processed the points of the warp's next unit travel to shared memory
+// (cp.async), so only the very first unit of a warp waits on HBM for them.
 template <typename T, int NU, int G>
 __global__ void __launch_bounds__(kWinThreads)
 msda_fwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ shapes,
                     const int64_t* __restrict__ lsi, const T* __restrict__ loc,
-                    const T* __restrict__ aw, T* __restrict__ out, Dims d, int nqc) {
+                    const T* __restrict__ aw, T* __restrict__ out, Dims d, int nqc,
+                    int units) {
+  using Raw = typename Unit<T>::Raw;
+  using SM = WinSmem<T, 1, false, 0>;
   constexpr int E = Unit<T>::E;
-  constexpr int NG = kWinThreads / G;
-  __shared__ int s_lvl[3 * kMaxLevelsFast];
-  __shared__ int s_one_d;
-  __shared__ __align__(16) float s_win[NG * kWinGroupFloats];
-  stage_levels(shapes, lsi, d.L, s_lvl, &s_one_d);
+  constexpr int NS = kWinStages;
+  constexpr int LPL = (kWinMaxL * 4 + G - 1) / G;
+  __shared__ int s_lvl[3 * kWinMaxL];
+  extern __shared__ __align__(16) char s_dyn[];
+  const bool one_d = win_stage_levels(shapes, lsi, d.L, s_lvl);
+  const int ustep = gridDim.x * (kWinThreads / 32);
+  const int uend = units;
 
-  const int tile = blockIdx.x;
-  const int m = tile % d.M;
-  const int qc = (tile / d.M) % nqc;
-  const int b = tile / (d.M * nqc);
   const int gi = threadIdx.x / G;
   const int j = threadIdx.x % G;
   const int lane = threadIdx.x & 31;
-  const int q0 = (qc * NG + gi) * kWinQ;
-  const int nq = min(kWinQ, d.Lq - q0);
-  if (nq <= 0) return;
-  float* s_grp = s_win + gi * kWinGroupFloats;
-  if (!s_one_d) {
-    fwd_body<T, NU, G, 4>(value, loc, aw, out, d, b, m, q0, q0 + nq, 1, s_lvl,
-                          reinterpret_cast<TapMeta<4>*>(s_grp));
+  const int gq = (gi & 3) * kWinQ;          // this group's query offset inside a unit
+  char* s_grp = s_dyn + gi * SM::kGroupBytes;
+  char* pts = s_grp + SM::kPlanBytes;
+  const float4* Wt = reinterpret_cast<const float4*>(s_grp);
+  const unsigned* rowoff = reinterpret_cast<const unsigned*>(s_grp + 16 * kWinRows);
+
+  int u = blockIdx.x * (kWinThreads / 32) + (threadIdx.x >> 5);
+  if (!one_d) {
+    for (; u < uend; u += ustep) {
+      const WinUnit w = win_decode(u, nqc, d.M);
+      const int q0 = w.q0 + gq;
+      fwd_body<T, NU, G, 4>(value, loc, aw, out, d, w.b, w.m, q0, min(q0 + kWinQ, d.Lq), 1, s_lvl,
+                            reinterpret_cast<TapMeta<4>*>(s_grp));
+      __syncwarp();
+    }
     return;
   }
-  const unsigned mask = group_mask<G>(lane);
-  const bool have_q = (j & 3) < nq;
-  const size_t grp_me = ((size_t)b * d.Lq + q0 + (have_q ? (j & 3) : 0)) * d.M + m;
-  WinPlan pl;
-  if (!win_build<T, G>(loc, aw, d, grp_me, have_q, s_lvl, s_grp, j, lane & ~(G - 1), mask, pl)) {
-    fwd_body<T, NU, G, 2>(value, loc, aw, out, d, b, m, q0, q0 + nq, 1, s_lvl,
-                          reinterpret_cast<TapMeta<2>*>(s_grp));
-    return;
+  WinFetch<T> fetch;
+  fetch.init(d, j);
+  if (u < uend) {
+    const WinUnit w = win_decode(u, nqc, d.M);
+    fetch.issue(loc, aw, d, w.b, w.m, w.q0 + gq, pts);
   }
-  const T* vb = value + ((size_t)b * d.S * d.M + m) * d.D + j * E;
-  fwd_win_rows<T, NU, G>(vb, out, d, b, m, q0, nq, s_grp, j, pl.rtot);
+  win_cp_commit();
+  while (u < uend) {
+    const WinUnit w = win_decode(u, nqc, d.M);
+    const int b = w.b, m = w.m, q0 = w.q0 + gq;
+    const int nq = max(min(kWinQ, d.Lq - q0), 0);
+    const bool have_q = (j & 3) < nq;
+    win_cp_wait_all();
+    __syncwarp();
+    int tb[LPL], rt, wmax;
+    const bool ok = win_build<T, G>(pts, d, have_q, s_lvl, s_grp, j, lane & ~(G - 1), tb, rt, wmax);
+    // win_build ends with a warp barrier: the staged points are consumed, the
+    // buffer can take the next unit's
+    const int un = u + ustep;
+    if (un < uend) {
+      const WinUnit wn = win_decode(un, nqc, d.M);
+      fetch.issue(loc, aw, d, wn.b, wn.m, wn.q0 + gq, pts);
+    }
+    win_cp_commit();
+
+    const char* vbb =
+        reinterpret_cast<const char*>(value + ((size_t)b * d.S * d.M + m) * d.D) + j * 16;
+    float2 acc[kWinQ][NU][E / 2];
+#pragma unroll
+    for (int q = 0; q < kWinQ; ++q)
+#pragma unroll
+      for (int uu = 0; uu < NU; ++uu)
+#pragma unroll
+        for (int c = 0; c < E / 2; ++c) acc[q][uu][c] = make_float2(0.f, 0.f);
+
+    // NS rows in flight per lane: row t+NS+s is requested as soon as row t+s is consumed
+    Raw buf[NS][NU][4];
+#pragma unroll
+    for (int s = 0; s < NS; ++s)
+#pragma unroll
+      for (int uu = 0; uu < NU; ++uu)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) buf[s][uu][k] = Raw(0);
+    {
+      const uint4 r4 = *reinterpret_cast<const uint4*>(rowoff);
+      const unsigned ro[4] = {r4.x, r4.y, r4.z, r4.w};
+#pragma unroll
+      for (int s = 0; s < NS; ++s) win_load_row<T, NU, G>(vbb, ro[s], s < rt, buf[s]);
+    }
+    for (int t = 0; t < wmax; t += NS) {
+      const uint4 r4 = *reinterpret_cast<const uint4*>(rowoff + t + NS);
+      const unsigned ro[4] = {r4.x, r4.y, r4.z, r4.w};
+#pragma unroll
+      for (int s = 0; s < NS; ++s) {
+        const float4 wv = Wt[t + s];
+        const float wq[kWinQ] = {wv.x, wv.y, wv.z, wv.w};
+#pragma unroll
+        for (int uu = 0; uu < NU; ++uu) {
+          float v[E];
+          Unit<T>::unpack_raw(buf[s][uu], v);
+#pragma unroll
+          for (int q = 0; q < kWinQ; ++q) {
+            const float2 w2 = make_float2(wq[q], wq[q]);
+#pragma unroll
+            for (int c = 0; c < E / 2; ++c)
+              acc[q][uu][c] = __ffma2_rn(w2, make_float2(v[2 * c], v[2 * c + 1]), acc[q][uu][c]);
+          }
+        }
+        win_load_row<T, NU, G>(vbb, ro[s], t + NS + s < rt, buf[s]);
+      }
+    }
+    if (ok) {
+#pragma unroll
+      for (int q = 0; q < kWinQ; ++q) {
+        if (q < nq) {
+          T* og = out + (((size_t)b * d.Lq + q0 + q) * d.M + m) * d.D + j * E;
+#pragma unroll
+          for (int uu = 0; uu < NU; ++uu) {
+            float o[E];
+#pragma unroll
+            for (int c = 0; c < E / 2; ++c) { o[2 * c] = acc[q][uu][c].x; o[2 * c + 1] = acc[q][uu][c].y; }
+            Unit<T>::st_stream(og + uu * (G * E), o);
+          }
+        }
+      }
+    } else {
+      // the plan area doubles as the per-tap body's scratch
+      fwd_body<T, NU, G, 2>(value, loc, aw, out, d, b, m, q0, q0 + nq, 1, s_lvl,
+                            reinterpret_cast<TapMeta<2>*>(s_grp));
+    }
+    __syncwarp();
+    u = un;
+  }
 }
 
 // ------------------------------- backward -----------------------------------
+// One step = the two packed rows t, t+1: grad_value rows leave as 128-bit reds,
+// the 2 x 4 dots <grad_out[q], value row> are transpose-reduced over the 8
+// lanes; lane (qi, h) ends with the total for (row t+h, query qi).
 template <typename T, int NU, int G>
-__device__ __forceinline__ void bwd_win_block(const T* __restrict__ value,
-                                              const T* __restrict__ loc, const T* __restrict__ aw,
-                                              const T* __restrict__ gout,
-                                              float* __restrict__ gvalue, T* __restrict__ gloc,
-                                              T* __restrict__ gaw, const Dims& d, int b, int m,
-                                              int q0, int nq, size_t grp_me, bool have_q,
-                                              const int* s_lvl, float* s_grp, int j, unsigned mask,
-                                              const WinPlan& pl) {
-  static_assert(G == 8, "transpose-reduce of 2 rows x 4 queries over 8 lanes");
+__device__ __forceinline__ void bwd_win_step(const float4* Wt, float* Gs, char* gvbb, unsigned ro0,
+                                             unsigned ro1, int t, int rt, int j,
+                                             const typename Unit<T>::Raw (&b0)[NU][4],
+                                             const typename Unit<T>::Raw (&b1)[NU][4],
+                                             const float2 (&go)[kWinQ][NU][Unit<T>::E / 2]) {
   constexpr int E = Unit<T>::E;
-  constexpr int RB = 2;
-  constexpr int NH = G / 4;
-  constexpr int LPL = (kWinMaxL + NH - 1) / NH;
-  float4* Wt = reinterpret_cast<float4*>(s_grp);
-  float* Gs = s_grp;  // the dots G[t][qi] overwrite Wt[t][qi] row by row
-  const int* rowoff = reinterpret_cast<const int*>(s_grp + 4 * kWinCap);
-  const int qi = j & 3, h = j >> 2;
-  const size_t voff = ((size_t)b * d.S * d.M + m) * d.D + j * E;
-  const T* vb = value + voff;
-  float* gvb = gvalue + voff;
-
-  float2 go[kWinQ][NU][E / 2];
+  constexpr unsigned FULL = 0xffffffffu;
+  constexpr unsigned kAccScale = (unsigned)(sizeof(float) / sizeof(T));  // fp32 image of a T slab
+  float x[2 * kWinQ];
 #pragma unroll
-  for (int q = 0; q < kWinQ; ++q) {
-    const T* gg = gout + (((size_t)b * d.Lq + q0 + min(q, nq - 1)) * d.M + m) * d.D + j * E;
+  for (int r = 0; r < 2; ++r) {
+    const float4 w = Wt[t + r];
+    const float wq[kWinQ] = {w.x, w.y, w.z, w.w};
+    float* gp = reinterpret_cast<float*>(
+        const_cast<char*>(win_addr(gvbb, (r == 0 ? ro0 : ro1) * kAccScale)));
+    const bool real = t + r < rt;
+    float2 s[kWinQ];
+#pragma unroll
+    for (int q = 0; q < kWinQ; ++q) s[q] = make_float2(0.f, 0.f);
 #pragma unroll
     for (int u = 0; u < NU; ++u) {
-      float t[E];
-      Unit<T>::ld_stream(gg + u * (G * E), t);
-#pragma unroll
-      for (int c = 0; c < E / 2; ++c)
-        go[q][u][c] = q < nq ? make_float2(t[2 * c], t[2 * c + 1]) : make_float2(0.f, 0.f);
-    }
-  }
-
-  const int rtot = pl.rtot;
-  for (int t = 0; t < rtot; t += RB) {
-    const int2 ro2 = *reinterpret_cast<const int2*>(rowoff + t);
-    const int ro[RB] = {ro2.x, ro2.y};
-    float v[RB][NU][E];
-#pragma unroll
-    for (int r = 0; r < RB; ++r)
-#pragma unroll
-      for (int u = 0; u < NU; ++u) Unit<T>::ldg(vb + ro[r] + u * (G * E), ro[r] >= 0, v[r][u]);
-    float4 w[RB];
-#pragma unroll
-    for (int r = 0; r < RB; ++r) w[r] = Wt[t + r];
-    float dots[RB * kWinQ];
-#pragma unroll
-    for (int r = 0; r < RB; ++r) {
-      const float wq[kWinQ] = {w[r].x, w[r].y, w[r].z, w[r].w};
       // grad_value row: sum_q Wt[t][q] * grad_out[q]
+      float2 dv[E / 2];
 #pragma unroll
-      for (int u = 0; u < NU; ++u) {
-        float2 dv[E / 2];
-#pragma unroll
-        for (int c = 0; c < E / 2; ++c) dv[c] = make_float2(0.f, 0.f);
-#pragma unroll
-        for (int q = 0; q < kWinQ; ++q) {
-          const float2 w2 = make_float2(wq[q], wq[q]);
-#pragma unroll
-          for (int c = 0; c < E / 2; ++c) dv[c] = __ffma2_rn(w2, go[q][u][c], dv[c]);
-        }
-#pragma unroll
-        for (int c = 0; c < E / 2; c += 2)
-          red_add_f32x4_pred(gvb + ro[r] + u * (G * E) + 2 * c, ro[r] >= 0, dv[c].x, dv[c].y,
-                             dv[c + 1].x, dv[c + 1].y);
-      }
-      // this lane's share of <grad_out[q], value row>
+      for (int c = 0; c < E / 2; ++c) dv[c] = make_float2(0.f, 0.f);
 #pragma unroll
       for (int q = 0; q < kWinQ; ++q) {
-        float2 s = make_float2(0.f, 0.f);
+        const float2 w2 = make_float2(wq[q], wq[q]);
 #pragma unroll
-        for (int u = 0; u < NU; ++u)
-#pragma unroll
-          for (int c = 0; c < E / 2; ++c)
-            s = __ffma2_rn(go[q][u][c], make_float2(v[r][u][2 * c], v[r][u][2 * c + 1]), s);
-        dots[r * kWinQ + q] = s.x + s.y;
+        for (int c = 0; c < E / 2; ++c) dv[c] = __ffma2_rn(w2, go[q][u][c], dv[c]);
       }
+      if (real) {
+#pragma unroll
+        for (int c = 0; c < E / 2; c += 2)
+          red_add_f32x4(gp + u * (G * E) + 2 * c, dv[c].x, dv[c].y, dv[c + 1].x, dv[c + 1].y);
+      }
+      // this lane's share of <grad_out[q], value row>
+      float v[E];
+      Unit<T>::unpack_raw(r == 0 ? b0[u] : b1[u], v);
+#pragma unroll
+      for (int q = 0; q < kWinQ; ++q)
+#pragma unroll
+        for (int c = 0; c < E / 2; ++c)
+          s[q] = __ffma2_rn(go[q][u][c], make_float2(v[2 * c], v[2 * c + 1]), s[q]);
     }
-    const float tot = transpose_reduce<G>(dots, j, mask);  // lane j: row t + (j >> 2), query j & 3
-    __syncwarp(mask);
-    Gs[(t + h) * 4 + qi] = tot;
+#pragma unroll
+    for (int q = 0; q < kWinQ; ++q) x[r * kWinQ + q] = s[q].x + s[q].y;
   }
-  __syncwarp(mask);
-
-  // per-point gradients: reload the points, redo the geometry, pick the dots
-  const int LP = d.L * kWinP;
-#pragma unroll
-  for (int i = 0; i < LPL; ++i) {
-    const int l = h + i * NH;
-    const bool active = have_q && l < d.L;
-    const int ls = active ? l : 0;
-    float x[4], y[4], a[4];
-    WinPts<T>::ld(loc + (grp_me * LP + ls * kWinP) * 2, aw + grp_me * LP + ls * kWinP, x, y, a);
-    const int W = s_lvl[3 * ls + 1], start = s_lvl[3 * ls + 2];
-    int tb = pl.off[0] - pl.lo[0];
-#pragma unroll
-    for (int ll = 1; ll < kWinMaxL; ++ll)
-      if (l == ll) tb = pl.off[ll] - pl.lo[ll];
-    float gx[4], gy[4], ga[4];
-#pragma unroll
-    for (int p = 0; p < 4; ++p) {
-      int r0;
-      float w0, w1;
-      bool v0, v1;
-      WinCoef c;
-      win_point<true>(x[p], y[p], a[p], W, start, d.border != 0, active, r0, w0, w1, v0, v1, c);
-      const int t0 = (v0 || v1) ? (r0 + tb) * 4 + qi : qi;
-      const float g0 = v0 ? Gs[t0] : 0.f;
-      const float g1 = v1 ? Gs[t0 + 4] : 0.f;
-      ga[p] = fmaf(c.k0, g0, c.k1 * g1);
-      gx[p] = c.fx * (g1 - g0);
-      gy[p] = fmaf(c.cy0, g0, c.cy1 * g1);
-    }
-    if (active)
-      WinPts<T>::st(gloc + (grp_me * LP + l * kWinP) * 2, gaw + grp_me * LP + l * kWinP, gx, gy, ga);
-  }
+  const float tot = transpose_reduce<8>(x, j, FULL);
+  __syncwarp();
+  Gs[t * 4 + j] = tot;   // (row t + (j >> 2), query j & 3)
 }
 
 template <typename T, int NU, int G>
-__global__ void __launch_bounds__(kWinThreads)
+__global__ void __launch_bounds__(kWinThreads, 3)
 msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ shapes,
                     const int64_t* __restrict__ lsi, const T* __restrict__ loc,
                     const T* __restrict__ aw, const T* __restrict__ gout,
                     float* __restrict__ gvalue, T* __restrict__ gloc, T* __restrict__ gaw, Dims d,
-                    int nqc) {
-  constexpr int NG = kWinThreads / G;
-  __shared__ int s_lvl[3 * kMaxLevelsFast];
-  __shared__ int s_one_d;
-  __shared__ __align__(16) float s_win[NG * kWinGroupFloats];
-  stage_levels(shapes, lsi, d.L, s_lvl, &s_one_d);
+                    int nqc, int units) {
+  static_assert(G == 8, "two rows x four queries are transpose-reduced over 8 lanes");
+  using Raw = typename Unit<T>::Raw;
+  constexpr int E = Unit<T>::E;
+  constexpr int DD = NU * G * E;   // head channels
+  using SM = WinSmem<T, 2, true, DD>;
+  constexpr int NH = G / 4;
+  constexpr int NS = 4;
+  constexpr int LPL = (kWinMaxL * 4 + G - 1) / G;
+  __shared__ int s_lvl[3 * kWinMaxL];
+  extern __shared__ __align__(16) char s_dyn[];
+  const bool one_d = win_stage_levels(shapes, lsi, d.L, s_lvl);
+  const int ustep = gridDim.x * (kWinThreads / 32);
+  const int uend = units;
 
-  const int tile = blockIdx.x;
-  const int m = tile % d.M;
-  const int qc = (tile / d.M) % nqc;
-  const int b = tile / (d.M * nqc);
   const int gi = threadIdx.x / G;
   const int j = threadIdx.x % G;
   const int lane = threadIdx.x & 31;
-  const int q0 = (qc * NG + gi) * kWinQ;
-  const int nq = min(kWinQ, d.Lq - q0);
-  if (nq <= 0) return;
-  float* s_grp = s_win + gi * kWinGroupFloats;
-  if (!s_one_d) {
-    bwd_body<T, NU, G, 4>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q0, q0 + nq, 1, s_lvl,
-                          reinterpret_cast<TapMeta<4>*>(s_grp));
+  const int gq = (gi & 3) * kWinQ;
+  const int qi = j & 3, h = j >> 2;
+  char* s_grp = s_dyn + gi * SM::kGroupBytes;
+  char* pts_buf = s_grp + SM::kPlanBytes;                       // two buffers of kPtsBytes
+  char* go_buf = pts_buf + 2 * SM::kPtsBytes;                   // 4 x D grad_out
+  const float4* Wt = reinterpret_cast<const float4*>(s_grp);
+  float* Gs = reinterpret_cast<float*>(s_grp);  // the dots G[t][qi] overwrite Wt[t][qi] step by step
+  const unsigned* rowoff = reinterpret_cast<const unsigned*>(s_grp + 16 * kWinRows);
+
+  int u = blockIdx.x * (kWinThreads / 32) + (threadIdx.x >> 5);
+  if (!one_d) {
+    for (; u < uend; u += ustep) {
+      const WinUnit w = win_decode(u, nqc, d.M);
+      const int q0 = w.q0 + gq;
+      bwd_body<T, NU, G, 4>(value, loc, aw, gout, gvalue, gloc, gaw, d, w.b, w.m, q0,
+                            min(q0 + kWinQ, d.Lq), 1, s_lvl, reinterpret_cast<TapMeta<4>*>(s_grp));
+      __syncwarp();
+    }
     return;
   }
-  const unsigned mask = group_mask<G>(lane);
-  const bool have_q = (j & 3) < nq;
-  const size_t grp_me = ((size_t)b * d.Lq + q0 + (have_q ? (j & 3) : 0)) * d.M + m;
-  WinPlan pl;
-  if (!win_build<T, G>(loc, aw, d, grp_me, have_q, s_lvl, s_grp, j, lane & ~(G - 1), mask, pl)) {
-    bwd_body<T, NU, G, 2>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q0, q0 + nq, 1, s_lvl,
-                          reinterpret_cast<TapMeta<2>*>(s_grp));
-    return;
+  // grad_out rows of a block: 4 x D*sizeof(T) bytes, 16-byte pieces over the 8 lanes
+  auto fetch_gout = [&](const WinUnit& w) {
+    constexpr int per_q = DD * (int)sizeof(T) / 16;   // 16-byte pieces per query: NU * G
+    const char* gb = reinterpret_cast<const char*>(
+        gout + (((size_t)w.b * d.Lq + w.q0 + gq) * d.M + w.m) * d.D);
+    const unsigned qstride = (unsigned)(d.M * d.D) * (unsigned)sizeof(T);
+#pragma unroll
+    for (int q = 0; q < kWinQ; ++q)
+      if (w.q0 + gq + q < d.Lq) {
+#pragma unroll
+        for (int k = 0; k < per_q / 8; ++k)
+          win_cp16(go_buf + (q * per_q + k * 8 + j) * 16, win_addr(gb, q * qstride + (k * 8 + j) * 16));
+      }
+  };
+  int cur = 0;
+  WinFetch<T> fetch;
+  fetch.init(d, j);
+  if (u < uend) {
+    const WinUnit w = win_decode(u, nqc, d.M);
+    fetch.issue(loc, aw, d, w.b, w.m, w.q0 + gq, pts_buf);
+    fetch_gout(w);
   }
-  bwd_win_block<T, NU, G>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q0, nq, grp_me, have_q,
-                          s_lvl, s_grp, j, mask, pl);
+  win_cp_commit();
+  while (u < uend) {
+    const WinUnit w = win_decode(u, nqc, d.M);
+    const int b = w.b, m = w.m, q0 = w.q0 + gq;
+    const int nq = max(min(kWinQ, d.Lq - q0), 0);
+    const bool have_q = qi < nq;
+    const char* pts = pts_buf + cur * SM::kPtsBytes;
+    win_cp_wait_all();
+    __syncwarp();
+    int tb[LPL], rt, wmax;
+    const bool ok = win_build<T, G>(pts, d, have_q, s_lvl, s_grp, j, lane & ~(G - 1), tb, rt, wmax);
+
+    // grad_out of the 4 queries: shared memory -> registers (lane's channels)
+    float2 go[kWinQ][NU][E / 2];
+#pragma unroll
+    for (int q = 0; q < kWinQ; ++q) {
+#pragma unroll
+      for (int uu = 0; uu < NU; ++uu) {
+        Raw raw[4];
+        const uint4 t4 = *reinterpret_cast<const uint4*>(go_buf + q * (DD * (int)sizeof(T)) + uu * (G * 16) + j * 16);
+        raw[0] = __builtin_bit_cast(Raw, t4.x); raw[1] = __builtin_bit_cast(Raw, t4.y);
+        raw[2] = __builtin_bit_cast(Raw, t4.z); raw[3] = __builtin_bit_cast(Raw, t4.w);
+        float t[E];
+        Unit<T>::unpack_raw(raw, t);
+#pragma unroll
+        for (int c = 0; c < E / 2; ++c)
+          go[q][uu][c] = q < nq ? make_float2(t[2 * c], t[2 * c + 1]) : make_float2(0.f, 0.f);
+      }
+    }
+    __syncwarp();
+    // next unit: points into the other buffer, grad_out into the one just drained
+    const int un = u + ustep;
+    if (un < uend) {
+      const WinUnit wn = win_decode(un, nqc, d.M);
+      fetch.issue(loc, aw, d, wn.b, wn.m, wn.q0 + gq, pts_buf + (cur ^ 1) * SM::kPtsBytes);
+      fetch_gout(wn);
+    }
+    win_cp_commit();
+
+    const size_t voff = ((size_t)b * d.S * d.M + m) * d.D;
+    const char* vbb = reinterpret_cast<const char*>(value + voff) + j * 16;
+    char* gvbb = reinterpret_cast<char*>(gvalue + voff + j * E);
+
+    // NS rows in flight per lane
+    Raw buf[NS][NU][4];
+#pragma unroll
+    for (int s = 0; s < NS; ++s)
+#pragma unroll
+      for (int uu = 0; uu < NU; ++uu)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) buf[s][uu][k] = Raw(0);
+    uint4 rc = *reinterpret_cast<const uint4*>(rowoff);
+    win_load_row<T, NU, G>(vbb, rc.x, 0 < rt, buf[0]);
+    win_load_row<T, NU, G>(vbb, rc.y, 1 < rt, buf[1]);
+    win_load_row<T, NU, G>(vbb, rc.z, 2 < rt, buf[2]);
+    win_load_row<T, NU, G>(vbb, rc.w, 3 < rt, buf[3]);
+    for (int t = 0; t < wmax; t += NS) {
+      const uint4 rn = *reinterpret_cast<const uint4*>(rowoff + t + NS);
+      bwd_win_step<T, NU, G>(Wt, Gs, gvbb, rc.x, rc.y, t, rt, j, buf[0], buf[1], go);
+      win_load_row<T, NU, G>(vbb, rn.x, t + NS + 0 < rt, buf[0]);
+      win_load_row<T, NU, G>(vbb, rn.y, t + NS + 1 < rt, buf[1]);
+      bwd_win_step<T, NU, G>(Wt, Gs, gvbb, rc.z, rc.w, t + 2, rt, j, buf[2], buf[3], go);
+      win_load_row<T, NU, G>(vbb, rn.z, t + NS + 2 < rt, buf[2]);
+      win_load_row<T, NU, G>(vbb, rn.w, t + NS + 3 < rt, buf[3]);
+      rc = rn;
+    }
+    __syncwarp();
+
+    if (ok) {
+      // per-point gradients: the staged points again, the geometry again, the dots
+      const int LP = d.L * kWinP;
+      const size_t grp_me = ((size_t)b * d.Lq + (have_q ? q0 + qi : 0)) * d.M + m;
+#pragma unroll
+      for (int i = 0; i < LPL; ++i) {
+        const int l = h + i * NH;
+        const bool active = have_q && l < d.L;
+        const int ls = l < d.L ? l : 0;
+        float x[4], y[4], a[4];
+        WinPts<T>::ld_smem(win_pts_loc<T>(pts, d.L, qi, ls), win_pts_aw<T>(pts, d.L, qi, ls), x, y, a);
+        const int W = s_lvl[3 * ls + 1], start = s_lvl[3 * ls + 2];
+        float gx[4], gy[4], ga[4];
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+          int r0;
+          float w0, w1;
+          bool live, v0, v1;
+          WinCoef c;
+          win_point<true>(x[p], y[p], a[p], W, start, d.border != 0, active, r0, w0, w1, live, v0,
+                          v1, c);
+          const int t0 = (r0 + tb[i]) * 4 + qi;
+          const float g0 = v0 ? Gs[t0] : 0.f;
+          const float g1 = v1 ? Gs[t0 + 4] : 0.f;
+          ga[p] = fmaf(c.k0, g0, c.k1 * g1);
+          gx[p] = c.fx * (g1 - g0);
+          gy[p] = fmaf(c.cy0, g0, c.cy1 * g1);
+        }
+        if (active)
+          WinPts<T>::st(gloc + (grp_me * LP + l * kWinP) * 2, gaw + grp_me * LP + l * kWinP, gx, gy, ga);
+      }
+    } else {
+      bwd_body<T, NU, G, 2>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q0, q0 + nq, 1, s_lvl,
+                            reinterpret_cast<TapMeta<2>*>(s_grp));
+    }
+    __syncwarp();
+    cur ^= 1;
+    u = un;
+  }
 }
 
 }  // namespace msda

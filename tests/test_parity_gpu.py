@@ -92,7 +92,7 @@ def test_fp32_vs_oracle(oracle_c, case, padding, dist):
     N, Lq, M, D, P, shapes = case
     inp = synthetic.make_inputs(N, Lq, M, D, P, shapes, torch.float32, DEV, seed=7, dist=dist)
     want = run_oracle(oracle_c, inp, padding)
-    for flags in (0, _lib.MSDA_FLAG_FORCE_GENERIC, _lib.MSDA_FLAG_NO_WINDOW):
+    for flags in (0, _lib.MSDA_FLAG_FORCE_GENERIC, _lib.MSDA_FLAG_NO_WINDOW, _lib.MSDA_FLAG_FORCE_WINDOW):
         got = run_cuda(inp, padding, flags)
         assert np.abs(got[0] - want[0]).max() <= FWD_ABS_F32
         for g_, w_, nm in zip(got[1:], want[1:], ("grad_value", "grad_loc", "grad_aw")):
@@ -117,7 +117,7 @@ def test_bf16_vs_fp32_oracle_on_rounded_inputs(oracle_c, case, padding):
                                 value="normal")
     want = run_oracle(oracle_c, {k: (v.float() if v.is_floating_point() else v) for k, v in inp.items()},
                       padding)
-    for flags in (0, _lib.MSDA_FLAG_FORCE_GENERIC):
+    for flags in (0, _lib.MSDA_FLAG_FORCE_GENERIC, _lib.MSDA_FLAG_FORCE_WINDOW):
         got = run_cuda(inp, padding, flags)
         assert rel_err(got[0], want[0]) <= BF16_FWD_REL
         for g_, w_, nm in zip(got[1:], want[1:], ("grad_value", "grad_loc", "grad_aw")):

@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--dtypes", default="f32,bf16")
     ap.add_argument("--iters", type=int, default=50)
     ap.add_argument("--flags", default="0,4")
+    ap.add_argument("--ring", type=int, default=4, help="distinct input sets rotated (1 = L2-resident inputs)")
     args = ap.parse_args()
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(dev)
@@ -39,7 +40,7 @@ def main():
             for dts in args.dtypes.split(","):
                 dtype = {"f32": torch.float32, "bf16": torch.bfloat16}[dts]
                 ring = [synthetic.make_workload(wl, dtype, dev, seed=1234 + r, dist=dist, value="normal")
-                        for r in range(4)]
+                        for r in range(args.ring)]
                 outs = {}
                 for fl in [int(x) for x in args.flags.split(",")]:
                     bufs = [bench.OpBuffers(i, "zeros", 0) for i in ring]
@@ -49,12 +50,12 @@ def main():
                     fb, bb = synthetic.algorithmic_bytes(b0.N, b0.S, b0.Lq, b0.M, b0.D, b0.L, b0.P,
                                                          ring[0]["value"].element_size())
                     for i in range(8):
-                        b = bufs[i % 4]
+                        b = bufs[i % len(bufs)]
                         b.fwd(st); b.zero(); b.bwd(st)
                     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(args.iters)]
                     torch.cuda.synchronize()
                     for i in range(args.iters):
-                        b = bufs[i % 4]
+                        b = bufs[i % len(bufs)]
                         ev[i][0].record(); b.fwd(st)
                         ev[i][1].record(); b.zero()
                         ev[i][2].record(); b.bwd(st)
