@@ -319,7 +319,9 @@ def run_ours(args):
         pass
     hbm_peak = float(peaks["hbm_gbs"]) if peaks else 6650.0
     achieved = bytes_bwd / (bwd_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "msda_bwd_fast_kernel", "achieved": achieved, "peak": hbm_peak,
+    fam = b0.lib.msda_kernel_choice(N, S, M, D, L, Lq, P, b0.dt, b0.flags).decode()
+    kname = {"window": "win", "fast": "fast", "generic": "generic"}.get(fam, fam)
+    roofline = {"bound": "hbm", "kernel": "msda_bwd_%s_kernel" % kname, "achieved": achieved, "peak": hbm_peak,
                 "peak_source": peak_src + " (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s",
                 "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
                 "algorithmic_bytes_per_launch": bytes_bwd, "kernel_ms": bwd_ms,

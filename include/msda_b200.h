@@ -91,6 +91,14 @@ const char* msda_error_string(int status);
 /* Name of the kernel family msda_forward/backward would pick:
  * "fast" (vectorised, warp-cooperative) or "generic". */
 const char* msda_kernel_family(int64_t D, int dtype, unsigned flags);
+/* Kernel family for a full problem shape (16-byte aligned pointers assumed):
+ * "window"  row-window kernels msda_{fwd,bwd}_win_kernel (temporal maps, P = 4,
+ *           L <= 4, long query lists; per block of 4 queries they fall back to
+ *           the per-tap body when the block has no compact window),
+ * "fast"    per-tap vectorised kernels msda_{fwd,bwd}_fast_kernel,
+ * "generic" any-D / fp64 kernels, "invalid" for a bad shape or dtype. */
+const char* msda_kernel_choice(int64_t N, int64_t S, int64_t M, int64_t D, int64_t L,
+                               int64_t Lq, int64_t P, int dtype, unsigned flags);
 
 /*
  * out[b,q,m,:] = sum_{l,p} aw[b,q,m,l,p] * bilinear(value_l[b,:,m,:], loc[b,q,m,l,p])

@@ -31,6 +31,7 @@ EXPORTED_SYMBOLS = (
     "msda_abi_version",
     "msda_error_string",
     "msda_kernel_family",
+    "msda_kernel_choice",
     "msda_forward",
     "msda_backward_workspace_bytes",
     "msda_backward",
@@ -57,6 +58,8 @@ def _declare(lib):
     lib.msda_error_string.argtypes = [c.c_int]
     lib.msda_kernel_family.restype = c.c_char_p
     lib.msda_kernel_family.argtypes = [i64, c.c_int, u32]
+    lib.msda_kernel_choice.restype = c.c_char_p
+    lib.msda_kernel_choice.argtypes = [i64] * 7 + [c.c_int, u32]
     lib.msda_last_cuda_error.restype = c.c_int
     lib.msda_last_cuda_error.argtypes = []
     lib.msda_last_cuda_error_string.restype = c.c_char_p

@@ -126,8 +126,8 @@ inline bool win_applies(const Dims& d, int dtype, unsigned flags) {
   return false;
 }
 
-// Persistent launch: as many CTAs as fit on the device at once (the kernels
-// distribute 16-query units themselves).
+// Persistent launch: as many CTAs as are resident at once; warp w of the grid
+// takes units w, w + W, w + 2W, ...
 template <typename K>
 int win_grid(K kern, size_t smem, long long units, int* grid) {
   int dev = 0, sms = 0, per_sm = 0;
@@ -168,8 +168,7 @@ int launch_bwd_win(const void* value, const int64_t* shapes, const int64_t* lsi,
                    const Dims& d, cudaStream_t st) {
   const int nqc = (d.Lq + 4 * kWinQ - 1) / (4 * kWinQ);
   const long long units = (long long)d.N * d.M * nqc;
-  constexpr int DD = NU * G * (16 / (int)sizeof(T));
-  constexpr size_t smem = (size_t)(kWinThreads / G) * WinSmem<T, 2, true, DD>::kGroupBytes;
+  constexpr size_t smem = (size_t)(kWinThreads / G) * WinSmem<T, 2, false, 0>::kGroupBytes;
   auto kern = msda_bwd_win_kernel<T, NU, G>;
   int grid = 1;
   const int rc = win_grid(kern, smem, units, &grid);
@@ -251,6 +250,14 @@ const char* msda_error_string(int status) {
 
 const char* msda_kernel_family(int64_t D, int dtype, unsigned flags) {
   return fast_applies(D, 1, dtype, flags) ? "fast" : "generic";
+}
+
+const char* msda_kernel_choice(int64_t N, int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq,
+                               int64_t P, int dtype, unsigned flags) {
+  if (check_common(N, S, M, D, L, Lq, P, dtype, MSDA_PAD_ZEROS) != MSDA_OK) return "invalid";
+  const bool fast = S * M * D < (int64_t(1) << 31) && fast_applies(D, L, dtype, flags);
+  if (!fast) return "generic";
+  return win_applies(make_dims(N, S, M, D, L, Lq, P, MSDA_PAD_ZEROS), dtype, flags) ? "window" : "fast";
 }
 
 int msda_last_cuda_error(void) { return t_last_cuda_error; }

@@ -43,7 +43,7 @@ constexpr int kWinP = 4;         // points per level (template-free fast case)
 constexpr int kWinMaxL = 4;      // levels
 constexpr int kWinCap = 88;      // packed rows per block, multiple of 4
 constexpr int kWinRows = kWinCap + 8;  // + padding rows read by the software pipeline
-constexpr int kWinThreads = 128;
+constexpr int kWinThreads = 128;     // 4 warps = 4 adjacent units per CTA (they share rows in L1)
 constexpr int kWinMinQueries = 256;  // host heuristic: shorter query lists use the per-tap kernels
 
 struct WinCoef { float k0, k1, fx, cy0, cy1; };
@@ -83,9 +83,9 @@ __device__ __forceinline__ void win_point(float x, float y, float a, int W, int 
     c.k0 = v0 ? k0 : 0.f;
     c.k1 = v1 ? k1 : 0.f;
     c.fx = live ? sx * a * fy : 0.f;
-    const float sg = live ? copysignf(sy, -h_im) * a : 0.f;   // h_im >= 0: -sy, else +sy
-    c.cy0 = sg * hw;
-    c.cy1 = sg * lw;
+    const float sg = copysignf(sy, -h_im) * a;   // h_im >= 0: -sy, else +sy
+    c.cy0 = live ? sg * hw : 0.f;                // (a NaN location has NaN hw / lw)
+    c.cy1 = live ? sg * lw : 0.f;
   }
 }
 
@@ -219,55 +219,31 @@ struct WinSmem {
   static constexpr int kGroupBytes = kPlanBytes + NPB * kPtsBytes + kGoutBytes + 16;  // +16: bank skew
 };
 
-// cp.async the sampling points of block (b, q0.., m) into `dst` (loc of the 4
-// queries, then their attention weights); queries >= Lq are skipped.  The piece
-// a lane copies is the same for every block: (query, loc|aw, 16-byte index).
+// cp.async the sampling points of block (b, q0.., m) into `buf`: loc of the 4
+// queries, then their attention weights; queries >= Lq are skipped.  A query's
+// loc is at most 8 and its aw at most 4 16-byte pieces (L <= 4, P = 4), so lane j
+// copies piece j of each.
 template <typename T>
-struct WinFetch {
-  static constexpr int kMaxPieces = (4 * kWinMaxL * kWinP * 3 * (int)sizeof(T) / 16 + 7) / 8;
-  int n;                       // pieces of this lane
-  int qi[kMaxPieces];
-  unsigned src[kMaxPieces];    // byte offset from the block's loc (or aw) base
-  unsigned dst[kMaxPieces];    // byte offset in the staging buffer; bit 31: aw
-  __device__ __forceinline__ void init(const Dims& d, int j) {
-    const int LP = d.L * kWinP;
-    const int loc_chunks = LP * 2 * (int)sizeof(T) / 16;
-    const int aw_chunks = LP * (int)sizeof(T) / 16;
-    const int per_q = loc_chunks + aw_chunks;
-    n = 0;
+__device__ __forceinline__ void win_fetch_points(const T* __restrict__ loc, const T* __restrict__ aw,
+                                                 const Dims& d, int b, int m, int q0, char* buf,
+                                                 int j) {
+  const int LP = d.L * kWinP;
+  const int loc_chunks = LP * 2 * (int)sizeof(T) / 16;
+  const int aw_chunks = LP * (int)sizeof(T) / 16;
+  const size_t grp = ((size_t)b * d.Lq + q0) * d.M + m;
+  const char* lb = reinterpret_cast<const char*>(loc + grp * LP * 2) + j * 16;
+  const char* ab = reinterpret_cast<const char*>(aw + grp * LP) + j * 16;
+  const unsigned lstride = (unsigned)(d.M * LP * 2) * (unsigned)sizeof(T);   // next query, same head
+  char* ldst = buf + j * 16;
+  char* adst = buf + (4 * loc_chunks + j) * 16;
 #pragma unroll
-    for (int i = 0; i < kMaxPieces; ++i) {
-      const int c = j + 8 * i;
-      qi[i] = 0; src[i] = 0; dst[i] = 0;
-      if (c < 4 * per_q) {
-        n = i + 1;
-        const int q = c / per_q, k = c - q * per_q;
-        qi[i] = q;
-        if (k < loc_chunks) {
-          src[i] = (unsigned)(q * d.M * LP * 2 * (int)sizeof(T) + k * 16);
-          dst[i] = (unsigned)((q * loc_chunks + k) * 16);
-        } else {
-          src[i] = (unsigned)(q * d.M * LP * (int)sizeof(T) + (k - loc_chunks) * 16);
-          dst[i] = (unsigned)((4 * loc_chunks + q * aw_chunks + (k - loc_chunks)) * 16) | 0x80000000u;
-        }
-      }
+  for (int q = 0; q < kWinQ; ++q) {
+    if (q0 + q < d.Lq) {
+      if (j < loc_chunks) win_cp16(ldst + q * loc_chunks * 16, win_addr(lb, q * lstride));
+      if (j < aw_chunks) win_cp16(adst + q * aw_chunks * 16, win_addr(ab, q * (lstride >> 1)));
     }
   }
-  __device__ __forceinline__ void issue(const T* __restrict__ loc, const T* __restrict__ aw,
-                                        const Dims& d, int b, int m, int q0, char* buf) const {
-    const int LP = d.L * kWinP;
-    const size_t grp = ((size_t)b * d.Lq + q0) * d.M + m;
-    const char* lb = reinterpret_cast<const char*>(loc + grp * LP * 2);
-    const char* ab = reinterpret_cast<const char*>(aw + grp * LP);
-#pragma unroll
-    for (int i = 0; i < kMaxPieces; ++i) {
-      if (i < n && q0 + qi[i] < d.Lq) {
-        const bool is_aw = (dst[i] >> 31) != 0;
-        win_cp16(buf + (dst[i] & 0x7fffffffu), win_addr(is_aw ? ab : lb, src[i]));
-      }
-    }
-  }
-};
+}
 template <typename T>
 __device__ __forceinline__ const T* win_pts_loc(const char* pts, int L, int qi, int l) {
   return reinterpret_cast<const T*>(pts) + (qi * L * kWinP + l * kWinP) * 2;
@@ -451,11 +427,9 @@ msda_fwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
     }
     return;
   }
-  WinFetch<T> fetch;
-  fetch.init(d, j);
   if (u < uend) {
     const WinUnit w = win_decode(u, nqc, d.M);
-    fetch.issue(loc, aw, d, w.b, w.m, w.q0 + gq, pts);
+    win_fetch_points<T>(loc, aw, d, w.b, w.m, w.q0 + gq, pts, j);
   }
   win_cp_commit();
   while (u < uend) {
@@ -472,7 +446,7 @@ msda_fwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
     const int un = u + ustep;
     if (un < uend) {
       const WinUnit wn = win_decode(un, nqc, d.M);
-      fetch.issue(loc, aw, d, wn.b, wn.m, wn.q0 + gq, pts);
+      win_fetch_points<T>(loc, aw, d, wn.b, wn.m, wn.q0 + gq, pts, j);
     }
     win_cp_commit();
 
@@ -487,6 +461,7 @@ msda_fwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
         for (int c = 0; c < E / 2; ++c) acc[q][uu][c] = make_float2(0.f, 0.f);
 
     // NS rows in flight per lane: row t+NS+s is requested as soon as row t+s is consumed
+    const int rl = (d.dbg & 8) ? 0 : rt;
     Raw buf[NS][NU][4];
 #pragma unroll
     for (int s = 0; s < NS; ++s)
@@ -498,7 +473,7 @@ msda_fwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
       const uint4 r4 = *reinterpret_cast<const uint4*>(rowoff);
       const unsigned ro[4] = {r4.x, r4.y, r4.z, r4.w};
 #pragma unroll
-      for (int s = 0; s < NS; ++s) win_load_row<T, NU, G>(vbb, ro[s], s < rt, buf[s]);
+      for (int s = 0; s < NS; ++s) win_load_row<T, NU, G>(vbb, ro[s], s < rl, buf[s]);
     }
     for (int t = 0; t < wmax; t += NS) {
       const uint4 r4 = *reinterpret_cast<const uint4*>(rowoff + t + NS);
@@ -519,7 +494,7 @@ msda_fwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
               acc[q][uu][c] = __ffma2_rn(w2, make_float2(v[2 * c], v[2 * c + 1]), acc[q][uu][c]);
           }
         }
-        win_load_row<T, NU, G>(vbb, ro[s], t + NS + s < rt, buf[s]);
+        win_load_row<T, NU, G>(vbb, ro[s], t + NS + s < rl, buf[s]);
       }
     }
     if (ok) {
@@ -605,7 +580,7 @@ __device__ __forceinline__ void bwd_win_step(const float4* Wt, float* Gs, char* 
 }
 
 template <typename T, int NU, int G>
-__global__ void __launch_bounds__(kWinThreads, 3)
+__global__ void __launch_bounds__(kWinThreads, 4)
 msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ shapes,
                     const int64_t* __restrict__ lsi, const T* __restrict__ loc,
                     const T* __restrict__ aw, const T* __restrict__ gout,
@@ -614,8 +589,7 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
   static_assert(G == 8, "two rows x four queries are transpose-reduced over 8 lanes");
   using Raw = typename Unit<T>::Raw;
   constexpr int E = Unit<T>::E;
-  constexpr int DD = NU * G * E;   // head channels
-  using SM = WinSmem<T, 2, true, DD>;
+  using SM = WinSmem<T, 2, false, 0>;
   constexpr int NH = G / 4;
   constexpr int NS = 4;
   constexpr int LPL = (kWinMaxL * 4 + G - 1) / G;
@@ -632,7 +606,6 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
   const int qi = j & 3, h = j >> 2;
   char* s_grp = s_dyn + gi * SM::kGroupBytes;
   char* pts_buf = s_grp + SM::kPlanBytes;                       // two buffers of kPtsBytes
-  char* go_buf = pts_buf + 2 * SM::kPtsBytes;                   // 4 x D grad_out
   const float4* Wt = reinterpret_cast<const float4*>(s_grp);
   float* Gs = reinterpret_cast<float*>(s_grp);  // the dots G[t][qi] overwrite Wt[t][qi] step by step
   const unsigned* rowoff = reinterpret_cast<const unsigned*>(s_grp + 16 * kWinRows);
@@ -648,27 +621,10 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
     }
     return;
   }
-  // grad_out rows of a block: 4 x D*sizeof(T) bytes, 16-byte pieces over the 8 lanes
-  auto fetch_gout = [&](const WinUnit& w) {
-    constexpr int per_q = DD * (int)sizeof(T) / 16;   // 16-byte pieces per query: NU * G
-    const char* gb = reinterpret_cast<const char*>(
-        gout + (((size_t)w.b * d.Lq + w.q0 + gq) * d.M + w.m) * d.D);
-    const unsigned qstride = (unsigned)(d.M * d.D) * (unsigned)sizeof(T);
-#pragma unroll
-    for (int q = 0; q < kWinQ; ++q)
-      if (w.q0 + gq + q < d.Lq) {
-#pragma unroll
-        for (int k = 0; k < per_q / 8; ++k)
-          win_cp16(go_buf + (q * per_q + k * 8 + j) * 16, win_addr(gb, q * qstride + (k * 8 + j) * 16));
-      }
-  };
   int cur = 0;
-  WinFetch<T> fetch;
-  fetch.init(d, j);
   if (u < uend) {
     const WinUnit w = win_decode(u, nqc, d.M);
-    fetch.issue(loc, aw, d, w.b, w.m, w.q0 + gq, pts_buf);
-    fetch_gout(w);
+    win_fetch_points<T>(loc, aw, d, w.b, w.m, w.q0 + gq, pts_buf, j);
   }
   win_cp_commit();
   while (u < uend) {
@@ -677,43 +633,50 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
     const int nq = max(min(kWinQ, d.Lq - q0), 0);
     const bool have_q = qi < nq;
     const char* pts = pts_buf + cur * SM::kPtsBytes;
+    // grad_out of the 4 queries (this lane's channels): requested first, used
+    // after the window build, whose work covers their way from HBM
+    Raw gor[kWinQ][NU][4];
+    {
+      const char* gb = reinterpret_cast<const char*>(
+          gout + (((size_t)b * d.Lq + q0) * d.M + m) * d.D) + j * 16;
+      const unsigned qstride = (unsigned)(d.M * d.D) * (unsigned)sizeof(T);
+#pragma unroll
+      for (int q = 0; q < kWinQ; ++q)
+#pragma unroll
+        for (int uu = 0; uu < NU; ++uu) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) gor[q][uu][k] = Raw(0);
+          Unit<T>::ldg_keep(win_addr(gb, q * qstride) + uu * (G * 16), q < nq, gor[q][uu]);
+        }
+    }
     win_cp_wait_all();
     __syncwarp();
     int tb[LPL], rt, wmax;
     const bool ok = win_build<T, G>(pts, d, have_q, s_lvl, s_grp, j, lane & ~(G - 1), tb, rt, wmax);
-
-    // grad_out of the 4 queries: shared memory -> registers (lane's channels)
-    float2 go[kWinQ][NU][E / 2];
-#pragma unroll
-    for (int q = 0; q < kWinQ; ++q) {
-#pragma unroll
-      for (int uu = 0; uu < NU; ++uu) {
-        Raw raw[4];
-        const uint4 t4 = *reinterpret_cast<const uint4*>(go_buf + q * (DD * (int)sizeof(T)) + uu * (G * 16) + j * 16);
-        raw[0] = __builtin_bit_cast(Raw, t4.x); raw[1] = __builtin_bit_cast(Raw, t4.y);
-        raw[2] = __builtin_bit_cast(Raw, t4.z); raw[3] = __builtin_bit_cast(Raw, t4.w);
-        float t[E];
-        Unit<T>::unpack_raw(raw, t);
-#pragma unroll
-        for (int c = 0; c < E / 2; ++c)
-          go[q][uu][c] = q < nq ? make_float2(t[2 * c], t[2 * c + 1]) : make_float2(0.f, 0.f);
-      }
-    }
-    __syncwarp();
-    // next unit: points into the other buffer, grad_out into the one just drained
+    // next unit's points into the other buffer
     const int un = u + ustep;
     if (un < uend) {
       const WinUnit wn = win_decode(un, nqc, d.M);
-      fetch.issue(loc, aw, d, wn.b, wn.m, wn.q0 + gq, pts_buf + (cur ^ 1) * SM::kPtsBytes);
-      fetch_gout(wn);
+      win_fetch_points<T>(loc, aw, d, wn.b, wn.m, wn.q0 + gq, pts_buf + (cur ^ 1) * SM::kPtsBytes, j);
     }
     win_cp_commit();
+    float2 go[kWinQ][NU][E / 2];
+#pragma unroll
+    for (int q = 0; q < kWinQ; ++q)
+#pragma unroll
+      for (int uu = 0; uu < NU; ++uu) {
+        float t[E];
+        Unit<T>::unpack_raw(gor[q][uu], t);
+#pragma unroll
+        for (int c = 0; c < E / 2; ++c) go[q][uu][c] = make_float2(t[2 * c], t[2 * c + 1]);
+      }
 
     const size_t voff = ((size_t)b * d.S * d.M + m) * d.D;
     const char* vbb = reinterpret_cast<const char*>(value + voff) + j * 16;
     char* gvbb = reinterpret_cast<char*>(gvalue + voff + j * E);
 
     // NS rows in flight per lane
+    const int rl = (d.dbg & 8) ? 0 : rt;
     Raw buf[NS][NU][4];
 #pragma unroll
     for (int s = 0; s < NS; ++s)
@@ -721,19 +684,20 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
       for (int uu = 0; uu < NU; ++uu)
 #pragma unroll
         for (int k = 0; k < 4; ++k) buf[s][uu][k] = Raw(0);
+    const int rr = (d.dbg & 16) ? 0 : rt;   // rows whose grad_value reds are issued
     uint4 rc = *reinterpret_cast<const uint4*>(rowoff);
-    win_load_row<T, NU, G>(vbb, rc.x, 0 < rt, buf[0]);
-    win_load_row<T, NU, G>(vbb, rc.y, 1 < rt, buf[1]);
-    win_load_row<T, NU, G>(vbb, rc.z, 2 < rt, buf[2]);
-    win_load_row<T, NU, G>(vbb, rc.w, 3 < rt, buf[3]);
+    win_load_row<T, NU, G>(vbb, rc.x, 0 < rl, buf[0]);
+    win_load_row<T, NU, G>(vbb, rc.y, 1 < rl, buf[1]);
+    win_load_row<T, NU, G>(vbb, rc.z, 2 < rl, buf[2]);
+    win_load_row<T, NU, G>(vbb, rc.w, 3 < rl, buf[3]);
     for (int t = 0; t < wmax; t += NS) {
       const uint4 rn = *reinterpret_cast<const uint4*>(rowoff + t + NS);
-      bwd_win_step<T, NU, G>(Wt, Gs, gvbb, rc.x, rc.y, t, rt, j, buf[0], buf[1], go);
-      win_load_row<T, NU, G>(vbb, rn.x, t + NS + 0 < rt, buf[0]);
-      win_load_row<T, NU, G>(vbb, rn.y, t + NS + 1 < rt, buf[1]);
-      bwd_win_step<T, NU, G>(Wt, Gs, gvbb, rc.z, rc.w, t + 2, rt, j, buf[2], buf[3], go);
-      win_load_row<T, NU, G>(vbb, rn.z, t + NS + 2 < rt, buf[2]);
-      win_load_row<T, NU, G>(vbb, rn.w, t + NS + 3 < rt, buf[3]);
+      bwd_win_step<T, NU, G>(Wt, Gs, gvbb, rc.x, rc.y, t, rr, j, buf[0], buf[1], go);
+      win_load_row<T, NU, G>(vbb, rn.x, t + NS + 0 < rl, buf[0]);
+      win_load_row<T, NU, G>(vbb, rn.y, t + NS + 1 < rl, buf[1]);
+      bwd_win_step<T, NU, G>(Wt, Gs, gvbb, rc.z, rc.w, t + 2, rr, j, buf[2], buf[3], go);
+      win_load_row<T, NU, G>(vbb, rn.z, t + NS + 2 < rl, buf[2]);
+      win_load_row<T, NU, G>(vbb, rn.w, t + NS + 3 < rl, buf[3]);
       rc = rn;
     }
     __syncwarp();

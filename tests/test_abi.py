@@ -37,6 +37,16 @@ def test_abi_version_and_strings(lib):
     assert lib.msda_kernel_family(64, _lib.MSDA_F64, 0) == b"generic"
     assert lib.msda_kernel_family(30, _lib.MSDA_F32, 0) == b"generic"
     assert lib.msda_kernel_family(64, _lib.MSDA_F32, _lib.MSDA_FLAG_FORCE_GENERIC) == b"generic"
+    enc = (16, 1500, 8, 64, 4, 1500, 4)
+    dec = (64, 1500, 8, 64, 4, 100, 4)
+    assert lib.msda_kernel_choice(*enc, _lib.MSDA_F32, 0) == b"window"
+    assert lib.msda_kernel_choice(*enc, _lib.MSDA_BF16, 0) == b"window"
+    assert lib.msda_kernel_choice(*enc, _lib.MSDA_F32, _lib.MSDA_FLAG_NO_WINDOW) == b"fast"
+    assert lib.msda_kernel_choice(*dec, _lib.MSDA_F32, 0) == b"fast"           # short query list
+    assert lib.msda_kernel_choice(*dec, _lib.MSDA_F32, _lib.MSDA_FLAG_FORCE_WINDOW) == b"window"
+    assert lib.msda_kernel_choice(*enc, _lib.MSDA_F64, 0) == b"generic"
+    assert lib.msda_kernel_choice(16, 1500, 8, 64, 4, 1500, 8, _lib.MSDA_F32, 0) == b"fast"   # P != 4
+    assert lib.msda_kernel_choice(16, 1500, 8, 64, 4, 1500, 4, 7, 0) == b"invalid"
 
 
 def test_argument_validation_without_gpu(lib):

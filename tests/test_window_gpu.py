@@ -1,0 +1,167 @@
+"""GPU suite for the row-window kernels (csrc/msda_win.cuh) against the C oracle.
+
+The window path is taken per block of 4 consecutive queries whose packed per-level
+windows fit kWinCap rows; everything else in the same launch runs the per-tap body.
+These cases force the window kernels (MSDA_FLAG_FORCE_WINDOW) at sizes the oracle
+finishes in seconds and cover: locality (model-like locations), ragged query counts
+(Lq % 16 != 0, Lq < 4), 1..4 levels, both paddings, vertical coordinates != 0.5 on
+(1, W) maps, taps that fall off either end of a level, NaN locations, blocks that
+straddle a level boundary (fallback inside a window launch) and bf16.
+
+Tolerances as in tests/test_parity_gpu.py.
+"""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+import mfl_b200  # noqa: E402,F401
+from mfl_b200 import MultiScaleDeformableAttention as MSDA  # noqa: E402
+from mfl_b200 import _lib, synthetic  # noqa: E402
+
+DEV = "cuda"
+FWD_ABS_F32 = 1e-5
+GRAD_REL_F32 = 1e-4
+BF16_FWD_REL = 2.0 ** -7
+BF16_GRAD_REL = 2e-2
+WIN = _lib.MSDA_FLAG_FORCE_WINDOW
+
+
+def rel_err(a, b):
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    return (np.abs(a - b).max() / max(np.abs(b).max(), 1e-30)) if b.size else 0.0
+
+
+def run_cuda(inp, padding, flags):
+    v, s, l, loc, aw, go = (inp[k] for k in ("value", "shapes", "lsi", "loc", "aw", "grad_out"))
+    out = MSDA.ms_deform_attn_forward(v, s, l, loc, aw, 64, padding_mode=padding, flags=flags)
+    gv, gl, ga = MSDA.ms_deform_attn_backward(v, s, l, loc, aw, go, 64, padding_mode=padding, flags=flags)
+    torch.cuda.synchronize()
+    return [t.float().cpu().numpy() for t in (out, gv, gl, ga)]
+
+
+def run_oracle(oracle_c, inp, padding):
+    f = {k: (v.float() if v.is_floating_point() else v) for k, v in inp.items()}
+    args = [f[k] for k in ("value", "shapes", "lsi", "loc", "aw")]
+    out = oracle_c.forward(*args, padding)
+    gv, gl, ga = oracle_c.backward(*args, f["grad_out"], padding)
+    return out, gv, gl, ga
+
+
+def check_f32(got, want, smooth=None):
+    assert np.abs(got[0] - want[0]).max() <= FWD_ABS_F32
+    assert rel_err(got[1], want[1]) <= GRAD_REL_F32, "grad_value"
+    assert rel_err(got[3], want[3]) <= GRAD_REL_F32, "grad_attn_weight"
+    gl_g, gl_w = got[2], want[2]
+    if smooth is not None:
+        gl_g, gl_w = gl_g * smooth, gl_w * smooth
+    assert rel_err(gl_g, gl_w) <= GRAD_REL_F32, "grad_sampling_loc"
+
+
+def smooth_mask(inp, eps=1e-4):
+    """grad_sampling_loc jumps where a pixel coordinate crosses an integer; fp32 rounding of
+    loc*W-0.5 may differ by an ulp between two correct implementations (tests/test_fullsize_gpu.py)."""
+    loc = inp["loc"].double().cpu()
+    sh = inp["shapes"].cpu()
+    wh = torch.stack((sh[:, 1], sh[:, 0]), -1).double()[None, None, None, :, None, :]
+    pix = loc * wh - 0.5
+    return (((pix - pix.round()).abs() > eps) | (wh == 1)).all(-1, keepdim=True).numpy()
+
+
+CASES = [
+    # N, T (levels), M, D, enc (queries = tokens) or Lq
+    (2, [96, 48, 24, 12], 8, 64, None),      # encoder-like, Lq = 180 (not a multiple of 16)
+    (3, [50, 25], 4, 64, None),              # two levels, Lq = 75
+    (2, [40], 2, 64, None),                  # one level
+    (2, [33, 17, 9], 3, 64, None),           # three levels, odd sizes
+    (2, [64, 32, 16, 8], 8, 32, None),       # D = 32: one 16-byte unit per lane
+    (1, [20, 10, 5, 3], 2, 64, 3),           # fewer queries than one block
+    (2, [80, 40, 20, 10], 4, 64, 37),        # decoder-like random reference points (mostly fallback)
+]
+IDS = ["enc180", "L2", "L1", "L3odd", "D32", "Lq3", "dec37"]
+
+
+def make(case, dtype, seed, dist="model"):
+    N, T, M, D, Lq = case
+    enc = Lq is None
+    return synthetic.make_inputs(N, sum(T) if enc else Lq, M, D, 4, [(1, t) for t in T], dtype, DEV, seed=seed,
+                                 dist=dist, value="small" if dtype == torch.float32 else "normal", enc_ref=enc)
+
+
+@pytest.mark.parametrize("case", CASES, ids=IDS)
+@pytest.mark.parametrize("padding", ["zeros", "border"])
+def test_window_fp32_model_locations(oracle_c, case, padding):
+    inp = make(case, torch.float32, seed=11)
+    check_f32(run_cuda(inp, padding, WIN), run_oracle(oracle_c, inp, padding), smooth_mask(inp))
+
+
+@pytest.mark.parametrize("case", CASES[:4], ids=IDS[:4])
+@pytest.mark.parametrize("padding", ["zeros", "border"])
+def test_window_matches_per_tap_kernels(case, padding):
+    """Same launch arguments through both kernel families."""
+    inp = make(case, torch.float32, seed=12)
+    a = run_cuda(inp, padding, WIN)
+    b = run_cuda(inp, padding, _lib.MSDA_FLAG_NO_WINDOW)
+    assert np.abs(a[0] - b[0]).max() <= 2e-6
+    m = smooth_mask(inp)
+    for x, y, nm in ((a[1], b[1], "gv"), (a[2] * m, b[2] * m, "gl"), (a[3], b[3], "ga")):
+        assert rel_err(x, y) <= 2e-5, nm
+
+
+@pytest.mark.parametrize("padding", ["zeros", "border"])
+def test_window_vertical_coordinate_and_edges(oracle_c, padding):
+    """(1, W) maps with y != 0.5 (the single row is the low or the high row of the vertical
+    pair), x running off both ends, and a NaN location."""
+    inp = make(CASES[0], torch.float32, seed=13)
+    g = torch.Generator(device=DEV).manual_seed(5)
+    loc = inp["loc"].clone()
+    loc[..., 1] = torch.rand(loc.shape[:-1], device=DEV, generator=g) * 2.4 - 0.7      # h_im in (-1.2, 1.2)
+    loc[:, :8, :, :, :, 0] -= 0.02                                                      # off the left end
+    loc[:, -8:, :, :, :, 0] += 0.05                                                     # off the right end
+    loc[0, 17, 1, 2, 3, 0] = float("nan")
+    inp["loc"] = loc.contiguous()
+    got = run_cuda(inp, padding, WIN)
+    assert np.isfinite(got[0]).all()
+    ref = dict(inp)
+    if padding == "zeros":
+        # the oracle treats NaN like the reference: the gate fails, the point contributes nothing
+        want = run_oracle(oracle_c, ref, padding)
+        check_f32(got, want, smooth_mask(inp))
+        assert np.abs(got[2][0, 17, 1, 2, 3]).sum() == 0 and got[3][0, 17, 1, 2, 3] == 0
+    else:
+        ref["loc"] = torch.nan_to_num(inp["loc"], nan=-1.0)   # border: a NaN x clamps to column 0
+        want = run_oracle(oracle_c, ref, padding)
+        m = smooth_mask(ref)
+        m[0, 17, 1, 2, 3] = 0
+        check_f32(got, want, m)
+
+
+def test_window_uniform_locations_fall_back(oracle_c):
+    """Random locations: every block exceeds the window capacity and runs the per-tap body
+    inside the window launch."""
+    inp = make(CASES[0], torch.float32, seed=14, dist="uniform")
+    check_f32(run_cuda(inp, "zeros", WIN), run_oracle(oracle_c, inp, "zeros"), smooth_mask(inp))
+
+
+@pytest.mark.parametrize("case", [CASES[0], CASES[1]], ids=[IDS[0], IDS[1]])
+@pytest.mark.parametrize("padding", ["zeros", "border"])
+def test_window_bf16(oracle_c, case, padding):
+    inp = make(case, torch.bfloat16, seed=15)
+    got, want = run_cuda(inp, padding, WIN), run_oracle(oracle_c, inp, padding)
+    assert rel_err(got[0], want[0]) <= BF16_FWD_REL
+    for g_, w_, nm in zip(got[1:], want[1:], ("grad_value", "grad_loc", "grad_aw")):
+        assert rel_err(g_, w_) <= BF16_GRAD_REL, nm
+
+
+def test_window_default_heuristic_and_determinism():
+    """Lq >= 256 takes the window kernels by default; the forward is bitwise reproducible."""
+    inp = synthetic.make_inputs(2, 480, 8, 64, 4, [(1, 256), (1, 128), (1, 64), (1, 32)], torch.float32, DEV,
+                                seed=16, dist="model", enc_ref=True)
+    a = [inp[k] for k in ("value", "shapes", "lsi", "loc", "aw")]
+    o0 = MSDA.ms_deform_attn_forward(*a, 64)
+    o1 = MSDA.ms_deform_attn_forward(*a, 64, flags=WIN)
+    o2 = MSDA.ms_deform_attn_forward(*a, 64, flags=_lib.MSDA_FLAG_NO_WINDOW)
+    assert torch.equal(o0, o1)
+    assert float((o0 - o2).abs().max()) <= 2e-6 and not torch.equal(o0, o2)

@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--dtypes", default="f32,bf16")
     ap.add_argument("--iters", type=int, default=50)
     ap.add_argument("--flags", default="0,4")
+    ap.add_argument("--N", type=int, default=0, help="override the workload's batch size")
     ap.add_argument("--ring", type=int, default=4, help="distinct input sets rotated (1 = L2-resident inputs)")
     args = ap.parse_args()
     dev = torch.device("cuda", 0)
@@ -39,7 +40,7 @@ def main():
         for dist in args.dists.split(","):
             for dts in args.dtypes.split(","):
                 dtype = {"f32": torch.float32, "bf16": torch.bfloat16}[dts]
-                ring = [synthetic.make_workload(wl, dtype, dev, seed=1234 + r, dist=dist, value="normal")
+                ring = [synthetic.make_workload(wl, dtype, dev, seed=1234 + r, dist=dist, value="normal", N=args.N or None)
                         for r in range(args.ring)]
                 outs = {}
                 for fl in [int(x) for x in args.flags.split(",")]:
