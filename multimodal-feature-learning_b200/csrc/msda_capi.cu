@@ -3,6 +3,8 @@
 // Replaces the reference host launchers ms_deform_attn_cuda_forward/backward
 // (models/ops/src/cuda/ms_deform_attn_cuda.cu:20-153) and the D-dispatch table
 // ms_deformable_col2im_cuda (ms_deform_im2col_cuda.cuh:957-1328).
+#include <cstdlib>
+
 #include "../../include/msda_b200.h"
 #include "msda_fast.cuh"
 #include "msda_generic.cuh"
@@ -135,8 +137,13 @@ int win_grid(K kern, size_t smem, long long units, int* grid) {
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   if (e == cudaSuccess)
     e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (const char* cv = getenv("MSDA_DBG_CARVEOUT")) {   // experiment: shared-memory carveout in percent
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(cv));
+  }
   if (e == cudaSuccess)
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kWinThreads, smem);
+  if (const char* cv = getenv("MSDA_DBG_CTAS")) per_sm = atoi(cv) < per_sm ? atoi(cv) : per_sm;
   if (e != cudaSuccess) return cuda_fail(e);
   if (per_sm < 1) per_sm = 1;
   const long long warps = kWinThreads / 32;
