@@ -196,15 +196,43 @@ __device__ __forceinline__ bool win_stage_levels(const int64_t* __restrict__ sha
 // w + 2W, ... (W = warps in the grid), so at any moment the resident warps work
 // on neighbouring units -- the same few (b, m) slabs, which then stay in L2 --
 // exactly as a non-persistent launch would sweep them.
-struct WinUnit { int b, m, q0; };
+struct WinUnit {
+  int u, b, m, qc;                       // unit index and its (batch, head, 16-query chunk)
+  __device__ __forceinline__ int q0() const { return qc * (4 * kWinQ); }
+};
+// The stride W between a warp's units, split once into (chunks, heads, batches):
+// stepping a unit is then three adds with carry instead of two divisions.
+struct WinStride { int du, dq, dm, db; };
 
-__device__ __forceinline__ WinUnit win_decode(int u, int nqc, int M) {
+__device__ __forceinline__ WinUnit win_first_unit(int u, int nqc, int M) {
   WinUnit w;
   const int bm = u / nqc;
-  w.q0 = (u - bm * nqc) * (4 * kWinQ);
+  w.u = u;
+  w.qc = u - bm * nqc;
   w.b = bm / M;
   w.m = bm - w.b * M;
   return w;
+}
+__device__ __forceinline__ WinStride win_stride(int du, int nqc, int M) {
+  WinStride s;
+  const int t = du / nqc;
+  s.du = du;
+  s.dq = du - t * nqc;
+  s.db = t / M;
+  s.dm = t - s.db * M;
+  return s;
+}
+__device__ __forceinline__ WinUnit win_next_unit(const WinUnit& w, const WinStride& s, int nqc, int M) {
+  WinUnit n;
+  n.u = w.u + s.du;
+  int qc = w.qc + s.dq;
+  const int cq = qc >= nqc;
+  n.qc = qc - (cq ? nqc : 0);
+  int m = w.m + s.dm + cq;
+  const int cm = m >= M;
+  n.m = m - (cm ? M : 0);
+  n.b = w.b + s.db + cm;
+  return n;
 }
 
 // Shared memory of one group (block of 4 queries):
@@ -417,25 +445,21 @@ msda_fwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
   const float4* Wt = reinterpret_cast<const float4*>(s_grp);
   const unsigned* rowoff = reinterpret_cast<const unsigned*>(s_grp + 16 * kWinRows);
 
-  int u = blockIdx.x * (kWinThreads / 32) + (threadIdx.x >> 5);
+  const WinStride ust = win_stride(ustep, nqc, d.M);
+  WinUnit w = win_first_unit(blockIdx.x * (kWinThreads / 32) + (threadIdx.x >> 5), nqc, d.M);
   if (!one_d) {
-    for (; u < uend; u += ustep) {
-      const WinUnit w = win_decode(u, nqc, d.M);
-      const int q0 = w.q0 + gq;
+    for (; w.u < uend; w = win_next_unit(w, ust, nqc, d.M)) {
+      const int q0 = w.q0() + gq;
       fwd_body<T, NU, G, 4>(value, loc, aw, out, d, w.b, w.m, q0, min(q0 + kWinQ, d.Lq), 1, s_lvl,
                             reinterpret_cast<TapMeta<4>*>(s_grp));
       __syncwarp();
     }
     return;
   }
-  if (u < uend) {
-    const WinUnit w = win_decode(u, nqc, d.M);
-    win_fetch_points<T>(loc, aw, d, w.b, w.m, w.q0 + gq, pts, j);
-  }
+  if (w.u < uend) win_fetch_points<T>(loc, aw, d, w.b, w.m, w.q0() + gq, pts, j);
   win_cp_commit();
-  while (u < uend) {
-    const WinUnit w = win_decode(u, nqc, d.M);
-    const int b = w.b, m = w.m, q0 = w.q0 + gq;
+  while (w.u < uend) {
+    const int b = w.b, m = w.m, q0 = w.q0() + gq;
     const int nq = max(min(kWinQ, d.Lq - q0), 0);
     const bool have_q = (j & 3) < nq;
     win_cp_wait_all();
@@ -444,11 +468,8 @@ msda_fwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
     const bool ok = win_build<T, G>(pts, d, have_q, s_lvl, s_grp, j, lane & ~(G - 1), tb, rt, wmax);
     // win_build ends with a warp barrier: the staged points are consumed, the
     // buffer can take the next unit's
-    const int un = u + ustep;
-    if (un < uend) {
-      const WinUnit wn = win_decode(un, nqc, d.M);
-      win_fetch_points<T>(loc, aw, d, wn.b, wn.m, wn.q0 + gq, pts, j);
-    }
+    const WinUnit wn = win_next_unit(w, ust, nqc, d.M);
+    if (wn.u < uend) win_fetch_points<T>(loc, aw, d, wn.b, wn.m, wn.q0() + gq, pts, j);
     win_cp_commit();
 
     const char* vbb =
@@ -526,7 +547,7 @@ msda_fwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
                             reinterpret_cast<TapMeta<2>*>(s_grp));
     }
     __syncwarp();
-    u = un;
+    w = wn;
   }
 }
 
@@ -619,11 +640,11 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
   float* Gs = reinterpret_cast<float*>(s_grp);  // the dots G[t][qi] overwrite Wt[t][qi] step by step
   const unsigned* rowoff = reinterpret_cast<const unsigned*>(s_grp + 16 * kWinRows);
 
-  int u = blockIdx.x * (kWinThreads / 32) + (threadIdx.x >> 5);
+  const WinStride ust = win_stride(ustep, nqc, d.M);
+  WinUnit w = win_first_unit(blockIdx.x * (kWinThreads / 32) + (threadIdx.x >> 5), nqc, d.M);
   if (!one_d) {
-    for (; u < uend; u += ustep) {
-      const WinUnit w = win_decode(u, nqc, d.M);
-      const int q0 = w.q0 + gq;
+    for (; w.u < uend; w = win_next_unit(w, ust, nqc, d.M)) {
+      const int q0 = w.q0() + gq;
       bwd_body<T, NU, G, 4>(value, loc, aw, gout, gvalue, gloc, gaw, d, w.b, w.m, q0,
                             min(q0 + kWinQ, d.Lq), 1, s_lvl, reinterpret_cast<TapMeta<4>*>(s_grp));
       __syncwarp();
@@ -631,14 +652,10 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
     return;
   }
   int cur = 0;
-  if (u < uend) {
-    const WinUnit w = win_decode(u, nqc, d.M);
-    win_fetch_points<T>(loc, aw, d, w.b, w.m, w.q0 + gq, pts_buf, j);
-  }
+  if (w.u < uend) win_fetch_points<T>(loc, aw, d, w.b, w.m, w.q0() + gq, pts_buf, j);
   win_cp_commit();
-  while (u < uend) {
-    const WinUnit w = win_decode(u, nqc, d.M);
-    const int b = w.b, m = w.m, q0 = w.q0 + gq;
+  while (w.u < uend) {
+    const int b = w.b, m = w.m, q0 = w.q0() + gq;
     const int nq = max(min(kWinQ, d.Lq - q0), 0);
     const bool have_q = qi < nq;
     const char* pts = pts_buf + cur * SM::kPtsBytes;
@@ -663,11 +680,9 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
     int tb[LPL], rt, wmax;
     const bool ok = win_build<T, G>(pts, d, have_q, s_lvl, s_grp, j, lane & ~(G - 1), tb, rt, wmax);
     // next unit's points into the other buffer
-    const int un = u + ustep;
-    if (un < uend) {
-      const WinUnit wn = win_decode(un, nqc, d.M);
-      win_fetch_points<T>(loc, aw, d, wn.b, wn.m, wn.q0 + gq, pts_buf + (cur ^ 1) * SM::kPtsBytes, j);
-    }
+    const WinUnit wn = win_next_unit(w, ust, nqc, d.M);
+    if (wn.u < uend)
+      win_fetch_points<T>(loc, aw, d, wn.b, wn.m, wn.q0() + gq, pts_buf + (cur ^ 1) * SM::kPtsBytes, j);
     win_cp_commit();
     float2 go[kWinQ][NU][E / 2];
 #pragma unroll
@@ -748,7 +763,7 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
     }
     __syncwarp();
     cur ^= 1;
-    u = un;
+    w = wn;
   }
 }
 
