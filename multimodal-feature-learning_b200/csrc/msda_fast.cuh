@@ -116,6 +116,10 @@ template <> struct Unit<float> {
                  : "+f"(v[0]), "+f"(v[1]), "+f"(v[2]), "+f"(v[3])
                  : "l"(p), "r"((int)pred));
   }
+  static __device__ __forceinline__ void ldg_raw(const char* p, float (&v)[4]) {
+    const float4 t = __ldg(reinterpret_cast<const float4*>(p));
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  }
   static __device__ __forceinline__ void unpack_raw(const float (&r)[4], float (&v)[4]) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) v[i] = r[i];
@@ -156,6 +160,10 @@ template <> struct Unit<__nv_bfloat16> {
                  "@p ld.global.nc.v4.b32 {%0, %1, %2, %3}, [%4];\n\t}"
                  : "+r"(w[0]), "+r"(w[1]), "+r"(w[2]), "+r"(w[3])
                  : "l"(p), "r"((int)pred));
+  }
+  static __device__ __forceinline__ void ldg_raw(const char* p, uint32_t (&w)[4]) {
+    const uint4 t = __ldg(reinterpret_cast<const uint4*>(p));
+    w[0] = t.x; w[1] = t.y; w[2] = t.z; w[3] = t.w;
   }
   static __device__ __forceinline__ void unpack_raw(const uint32_t (&w)[4], float (&v)[8]) {
     unpack(w, v);

@@ -413,6 +413,17 @@ __device__ __forceinline__ void win_load_row(const char* vbb, unsigned off, bool
   for (int u = 0; u < NU; ++u) Unit<T>::ldg_keep(p + u * (G * 16), pred, buf[u]);
 }
 
+// The first kWinStages rows of a plan: rowoff always holds a valid row there
+// (win_build pads with the block's last row, or row 0 of the slab), so these
+// loads need no predicate and the buffers no initial value.
+template <typename T, int NU, int G>
+__device__ __forceinline__ void win_load_row_first(const char* vbb, unsigned off,
+                                                   typename Unit<T>::Raw (&buf)[NU][4]) {
+  const char* p = win_addr(vbb, off);
+#pragma unroll
+  for (int u = 0; u < NU; ++u) Unit<T>::ldg_raw(p + u * (G * 16), buf[u]);
+}
+
 constexpr int kWinStages = 4;   // value rows in flight per lane (8 measured the same: 53.7 us at ENC)
 
 // ------------------------------- forward ------------------------------------
@@ -485,12 +496,6 @@ msda_fwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
     // NS rows in flight per lane: row t+NS+s is requested as soon as row t+s is consumed
     const int rl = (d.dbg & 8) ? 0 : rt;
     Raw buf[NS][NU][4];
-#pragma unroll
-    for (int s = 0; s < NS; ++s)
-#pragma unroll
-      for (int uu = 0; uu < NU; ++uu)
-#pragma unroll
-        for (int k = 0; k < 4; ++k) buf[s][uu][k] = Raw(0);
     {
       unsigned ro[NS];
 #pragma unroll
@@ -499,7 +504,7 @@ msda_fwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
         ro[s] = r4.x; ro[s + 1] = r4.y; ro[s + 2] = r4.z; ro[s + 3] = r4.w;
       }
 #pragma unroll
-      for (int s = 0; s < NS; ++s) win_load_row<T, NU, G>(vbb, ro[s], s < rl, buf[s]);
+      for (int s = 0; s < NS; ++s) win_load_row_first<T, NU, G>(vbb, ro[s], buf[s]);
     }
     for (int t = 0; t < wmax; t += NS) {
       unsigned ro[NS];
@@ -702,18 +707,12 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
     // NS rows in flight per lane
     const int rl = (d.dbg & 8) ? 0 : rt;
     Raw buf[NS][NU][4];
-#pragma unroll
-    for (int s = 0; s < NS; ++s)
-#pragma unroll
-      for (int uu = 0; uu < NU; ++uu)
-#pragma unroll
-        for (int k = 0; k < 4; ++k) buf[s][uu][k] = Raw(0);
     const int rr = (d.dbg & 16) ? 0 : rt;   // rows whose grad_value reds are issued
     uint4 rc = *reinterpret_cast<const uint4*>(rowoff);
-    win_load_row<T, NU, G>(vbb, rc.x, 0 < rl, buf[0]);
-    win_load_row<T, NU, G>(vbb, rc.y, 1 < rl, buf[1]);
-    win_load_row<T, NU, G>(vbb, rc.z, 2 < rl, buf[2]);
-    win_load_row<T, NU, G>(vbb, rc.w, 3 < rl, buf[3]);
+    win_load_row_first<T, NU, G>(vbb, rc.x, buf[0]);
+    win_load_row_first<T, NU, G>(vbb, rc.y, buf[1]);
+    win_load_row_first<T, NU, G>(vbb, rc.z, buf[2]);
+    win_load_row_first<T, NU, G>(vbb, rc.w, buf[3]);
     for (int t = 0; t < wmax; t += NS) {
       const uint4 rn = *reinterpret_cast<const uint4*>(rowoff + t + NS);
       bwd_win_step<T, NU, G>(Wt, Gs, gvbb, rc.x, rc.y, t, rr, j, buf[0], buf[1], go);
