@@ -14,6 +14,13 @@ WORKLOADS = {
     "CPU": dict(N=2, Lq=100, T=[300, 150, 75, 38], M=8, D=64, P=4, enc=False),
     "ENC": dict(N=16, Lq=None, T=[800, 400, 200, 100], M=8, D=64, P=4, enc=True),
     "DEC": dict(N=64, Lq=100, T=[800, 400, 200, 100], M=8, D=64, P=4, enc=False),
+    # the four calls of one multimodal encoder layer
+    # (models/deformable/multimodal_deformable_transformer.py:256-271): video and audio
+    # self-attention, then audio tokens over the video memory and video tokens over the audio memory
+    "MM_VV": dict(N=16, Lq=None, T=[640, 320, 160, 80], M=8, D=64, P=4, enc=True),
+    "MM_AA": dict(N=16, Lq=None, T=[160, 80, 40, 20], M=8, D=64, P=4, enc=True),
+    "MM_AV": dict(N=16, Lq=None, T=[640, 320, 160, 80], M=8, D=64, P=4, enc=True, Tq=[160, 80, 40, 20]),
+    "MM_VA": dict(N=16, Lq=None, T=[160, 80, 40, 20], M=8, D=64, P=4, enc=True, Tq=[640, 320, 160, 80]),
 }
 
 
@@ -40,12 +47,15 @@ def encoder_reference_points(T, device):
 
 
 def make_inputs(N, Lq, M, D, P, shapes_hw, dtype=torch.float32, device="cuda", seed=1234,
-                dist="uniform", value="small", enc_ref=False, requires_grad=False):
+                dist="uniform", value="small", enc_ref=False, requires_grad=False, query_T=None):
     """dist: 'uniform'  loc ~ U[0,1)^2 (models/ops/test.py:34)
              'model'    loc_x = ref + (bias[m,p] + 0.5*N(0,1)) / W_l   (a freshly initialised module)
              'interior' every tap inside the map (zeros == border)
              'spill'    loc ~ U[-0.25, 1.25) (exercises the gate / clamping)
        value: 'small' ~ U[0,1)*0.01 (test.py:33), 'normal' ~ N(0,1)
+       enc_ref: the queries are the tokens of a multi-level sequence (of the value's own
+       levels, or of `query_T` when the queries come from the other modality) and carry the
+       encoder's reference points.
        For maps with H == 1 the y coordinate is the constant 0.5 the module stacks on."""
     gen = torch.Generator(device=device).manual_seed(seed)
     shapes, lsi, S = level_tensors(shapes_hw, device)
@@ -56,7 +66,7 @@ def make_inputs(N, Lq, M, D, P, shapes_hw, dtype=torch.float32, device="cuda", s
     else:
         val = torch.randn(N, S, M, D, **f32)
     if enc_ref:
-        ref = encoder_reference_points([int(w) for _, w in shapes_hw], device)[None, :].expand(N, -1)
+        ref = encoder_reference_points(query_T or [int(w) for _, w in shapes_hw], device)[None, :].expand(N, -1)
         assert ref.shape[1] == Lq
     else:
         ref = torch.rand(N, Lq, **f32)
@@ -93,9 +103,9 @@ def make_workload(name, dtype=torch.float32, device="cuda", seed=1234, dist="mod
                   N=None):
     w = WORKLOADS[name]
     T = w["T"]
-    Lq = w["Lq"] if w["Lq"] is not None else sum(T)
+    Lq = w["Lq"] if w["Lq"] is not None else sum(w.get("Tq", T))
     return make_inputs(N or w["N"], Lq, w["M"], w["D"], w["P"], [(1, t) for t in T], dtype, device,
-                       seed, dist, value, enc_ref=w["enc"])
+                       seed, dist, value, enc_ref=w["enc"], query_T=w.get("Tq"))
 
 
 def algorithmic_bytes(N, S, Lq, M, D, L, P, elem_bytes):

@@ -56,6 +56,24 @@ def test_fullsize_fp32_vs_torch_port_on_gpu(workload, dist, padding):
     assert rel(got[2] * ok, want[2] * ok) <= 1e-4                  # grad_sampling_loc (x and y)
 
 
+@pytest.mark.parametrize("workload", ["MM_VV", "MM_AA", "MM_AV", "MM_VA"])
+@pytest.mark.parametrize("padding", ["zeros", "border"])
+def test_multimodal_layer_calls_fp32_vs_torch_port_on_gpu(workload, padding):
+    """The four op calls of one multimodal encoder layer
+    (models/deformable/multimodal_deformable_transformer.py:256-271): queries of one
+    modality (1200 video / 300 audio tokens) over the memory of the same or the other one."""
+    inp = synthetic.make_workload(workload, torch.float32, DEV, seed=44, dist="model", value="small")
+    w = synthetic.WORKLOADS[workload]
+    assert inp["loc"].shape[1] == sum(w.get("Tq", w["T"])) and inp["value"].shape[1] == sum(w["T"])
+    got = _grads(lambda v, loc, aw: ms_deform_attn(v, inp["shapes"], inp["lsi"], loc, aw, 64, padding), inp)
+    want = _grads(lambda v, loc, aw: ms_deform_attn_core_pytorch(v, inp["shapes"], loc, aw, padding), inp)
+    assert float((got[0] - want[0]).abs().max()) <= 1e-5
+    assert rel(got[1], want[1]) <= 1e-4
+    assert rel(got[3], want[3]) <= 1e-4
+    ok = _smooth_points(inp)
+    assert rel(got[2] * ok, want[2] * ok) <= 1e-4
+
+
 @pytest.mark.parametrize("workload", ["ENC", "DEC"])
 def test_fullsize_bf16_vs_fp32_kernel_on_rounded_inputs(workload):
     inp = synthetic.make_workload(workload, torch.bfloat16, DEV, seed=43, dist="model", value="normal")

@@ -1,0 +1,225 @@
+#!/usr/bin/env python
+"""BASELINE.json configs[4]: the data-parallel training step around the op.
+
+A compact deformable encoder-decoder of the reference's size and layer recipe
+(models/deformable/unimodal_deformable_transformer.py:189-250 encoder layer,
+:298-374 decoder layer; 6 + 6 layers, d_model 512, ffn 2048, 8 heads, 4 levels,
+4 points, 100 event queries, T = [800, 400, 200, 100]) whose deformable attention
+is this repo's MSDeformAttn module, i.e. the sm_100a kernels behind the C-ABI.
+It exists to time the op in the step it serves and the 1 -> N GPU scaling of that
+step; it is a measurement harness, not a model zoo: no captioning heads, no
+matcher, no dataset.  Per SURVEY.md section 8(d): synthetic features, per-GPU batch 16
+(weak scaling), loss = mean of the decoder outputs squared, AdamW 1e-4, gradient clip
+0.1, DistributedDataParallel over NCCL (one gradient all-reduce per step, bucketed
+and overlapped with the backward).
+
+  python tools/train_step.py [--steps 20] [--warmup 5] [--batch 16] [--layers 6]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+      --master-port P tools/train_step.py --steps 20
+
+Prints one JSON line on rank 0: samples/s over all ranks (device-timed, max over
+ranks) and the share of the step's GPU time spent inside the op's kernels (torch
+profiler kernel records of one extra, untimed step).  fp32 like the reference (its op
+dispatches fp32/fp64 only and the training script has no autocast); the modules'
+`shapes.sum() == Len_in` assertion, a host sync per call in the reference
+(ms_deform_attn.py:93), is switched off after the first step.
+"""
+import argparse
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+import torch.nn.functional as F
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import mfl_b200  # noqa: E402,F401
+from mfl_b200 import synthetic  # noqa: E402
+from mfl_b200.modules import MSDeformAttn  # noqa: E402
+
+
+class EncoderLayer(nn.Module):
+    """post-norm: x = LN(x + attn(x + pos)); x = LN(x + ffn(x))  (…transformer.py:228-250)"""
+
+    def __init__(self, C, ffn, M, L, P):
+        super().__init__()
+        self.self_attn = MSDeformAttn(C, L, M, P)
+        self.norm1 = nn.LayerNorm(C)
+        self.linear1 = nn.Linear(C, ffn)
+        self.linear2 = nn.Linear(ffn, C)
+        self.norm2 = nn.LayerNorm(C)
+
+    def forward(self, x, pos, ref, T, lsi):
+        x = self.norm1(x + self.self_attn(x + pos, ref, x, T, lsi))
+        return self.norm2(x + self.linear2(F.relu(self.linear1(x))))
+
+
+class DecoderLayer(nn.Module):
+    """query self-attention (nn.MultiheadAttention), deformable cross-attention over the
+    encoder memory, ffn; post-norm  (…transformer.py:342-374)"""
+
+    def __init__(self, C, ffn, M, L, P):
+        super().__init__()
+        self.cross_attn = MSDeformAttn(C, L, M, P)
+        self.norm1 = nn.LayerNorm(C)
+        self.self_attn = nn.MultiheadAttention(C, M, batch_first=True)
+        self.norm2 = nn.LayerNorm(C)
+        self.linear1 = nn.Linear(C, ffn)
+        self.linear2 = nn.Linear(ffn, C)
+        self.norm3 = nn.LayerNorm(C)
+
+    def forward(self, tgt, qpos, ref, mem, T, lsi):
+        q = tgt + qpos
+        tgt = self.norm2(tgt + self.self_attn(q, q, tgt, need_weights=False)[0])
+        tgt = self.norm1(tgt + self.cross_attn(tgt + qpos, ref, mem, T, lsi))
+        return self.norm3(tgt + self.linear2(F.relu(self.linear1(tgt))))
+
+
+class DeformableEncoderDecoder(nn.Module):
+    def __init__(self, C=512, ffn=2048, M=8, L=4, P=4, layers=6, queries=100):
+        super().__init__()
+        self.encoder = nn.ModuleList(EncoderLayer(C, ffn, M, L, P) for _ in range(layers))
+        self.decoder = nn.ModuleList(DecoderLayer(C, ffn, M, L, P) for _ in range(layers))
+        self.level_embed = nn.Parameter(torch.randn(L, C))
+        self.query_embed = nn.Embedding(queries, 2 * C)
+        self.reference_points = nn.Linear(C, 1)
+        self.L = L
+
+    def forward(self, src, pos, enc_ref, T, lsi):
+        N = src.shape[0]
+        sizes = [int(t) for t in T.tolist()] if not hasattr(self, "_sizes") else self._sizes
+        self._sizes = sizes
+        lvl = torch.cat([self.level_embed[l].expand(t, -1) for l, t in enumerate(sizes)])
+        pos = pos + lvl[None]
+        x = src
+        for layer in self.encoder:
+            x = layer(x, pos, enc_ref, T, lsi)
+        qpos, tgt = self.query_embed.weight.chunk(2, -1)
+        qpos = qpos[None].expand(N, -1, -1)
+        tgt = tgt[None].expand(N, -1, -1)
+        ref = self.reference_points(qpos).sigmoid()[:, :, None, :].expand(-1, -1, self.L, -1)
+        for layer in self.decoder:
+            tgt = layer(tgt, qpos, ref, x, T, lsi)
+        return tgt
+
+
+def op_share(step_fn):
+    """Share of one step's GPU time spent in this repo's kernels (names msda_*), from the
+    torch profiler's kernel records; None if the profiler is unavailable on the box."""
+    try:
+        from torch.profiler import ProfilerActivity, profile
+        with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+            step_fn()
+            torch.cuda.synchronize()
+        ours = total = 0.0
+        launches = 0
+        for e in prof.events():
+            if e.device_type == torch.autograd.DeviceType.CUDA:
+                t = float(e.device_time_total or 0.0)
+                total += t
+                if "msda_" in e.name:
+                    ours += t
+                    launches += 1
+        return (ours / total if total > 0 else None), ours, total, launches
+    except Exception as exc:  # noqa: BLE001
+        print("profiler unavailable: %r" % (exc,), file=sys.stderr)
+        return None, None, None, None
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--batch", type=int, default=16, help="per-GPU batch (weak scaling)")
+    ap.add_argument("--layers", type=int, default=6)
+    ap.add_argument("--no-tf32", action="store_true",
+                    help="full-fp32 GEMMs (default: TF32 matmuls, as in the reference's torch 1.11 image)")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("tools/train_step.py needs a CUDA device: the op has no CPU path")
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    torch.backends.cuda.matmul.allow_tf32 = not args.no_tf32
+    torch.backends.cudnn.allow_tf32 = not args.no_tf32
+    w = synthetic.WORKLOADS["ENC"]
+    T_list, C = w["T"], w["M"] * w["D"]
+    torch.manual_seed(1234)                                  # same initial weights on every rank
+    model = DeformableEncoderDecoder(C, 2048, w["M"], len(T_list), w["P"], args.layers, 100).to(dev)
+    n_params = sum(p.numel() for p in model.parameters())
+    net = model
+    if world > 1:
+        net = nn.parallel.DistributedDataParallel(model, device_ids=[local], gradient_as_bucket_view=True)
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-4, weight_decay=1e-4, fused=True)
+
+    gen = torch.Generator(device=dev).manual_seed(99 + rank)  # each rank its own shard of videos
+    S = sum(T_list)
+    src = torch.randn(args.batch, S, C, device=dev, generator=gen)
+    pos = torch.randn(args.batch, S, C, device=dev, generator=gen) * 0.1
+    T = torch.tensor(T_list, dtype=torch.long, device=dev)
+    lsi = torch.cat((T.new_zeros(1), T.cumsum(0)[:-1]))
+    enc_ref = synthetic.encoder_reference_points(T_list, dev)[None, :, None, None].expand(
+        args.batch, -1, len(T_list), 1).contiguous()
+
+    def step():
+        opt.zero_grad(set_to_none=True)
+        out = net(src, pos, enc_ref, T, lsi)
+        loss = out.float().pow(2).mean()
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(model.parameters(), 0.1)
+        opt.step()
+        return loss
+
+    step()                                                   # checks the level sizes once
+    for mod in model.modules():
+        if isinstance(mod, MSDeformAttn):
+            mod.check_input_lengths = False
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        loss = step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_step = float(ms) / args.steps
+    share = op_share(step) if rank == 0 else None
+    if rank == 0:
+        print(json.dumps({
+            "metric": "deformable encoder-decoder training step, samples/s", "value": args.batch * world / ms_step * 1e3,
+            "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_step, "scaling": "weak", "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "configs[4]: %d+%d layers, d_model %d, ffn 2048, T=%s, 100 queries, "
+                                   "batch %d per GPU, AdamW, clip 0.1, %s GEMMs%s" % (
+                                       args.layers, args.layers, C, T_list, args.batch,
+                                       "fp32" if args.no_tf32 else "tf32",
+                                       ", DDP/NCCL" if world > 1 else ""),
+                       "params": n_params},
+            "loss": float(loss.detach()),
+            "op_share_of_gpu_time": share[0], "op_us_per_step": share[1], "gpu_us_per_step": share[2],
+            "op_launches_per_step": share[3],
+        }), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
