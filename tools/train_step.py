@@ -200,7 +200,10 @@ def main():
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_step = float(ms) / args.steps
-    share = op_share(step) if rank == 0 else None
+    if rank == 0:
+        share = op_share(step)
+    else:
+        step()          # the profiled step still all-reduces gradients: every rank takes part
     if rank == 0:
         print(json.dumps({
             "metric": "deformable encoder-decoder training step, samples/s", "value": args.batch * world / ms_step * 1e3,
