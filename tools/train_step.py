@@ -136,9 +136,21 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--batch", type=int, default=16, help="per-GPU batch (weak scaling)")
     ap.add_argument("--layers", type=int, default=6)
+    ap.add_argument("--cuda-graph", action="store_true",
+                    help="capture forward + backward + gradient all-reduce + clip + AdamW in one CUDA graph and "
+                         "replay it per step (the op enqueues on the capturing stream, allocates nothing itself)")
+    ap.add_argument("--sync", default="flat", choices=["flat", "ddp"],
+                    help="gradient exchange at N > 1: 'flat' = every .grad is a view of one 158 MB buffer, one NCCL "
+                         "all-reduce (avg) after the backward, no autograd hooks; 'ddp' = DistributedDataParallel "
+                         "(bucketed, overlapped with the backward, ~3 ms more host work per step)")
+    ap.add_argument("--bucket-mb", type=int, default=25, help="DDP gradient bucket size")
+    ap.add_argument("--static-graph", action="store_true", help="DDP static_graph=True")
+    ap.add_argument("--bf16-grads", action="store_true", help="all-reduce gradients in bf16 (DDP comm hook)")
     ap.add_argument("--no-tf32", action="store_true",
                     help="full-fp32 GEMMs (default: TF32 matmuls, as in the reference's torch 1.11 image)")
     args = ap.parse_args()
+    if args.cuda_graph and args.sync == "ddp":
+        raise SystemExit("--cuda-graph needs --sync flat (DDP's reducer waits on the host inside the backward)")
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -149,6 +161,8 @@ def main():
     torch.cuda.set_device(dev)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if args.cuda_graph:
+            os.environ["TORCH_NCCL_ASYNC_ERROR_HANDLING"] = "0"   # its watchdog polls events: illegal in capture
         dist.init_process_group("nccl", device_id=dev)
 
     torch.backends.cuda.matmul.allow_tf32 = not args.no_tf32
@@ -159,9 +173,24 @@ def main():
     model = DeformableEncoderDecoder(C, 2048, w["M"], len(T_list), w["P"], args.layers, 100).to(dev)
     n_params = sum(p.numel() for p in model.parameters())
     net = model
-    if world > 1:
-        net = nn.parallel.DistributedDataParallel(model, device_ids=[local], gradient_as_bucket_view=True)
-    opt = torch.optim.AdamW(model.parameters(), lr=1e-4, weight_decay=1e-4, fused=True)
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    flat = None
+    if world > 1 and args.sync == "ddp":
+        with torch.cuda.stream(side if args.cuda_graph else torch.cuda.current_stream()):
+            net = nn.parallel.DistributedDataParallel(model, device_ids=[local], gradient_as_bucket_view=True,
+                                                      bucket_cap_mb=args.bucket_mb, static_graph=args.static_graph)
+        if args.bf16_grads:
+            from torch.distributed.algorithms.ddp_comm_hooks import default_hooks
+            net.register_comm_hook(None, default_hooks.bf16_compress_hook)
+    elif world > 1:
+        flat = torch.zeros(n_params, device=dev)
+        o = 0
+        for p_ in model.parameters():
+            p_.grad = flat[o:o + p_.numel()].view_as(p_)
+            o += p_.numel()
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-4, weight_decay=1e-4, fused=True,
+                            capturable=args.cuda_graph)
 
     gen = torch.Generator(device=dev).manual_seed(99 + rank)  # each rank its own shard of videos
     S = sum(T_list)
@@ -172,19 +201,50 @@ def main():
     enc_ref = synthetic.encoder_reference_points(T_list, dev)[None, :, None, None].expand(
         args.batch, -1, len(T_list), 1).contiguous()
 
-    def step():
-        opt.zero_grad(set_to_none=True)
+    def eager_step():
+        if flat is None:
+            opt.zero_grad(set_to_none=True)
+        else:
+            flat.zero_()
         out = net(src, pos, enc_ref, T, lsi)
         loss = out.float().pow(2).mean()
         loss.backward()
-        torch.nn.utils.clip_grad_norm_(model.parameters(), 0.1)
+        if flat is not None:
+            dist.all_reduce(flat, op=dist.ReduceOp.AVG)
+        torch.nn.utils.clip_grad_norm_(model.parameters(), 0.1, foreach=True)
         opt.step()
         return loss
 
-    step()                                                   # checks the level sizes once
+    step = eager_step
+    eager_step()                                             # checks the level sizes once
     for mod in model.modules():
         if isinstance(mod, MSDeformAttn):
             mod.check_input_lengths = False
+    if args.cuda_graph:
+        # warm up on a side stream (DDP wants 11 iterations before a capture), then record one step
+        torch.cuda.synchronize()
+        with torch.cuda.stream(side):
+            for _ in range(11):
+                eager_step()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        if flat is None:
+            opt.zero_grad(set_to_none=True)
+        with torch.cuda.graph(graph):
+            if flat is not None:
+                flat.zero_()
+            out = net(src, pos, enc_ref, T, lsi)
+            graph_loss = out.float().pow(2).mean()
+            graph_loss.backward()
+            if flat is not None:
+                dist.all_reduce(flat, op=dist.ReduceOp.AVG)
+            torch.nn.utils.clip_grad_norm_(model.parameters(), 0.1, foreach=True)
+            opt.step()
+
+        def step():
+            graph.replay()
+            return graph_loss
     for _ in range(args.warmup):
         step()
     torch.cuda.synchronize()
@@ -210,15 +270,26 @@ def main():
             "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "scaling": "weak", "dtype": "f32", "data": "synthetic",
             "config": {"workload": "configs[4]: %d+%d layers, d_model %d, ffn 2048, T=%s, 100 queries, "
-                                   "batch %d per GPU, AdamW, clip 0.1, %s GEMMs%s" % (
+                                   "batch %d per GPU, AdamW, clip 0.1, %s GEMMs%s%s" % (
                                        args.layers, args.layers, C, T_list, args.batch,
                                        "fp32" if args.no_tf32 else "tf32",
-                                       ", DDP/NCCL" if world > 1 else ""),
+                                       ", whole step replayed as one CUDA graph" if args.cuda_graph else "",
+                                       ("" if world == 1 else ", one flat NCCL all-reduce of %.1f MB" % (n_params * 4 / 1e6)
+                                        if flat is not None else
+                                        ", DDP/NCCL bucket %d MB%s%s" % (args.bucket_mb, ", static graph" if args.static_graph else "",
+                                                                         ", bf16 gradient all-reduce" if args.bf16_grads else ""))),
                        "params": n_params},
             "loss": float(loss.detach()),
             "op_share_of_gpu_time": share[0], "op_us_per_step": share[1], "gpu_us_per_step": share[2],
             "op_launches_per_step": share[3],
         }), flush=True)
+    if world > 1 and args.cuda_graph:
+        # tearing down a communicator whose collectives live in a captured graph can block:
+        # everything is measured and printed, leave without the teardown
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
