@@ -3,7 +3,6 @@
 // Replaces the reference host launchers ms_deform_attn_cuda_forward/backward
 // (models/ops/src/cuda/ms_deform_attn_cuda.cu:20-153) and the D-dispatch table
 // ms_deformable_col2im_cuda (ms_deform_im2col_cuda.cuh:957-1328).
-#include <cstdlib>
 
 #include "../../include/msda_b200.h"
 #include "msda_fast.cuh"
@@ -66,7 +65,6 @@ inline Dims make_dims(int64_t N, int64_t S, int64_t M, int64_t D, int64_t L, int
   Dims d;
   d.N = (int)N; d.S = (int)S; d.M = (int)M; d.D = (int)D; d.L = (int)L; d.Lq = (int)Lq; d.P = (int)P;
   d.border = padding == MSDA_PAD_BORDER;
-  d.dbg = 0;
   return d;
 }
 
@@ -137,13 +135,8 @@ int win_grid(K kern, size_t smem, long long units, int* grid) {
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   if (e == cudaSuccess)
     e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (const char* cv = getenv("MSDA_DBG_CARVEOUT")) {   // experiment: shared-memory carveout in percent
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(cv));
-  }
   if (e == cudaSuccess)
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kWinThreads, smem);
-  if (const char* cv = getenv("MSDA_DBG_CTAS")) per_sm = atoi(cv) < per_sm ? atoi(cv) : per_sm;
   if (e != cudaSuccess) return cuda_fail(e);
   if (per_sm < 1) per_sm = 1;
   const long long warps = kWinThreads / 32;
@@ -283,7 +276,6 @@ int msda_forward(const void* value, const int64_t* spatial_shapes, const int64_t
     return MSDA_ERR_NULL_POINTER;
   if (S > 0 && !value) return MSDA_ERR_NULL_POINTER;
   Dims d = make_dims(N, S, M, D, L, Lq, P, padding);
-  d.dbg = (int)((flags >> 20) & 0xffu);
   cudaStream_t st = (cudaStream_t)stream;
   const bool fits32 = S * M * D < (int64_t(1) << 31);
   const bool fast = fits32 && fast_applies(D, L, dtype, flags) && aligned16(value) && aligned16(output) &&
@@ -333,7 +325,6 @@ int msda_backward(const void* value, const int64_t* spatial_shapes, const int64_
   const int rc = check_common(N, S, M, D, L, Lq, P, dtype, padding);
   if (rc != MSDA_OK) return rc;
   Dims d = make_dims(N, S, M, D, L, Lq, P, padding);
-  d.dbg = (int)((flags >> 20) & 0xffu);
   cudaStream_t st = (cudaStream_t)stream;
   const size_t esz = dtype == MSDA_F64 ? 8 : dtype == MSDA_F32 ? 4 : 2;
   const size_t nvalue = (size_t)N * S * M * D;

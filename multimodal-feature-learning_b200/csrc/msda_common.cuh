@@ -144,7 +144,6 @@ constexpr int kMaxLevelsFast = 32;
 struct Dims {
   int N, S, M, D, L, Lq, P;
   int border;
-  int dbg;   // developer experiments (flags bits 20..27); 0 in production
 };
 
 }  // namespace msda

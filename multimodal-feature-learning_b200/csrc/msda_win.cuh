@@ -356,7 +356,6 @@ __device__ __forceinline__ bool win_build(const char* pts, const Dims& d, bool h
   rt = ok ? rtot : 0;
   if (!ok) last_row = 0;
   wmax = __reduce_max_sync(FULL, rt);
-  if (d.dbg & 1) wmax = 0;
 
   const unsigned row_bytes = (unsigned)(d.M * d.D) * (unsigned)sizeof(T);
   const int nfill = ((wmax + kWinFillPad - 1) & ~(kWinFillPad - 1)) + kWinFillPad;
@@ -494,7 +493,7 @@ msda_fwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
         for (int c = 0; c < E / 2; ++c) acc[q][uu][c] = make_float2(0.f, 0.f);
 
     // NS rows in flight per lane: row t+NS+s is requested as soon as row t+s is consumed
-    const int rl = (d.dbg & 8) ? 0 : rt;
+    const int rl = rt;
     Raw buf[NS][NU][4];
     {
       unsigned ro[NS];
@@ -705,9 +704,9 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
     char* gvbb = reinterpret_cast<char*>(gvalue + voff + j * E);
 
     // NS rows in flight per lane
-    const int rl = (d.dbg & 8) ? 0 : rt;
+    const int rl = rt;
     Raw buf[NS][NU][4];
-    const int rr = (d.dbg & 16) ? 0 : rt;   // rows whose grad_value reds are issued
+    const int rr = rt;                      // rows whose grad_value reds are issued
     uint4 rc = *reinterpret_cast<const uint4*>(rowoff);
     win_load_row_first<T, NU, G>(vbb, rc.x, buf[0]);
     win_load_row_first<T, NU, G>(vbb, rc.y, buf[1]);
