@@ -134,6 +134,39 @@ int msda_backward(const void* value, const int64_t* spatial_shapes,
                   int dtype, int padding, unsigned flags,
                   void* workspace, size_t workspace_bytes, void* stream);
 
+/*
+ * Module front-end: what MSDeformAttn.forward does between its Linear layers and
+ * the op (models/ops/modules/ms_deform_attn.py:98-117; live twin
+ * models/modules/attention.py:462-496) -- softmax of the attention logits over
+ * L*P, sampling locations from reference points and offsets, the constant
+ * y = 0.5 -- in one kernel instead of a softmax and four or five elementwise
+ * kernels.  All tensors contiguous, same dtype:
+ *   offsets [N,Lq,M,L,P]   logits [N,Lq,M,L*P]   ref [N,Lq,L,ref_dim]
+ *   level_sizes [L] int64 (device): T_l, the divisor of the offsets (ref_dim 1)
+ *   loc [N,Lq,M,L,P,2] = (ref0 + off / T_l, 0.5)                       ref_dim 1
+ *                        (ref0 + off / P * ref1 * 0.5, 0.5)            ref_dim 2
+ *   aw  [N,Lq,M,L,P]   = softmax(logits)
+ * SURVEY.md section 8(f) row 1 ("next"): first step, the arithmetic fused into one
+ * streaming kernel; folding it into the gather kernels themselves is later work.
+ */
+int msda_frontend_forward(const void* offsets, const void* logits, const void* ref,
+                          const int64_t* level_sizes, void* loc, void* aw,
+                          int64_t N, int64_t Lq, int64_t M, int64_t L, int64_t P,
+                          int ref_dim, int dtype, void* stream);
+
+/*
+ * Gradients of the above: grad_offsets, grad_logits (softmax backward from the
+ * saved aw) and, when grad_ref is not NULL, grad_ref [N,Lq,L,ref_dim] (summed
+ * over heads and points; fully written, no pre-zeroing needed).  The y half of
+ * grad_loc is ignored (y is a constant).
+ */
+int msda_frontend_backward(const void* offsets, const void* aw, const void* ref,
+                           const int64_t* level_sizes, const void* grad_loc,
+                           const void* grad_aw, void* grad_offsets, void* grad_logits,
+                           void* grad_ref,
+                           int64_t N, int64_t Lq, int64_t M, int64_t L, int64_t P,
+                           int ref_dim, int dtype, void* stream);
+
 /* Last CUDA runtime error code seen by the calling thread inside this library
  * (cudaError_t as int) and its string. */
 int msda_last_cuda_error(void);

@@ -35,6 +35,8 @@ EXPORTED_SYMBOLS = (
     "msda_forward",
     "msda_backward_workspace_bytes",
     "msda_backward",
+    "msda_frontend_forward",
+    "msda_frontend_backward",
     "msda_last_cuda_error",
     "msda_last_cuda_error_string",
 )
@@ -72,6 +74,10 @@ def _declare(lib):
     lib.msda_backward.argtypes = (
         [vp] * 9 + [i64] * 7 + [c.c_int, c.c_int, u32, vp, c.c_size_t, vp]
     )
+    lib.msda_frontend_forward.restype = c.c_int
+    lib.msda_frontend_forward.argtypes = [vp] * 6 + [i64] * 5 + [c.c_int, c.c_int, vp]
+    lib.msda_frontend_backward.restype = c.c_int
+    lib.msda_frontend_backward.argtypes = [vp] * 9 + [i64] * 5 + [c.c_int, c.c_int, vp]
     return lib
 
 

@@ -6,6 +6,7 @@
 
 #include "../../include/msda_b200.h"
 #include "msda_fast.cuh"
+#include "msda_frontend.cuh"
 #include "msda_generic.cuh"
 #include "msda_win.cuh"
 
@@ -118,7 +119,7 @@ inline bool win_applies(const Dims& d, int dtype, unsigned flags) {
   if (d.P != kWinP || d.L > kWinMaxL || d.S <= 0) return false;
   // the points of a query are staged with 16-byte cp.async pieces
   if ((d.L * d.P * (dtype == MSDA_BF16 ? 2 : 4)) % 16 != 0) return false;
-  if ((int64_t)d.N * d.M * ((d.Lq + 15) / 16) >= (int64_t(1) << 31)) return false;
+  if ((int64_t)d.N * d.M * ((d.Lq + 7) / 8) >= (int64_t(1) << 31)) return false;
   // 32-bit BYTE offsets inside one batch item's slab (fp32 accumulation image included)
   if ((int64_t)d.S * d.M * d.D * 4 >= (int64_t(1) << 32)) return false;
   if (dtype == MSDA_F32) return d.D == 64 || d.D == 32;
@@ -149,7 +150,8 @@ int win_grid(K kern, size_t smem, long long units, int* grid) {
 template <typename T, int NU, int G>
 int launch_fwd_win(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
                    const void* aw, void* out, const Dims& d, cudaStream_t st) {
-  const int nqc = (d.Lq + 4 * kWinQ - 1) / (4 * kWinQ);
+  constexpr int qpu = (32 / G) * kWinQ;                 // queries per unit (one warp)
+  const int nqc = (d.Lq + qpu - 1) / qpu;
   const long long units = (long long)d.N * d.M * nqc;
   constexpr size_t smem = (size_t)(kWinThreads / G) * WinSmem<T, 1, false, 0>::kGroupBytes;
   auto kern = msda_fwd_win_kernel<T, NU, G>;
@@ -166,7 +168,8 @@ template <typename T, int NU, int G>
 int launch_bwd_win(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
                    const void* aw, const void* gout, float* gvalue, void* gloc, void* gaw,
                    const Dims& d, cudaStream_t st) {
-  const int nqc = (d.Lq + 4 * kWinQ - 1) / (4 * kWinQ);
+  constexpr int qpu = (32 / G) * kWinQ;                 // queries per unit (one warp)
+  const int nqc = (d.Lq + qpu - 1) / qpu;
   const long long units = (long long)d.N * d.M * nqc;
   constexpr size_t smem = (size_t)(kWinThreads / G) * WinSmem<T, 2, false, 0>::kGroupBytes;
   auto kern = msda_bwd_win_kernel<T, NU, G>;
@@ -223,6 +226,58 @@ int launch_bwd_generic(const void* value, const int64_t* shapes, const int64_t* 
   msda_bwd_generic_kernel<T, GV><<<(unsigned)groups, 128, 0, st>>>(
       (const T*)value, shapes, lsi, (const T*)loc, (const T*)aw, (const T*)gout, gvalue, (T*)gloc,
       (T*)gaw, d);
+  const cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
+}
+
+
+// ---- module front-end (msda_frontend.cuh) -----------------------------------
+int check_front(int64_t N, int64_t Lq, int64_t M, int64_t L, int64_t P, int ref_dim, int dtype) {
+  if (N < 0 || Lq < 0 || M <= 0 || L <= 0 || P <= 0) return MSDA_ERR_BAD_SHAPE;
+  if (ref_dim != 1 && ref_dim != 2) return MSDA_ERR_BAD_SHAPE;
+  if (dtype != MSDA_F32 && dtype != MSDA_F64 && dtype != MSDA_BF16) return MSDA_ERR_BAD_DTYPE;
+  if (L * P >= (int64_t(1) << 20) || M >= (int64_t(1) << 20)) return MSDA_ERR_TOO_LARGE;
+  if (N * Lq >= (int64_t(1) << 40) / M) return MSDA_ERR_TOO_LARGE;
+  return MSDA_OK;
+}
+
+template <typename T>
+int launch_front_fwd(const void* off, const void* logits, const void* ref, const int64_t* tl,
+                     void* loc, void* aw, const FrontDims& d, cudaStream_t st) {
+  const unsigned grid = (unsigned)((d.groups + kFrontThreads - 1) / kFrontThreads);
+  // 4 points per 8/16/32-byte piece when P allows it and the arrays are aligned for it
+  const bool vec = d.P % 4 == 0 && aligned16(off) && aligned16(logits) && aligned16(loc) && aligned16(aw);
+  if (vec)
+    msda_frontend_fwd_kernel<T, 4><<<grid, kFrontThreads, 0, st>>>(
+        (const T*)off, (const T*)logits, (const T*)ref, tl, (T*)loc, (T*)aw, d);
+  else
+    msda_frontend_fwd_kernel<T, 1><<<grid, kFrontThreads, 0, st>>>(
+        (const T*)off, (const T*)logits, (const T*)ref, tl, (T*)loc, (T*)aw, d);
+  const cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
+}
+
+template <typename T>
+int launch_front_bwd(const void* off, const void* aw, const void* ref, const int64_t* tl,
+                     const void* gloc, const void* gaw, void* goff, void* glogits, void* gref,
+                     int64_t gref_elems, const FrontDims& d, cudaStream_t st) {
+  const unsigned grid = (unsigned)((d.groups + kFrontThreads - 1) / kFrontThreads);
+  const bool vec = d.P % 4 == 0 && aligned16(off) && aligned16(aw) && aligned16(gloc) &&
+                   aligned16(gaw) && aligned16(goff) && aligned16(glogits);
+  const bool shfl = log2_exact(d.M) >= 0;
+  if (gref && !shfl) {   // atomics accumulate into zeros
+    const cudaError_t e = cudaMemsetAsync(gref, 0, (size_t)gref_elems * sizeof(T), st);
+    if (e != cudaSuccess) return cuda_fail(e);
+  }
+#define MSDA_FRONT_BWD(V_, S_)                                                              \
+  msda_frontend_bwd_kernel<T, V_, S_><<<grid, kFrontThreads, 0, st>>>(                       \
+      (const T*)off, (const T*)aw, (const T*)ref, tl, (const T*)gloc, (const T*)gaw, (T*)goff, \
+      (T*)glogits, (T*)gref, d)
+  if (vec && shfl) MSDA_FRONT_BWD(4, true);
+  else if (vec) MSDA_FRONT_BWD(4, false);
+  else if (shfl) MSDA_FRONT_BWD(1, true);
+  else MSDA_FRONT_BWD(1, false);
+#undef MSDA_FRONT_BWD
   const cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
 }
@@ -404,6 +459,48 @@ int msda_backward(const void* value, const int64_t* spatial_shapes, const int64_
     if (e != cudaSuccess) return cuda_fail(e);
   }
   return MSDA_OK;
+}
+
+
+int msda_frontend_forward(const void* offsets, const void* logits, const void* ref,
+                          const int64_t* level_sizes, void* loc, void* aw, int64_t N, int64_t Lq,
+                          int64_t M, int64_t L, int64_t P, int ref_dim, int dtype, void* stream) {
+  const int rc = check_front(N, Lq, M, L, P, ref_dim, dtype);
+  if (rc != MSDA_OK) return rc;
+  if (N == 0 || Lq == 0) return MSDA_OK;
+  if (!offsets || !logits || !ref || !level_sizes || !loc || !aw) return MSDA_ERR_NULL_POINTER;
+  FrontDims d;
+  d.groups = (long long)(N * Lq * M);
+  d.M = (int)M; d.L = (int)L; d.P = (int)P; d.ref_dim = ref_dim;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == MSDA_F32) return launch_front_fwd<float>(offsets, logits, ref, level_sizes, loc, aw, d, st);
+  if (dtype == MSDA_F64) return launch_front_fwd<double>(offsets, logits, ref, level_sizes, loc, aw, d, st);
+  return launch_front_fwd<__nv_bfloat16>(offsets, logits, ref, level_sizes, loc, aw, d, st);
+}
+
+int msda_frontend_backward(const void* offsets, const void* aw, const void* ref,
+                           const int64_t* level_sizes, const void* grad_loc, const void* grad_aw,
+                           void* grad_offsets, void* grad_logits, void* grad_ref, int64_t N,
+                           int64_t Lq, int64_t M, int64_t L, int64_t P, int ref_dim, int dtype,
+                           void* stream) {
+  const int rc = check_front(N, Lq, M, L, P, ref_dim, dtype);
+  if (rc != MSDA_OK) return rc;
+  if (N == 0 || Lq == 0) return MSDA_OK;
+  if (!offsets || !aw || !ref || !level_sizes || !grad_loc || !grad_aw || !grad_offsets || !grad_logits)
+    return MSDA_ERR_NULL_POINTER;
+  FrontDims d;
+  d.groups = (long long)(N * Lq * M);
+  d.M = (int)M; d.L = (int)L; d.P = (int)P; d.ref_dim = ref_dim;
+  const int64_t ge = N * Lq * L * ref_dim;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == MSDA_F32)
+    return launch_front_bwd<float>(offsets, aw, ref, level_sizes, grad_loc, grad_aw, grad_offsets,
+                                   grad_logits, grad_ref, ge, d, st);
+  if (dtype == MSDA_F64)
+    return launch_front_bwd<double>(offsets, aw, ref, level_sizes, grad_loc, grad_aw, grad_offsets,
+                                    grad_logits, grad_ref, ge, d, st);
+  return launch_front_bwd<__nv_bfloat16>(offsets, aw, ref, level_sizes, grad_loc, grad_aw,
+                                         grad_offsets, grad_logits, grad_ref, ge, d, st);
 }
 
 }  // extern "C"

@@ -191,14 +191,15 @@ __device__ __forceinline__ bool win_stage_levels(const int64_t* __restrict__ sha
 }
 
 // ---- work distribution ------------------------------------------------------
-// A UNIT = 16 consecutive queries (4 blocks, one per 8-lane group of a warp) of
-// one (batch, head).  Warp w of the (persistent) grid takes units w, w + W,
+// A UNIT = the 32 / G blocks of one warp (one per G-lane group): 16 consecutive
+// queries of one (batch, head) for G = 8, 8 for G = 16.  Warp w of the (persistent) grid takes units w, w + W,
 // w + 2W, ... (W = warps in the grid), so at any moment the resident warps work
 // on neighbouring units -- the same few (b, m) slabs, which then stay in L2 --
 // exactly as a non-persistent launch would sweep them.
 struct WinUnit {
   int u, b, m, qc;                       // unit index and its (batch, head, 16-query chunk)
-  __device__ __forceinline__ int q0() const { return qc * (4 * kWinQ); }
+  // first query of the unit; qpu = queries per unit = (32 / G) blocks of kWinQ
+  __device__ __forceinline__ int q0(int qpu) const { return qc * qpu; }
 };
 // The stride W between a warp's units, split once into (chunks, heads, batches):
 // stepping a unit is then three adds with carry instead of two divisions.
@@ -449,7 +450,8 @@ msda_fwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
   const int gi = threadIdx.x / G;
   const int j = threadIdx.x % G;
   const int lane = threadIdx.x & 31;
-  const int gq = (gi & 3) * kWinQ;          // this group's query offset inside a unit
+  constexpr int QPU = (32 / G) * kWinQ;     // queries per unit
+  const int gq = (gi % (32 / G)) * kWinQ;   // this group's query offset inside a unit
   char* s_grp = s_dyn + gi * SM::kGroupBytes;
   char* pts = s_grp + SM::kPlanBytes;
   const float4* Wt = reinterpret_cast<const float4*>(s_grp);
@@ -459,17 +461,17 @@ msda_fwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
   WinUnit w = win_first_unit(blockIdx.x * (kWinThreads / 32) + (threadIdx.x >> 5), nqc, d.M);
   if (!one_d) {
     for (; w.u < uend; w = win_next_unit(w, ust, nqc, d.M)) {
-      const int q0 = w.q0() + gq;
+      const int q0 = w.q0(QPU) + gq;
       fwd_body<T, NU, G, 4>(value, loc, aw, out, d, w.b, w.m, q0, min(q0 + kWinQ, d.Lq), 1, s_lvl,
                             reinterpret_cast<TapMeta<4>*>(s_grp));
       __syncwarp();
     }
     return;
   }
-  if (w.u < uend) win_fetch_points<T>(loc, aw, d, w.b, w.m, w.q0() + gq, pts, j);
+  if (w.u < uend) win_fetch_points<T>(loc, aw, d, w.b, w.m, w.q0(QPU) + gq, pts, j);
   win_cp_commit();
   while (w.u < uend) {
-    const int b = w.b, m = w.m, q0 = w.q0() + gq;
+    const int b = w.b, m = w.m, q0 = w.q0(QPU) + gq;
     const int nq = max(min(kWinQ, d.Lq - q0), 0);
     const bool have_q = (j & 3) < nq;
     win_cp_wait_all();
@@ -479,7 +481,7 @@ msda_fwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
     // win_build ends with a warp barrier: the staged points are consumed, the
     // buffer can take the next unit's
     const WinUnit wn = win_next_unit(w, ust, nqc, d.M);
-    if (wn.u < uend) win_fetch_points<T>(loc, aw, d, wn.b, wn.m, wn.q0() + gq, pts, j);
+    if (wn.u < uend) win_fetch_points<T>(loc, aw, d, wn.b, wn.m, wn.q0(QPU) + gq, pts, j);
     win_cp_commit();
 
     const char* vbb =
@@ -636,7 +638,8 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
   const int gi = threadIdx.x / G;
   const int j = threadIdx.x % G;
   const int lane = threadIdx.x & 31;
-  const int gq = (gi & 3) * kWinQ;
+  constexpr int QPU = (32 / G) * kWinQ;
+  const int gq = (gi % (32 / G)) * kWinQ;
   const int qi = j & 3, h = j >> 2;
   char* s_grp = s_dyn + gi * SM::kGroupBytes;
   char* pts_buf = s_grp + SM::kPlanBytes;                       // two buffers of kPtsBytes
@@ -648,7 +651,7 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
   WinUnit w = win_first_unit(blockIdx.x * (kWinThreads / 32) + (threadIdx.x >> 5), nqc, d.M);
   if (!one_d) {
     for (; w.u < uend; w = win_next_unit(w, ust, nqc, d.M)) {
-      const int q0 = w.q0() + gq;
+      const int q0 = w.q0(QPU) + gq;
       bwd_body<T, NU, G, 4>(value, loc, aw, gout, gvalue, gloc, gaw, d, w.b, w.m, q0,
                             min(q0 + kWinQ, d.Lq), 1, s_lvl, reinterpret_cast<TapMeta<4>*>(s_grp));
       __syncwarp();
@@ -656,10 +659,10 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
     return;
   }
   int cur = 0;
-  if (w.u < uend) win_fetch_points<T>(loc, aw, d, w.b, w.m, w.q0() + gq, pts_buf, j);
+  if (w.u < uend) win_fetch_points<T>(loc, aw, d, w.b, w.m, w.q0(QPU) + gq, pts_buf, j);
   win_cp_commit();
   while (w.u < uend) {
-    const int b = w.b, m = w.m, q0 = w.q0() + gq;
+    const int b = w.b, m = w.m, q0 = w.q0(QPU) + gq;
     const int nq = max(min(kWinQ, d.Lq - q0), 0);
     const bool have_q = qi < nq;
     const char* pts = pts_buf + cur * SM::kPtsBytes;
@@ -686,7 +689,7 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
     // next unit's points into the other buffer
     const WinUnit wn = win_next_unit(w, ust, nqc, d.M);
     if (wn.u < uend)
-      win_fetch_points<T>(loc, aw, d, wn.b, wn.m, wn.q0() + gq, pts_buf + (cur ^ 1) * SM::kPtsBytes, j);
+      win_fetch_points<T>(loc, aw, d, wn.b, wn.m, wn.q0(QPU) + gq, pts_buf + (cur ^ 1) * SM::kPtsBytes, j);
     win_cp_commit();
     float2 go[kWinQ][NU][E / 2];
 #pragma unroll

@@ -18,6 +18,7 @@ import torch.nn.functional as F
 from torch import nn
 from torch.nn.init import constant_, xavier_uniform_
 
+from ..functions.frontend import msdeform_frontend
 from ..functions.ms_deform_attn_func import ms_deform_attn
 
 
@@ -52,6 +53,9 @@ class MSDeformAttn(nn.Module):
         self.padding_mode = padding_mode
         self.attn_weight_init = attn_weight_init
         self.check_input_lengths = True  # the reference's `assert shapes.sum() == Len_in` (a host sync)
+        # softmax + sampling locations in one kernel (functions/frontend.py); False = the
+        # reference's chain of torch kernels (ms_deform_attn.py:98-117), same results
+        self.fused_frontend = True
         self._len_cache = {}
 
         self.sampling_offsets = nn.Linear(d_model, n_heads * n_levels * n_points)
@@ -117,20 +121,23 @@ class MSDeformAttn(nn.Module):
             value = value.masked_fill(input_padding_mask[..., None], float(0))
         value = value.view(N, Len_in, M, self.d_model // M)
         sampling_offsets = self.sampling_offsets(query).view(N, Len_q, M, L, P)
-        attention_weights = F.softmax(self.attention_weights(query).view(N, Len_q, M, L * P), -1)
-        attention_weights = attention_weights.view(N, Len_q, M, L, P)
-
-        ref_t = reference_points[:, :, None, :, None, 0]
-        if reference_points.shape[-1] == 1:
-            sampling_locations = ref_t + sampling_offsets / input_spatial_shapes[None, None, None, :, None]
-        elif reference_points.shape[-1] == 2:
-            sampling_locations = ref_t + sampling_offsets / P * reference_points[:, :, None, :, None, 1] * 0.5
-        else:
+        logits = self.attention_weights(query).view(N, Len_q, M, L * P)
+        if reference_points.shape[-1] not in (1, 2):
             raise ValueError("Last dim of reference_points must be 1 or 2, but get {} instead.".format(
                 reference_points.shape[-1]))
-
-        # temporal -> (x = t, y = 0.5) on maps of shape (1, T_l)   (ms_deform_attn.py:114-117)
-        loc_xy = torch.stack((sampling_locations, torch.full_like(sampling_locations, 0.5)), -1)
+        if self.fused_frontend:
+            loc_xy, attention_weights = msdeform_frontend(sampling_offsets, logits, reference_points,
+                                                          input_spatial_shapes)
+            sampling_locations = loc_xy[..., 0]
+        else:
+            attention_weights = F.softmax(logits, -1).view(N, Len_q, M, L, P)
+            ref_t = reference_points[:, :, None, :, None, 0]
+            if reference_points.shape[-1] == 1:
+                sampling_locations = ref_t + sampling_offsets / input_spatial_shapes[None, None, None, :, None]
+            else:
+                sampling_locations = ref_t + sampling_offsets / P * reference_points[:, :, None, :, None, 1] * 0.5
+            # temporal -> (x = t, y = 0.5) on maps of shape (1, T_l)   (ms_deform_attn.py:114-117)
+            loc_xy = torch.stack((sampling_locations, torch.full_like(sampling_locations, 0.5)), -1)
         shapes_hw = torch.stack((torch.ones_like(input_spatial_shapes), input_spatial_shapes), -1)
         output = ms_deform_attn(value, shapes_hw, input_level_start_index, loc_xy.contiguous(),
                                 attention_weights.contiguous(), self.im2col_step, self.padding_mode)

@@ -31,3 +31,21 @@ def ms_deform_attn_core_pytorch(value, value_spatial_shapes, sampling_locations,
     w = attention_weights.permute(0, 2, 1, 3, 4).reshape(n * m, 1, lq, n_lvl * n_pt)
     out = (stacked * w).sum(-1)                                      # (N*M, D, Lq)
     return out.view(n, m * d, lq).permute(0, 2, 1).contiguous()
+
+
+def frontend_pytorch(sampling_offsets, attention_logits, reference_points, level_sizes):
+    """Restatement of the module's front-end (models/ops/modules/ms_deform_attn.py:98-117;
+    live twin models/modules/attention.py:462-496): softmax over L*P, sampling locations
+    from reference points and offsets, the constant y = 0.5.  Oracle for
+    msda_frontend_forward / _backward (gradients through autograd)."""
+    n, lq, m, n_lvl, n_pt = sampling_offsets.shape
+    aw = F.softmax(attention_logits.reshape(n, lq, m, n_lvl * n_pt), -1).view(n, lq, m, n_lvl, n_pt)
+    ref0 = reference_points[:, :, None, :, None, 0]
+    if reference_points.shape[-1] == 1:
+        x = ref0 + sampling_offsets / level_sizes[None, None, None, :, None]
+    elif reference_points.shape[-1] == 2:
+        x = ref0 + sampling_offsets / n_pt * reference_points[:, :, None, :, None, 1] * 0.5
+    else:
+        raise ValueError("Last dim of reference_points must be 1 or 2")
+    loc = torch.stack((x, 0.5 * x.new_ones(x.shape)), -1)
+    return loc, aw

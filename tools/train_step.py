@@ -139,6 +139,9 @@ def main():
     ap.add_argument("--cuda-graph", action="store_true",
                     help="capture forward + backward + gradient all-reduce + clip + AdamW in one CUDA graph and "
                          "replay it per step (the op enqueues on the capturing stream, allocates nothing itself)")
+    ap.add_argument("--torch-frontend", action="store_true",
+                    help="MSDeformAttn.fused_frontend = False: the reference's softmax + elementwise torch kernels "
+                         "instead of msda_frontend_forward/backward")
     ap.add_argument("--sync", default="flat", choices=["flat", "ddp"],
                     help="gradient exchange at N > 1: 'flat' = every .grad is a view of one 158 MB buffer, one NCCL "
                          "all-reduce (avg) after the backward, no autograd hooks; 'ddp' = DistributedDataParallel "
@@ -172,6 +175,9 @@ def main():
     torch.manual_seed(1234)                                  # same initial weights on every rank
     model = DeformableEncoderDecoder(C, 2048, w["M"], len(T_list), w["P"], args.layers, 100).to(dev)
     n_params = sum(p.numel() for p in model.parameters())
+    for mod in model.modules():
+        if isinstance(mod, MSDeformAttn):
+            mod.fused_frontend = not args.torch_frontend
     net = model
     side = torch.cuda.Stream()
     side.wait_stream(torch.cuda.current_stream())
@@ -272,7 +278,7 @@ def main():
             "config": {"workload": "configs[4]: %d+%d layers, d_model %d, ffn 2048, T=%s, 100 queries, "
                                    "batch %d per GPU, AdamW, clip 0.1, %s GEMMs%s%s" % (
                                        args.layers, args.layers, C, T_list, args.batch,
-                                       "fp32" if args.no_tf32 else "tf32",
+                                       ("fp32" if args.no_tf32 else "tf32") + (", torch front-end" if args.torch_frontend else ", fused front-end"),
                                        ", whole step replayed as one CUDA graph" if args.cuda_graph else "",
                                        ("" if world == 1 else ", one flat NCCL all-reduce of %.1f MB" % (n_params * 4 / 1e6)
                                         if flat is not None else
