@@ -247,7 +247,12 @@ int launch_front_fwd(const void* off, const void* logits, const void* ref, const
   const unsigned grid = (unsigned)((d.groups + kFrontThreads - 1) / kFrontThreads);
   // 4 points per 8/16/32-byte piece when P allows it and the arrays are aligned for it
   const bool vec = d.P % 4 == 0 && aligned16(off) && aligned16(logits) && aligned16(loc) && aligned16(aw);
-  if (vec)
+  const int tpg = (int)(d.L * d.P / 4);          // 4-element pieces per group
+  if (vec && log2_exact(tpg) >= 0) {
+    const unsigned lgrid = (unsigned)((d.groups * tpg + kFrontThreads - 1) / kFrontThreads);
+    msda_frontend_fwd_lanes_kernel<T><<<lgrid, kFrontThreads, 0, st>>>(
+        (const T*)off, (const T*)logits, (const T*)ref, tl, (T*)loc, (T*)aw, d, tpg);
+  } else if (vec)
     msda_frontend_fwd_kernel<T, 4><<<grid, kFrontThreads, 0, st>>>(
         (const T*)off, (const T*)logits, (const T*)ref, tl, (T*)loc, (T*)aw, d);
   else
@@ -264,7 +269,10 @@ int launch_front_bwd(const void* off, const void* aw, const void* ref, const int
   const unsigned grid = (unsigned)((d.groups + kFrontThreads - 1) / kFrontThreads);
   const bool vec = d.P % 4 == 0 && aligned16(off) && aligned16(aw) && aligned16(gloc) &&
                    aligned16(gaw) && aligned16(goff) && aligned16(glogits);
-  const bool shfl = log2_exact(d.M) >= 0;
+  const int tpg = (int)(d.L * d.P / 4);
+  const bool lanes = vec && log2_exact(tpg) >= 0;
+  // shuffles reduce grad_ref over the heads of a query when those share a warp
+  const bool shfl = log2_exact(d.M) >= 0 && (!lanes || d.M * tpg <= 32);
   if (gref && !shfl) {   // atomics accumulate into zeros
     const cudaError_t e = cudaMemsetAsync(gref, 0, (size_t)gref_elems * sizeof(T), st);
     if (e != cudaSuccess) return cuda_fail(e);
@@ -273,7 +281,17 @@ int launch_front_bwd(const void* off, const void* aw, const void* ref, const int
   msda_frontend_bwd_kernel<T, V_, S_><<<grid, kFrontThreads, 0, st>>>(                       \
       (const T*)off, (const T*)aw, (const T*)ref, tl, (const T*)gloc, (const T*)gaw, (T*)goff, \
       (T*)glogits, (T*)gref, d)
-  if (vec && shfl) MSDA_FRONT_BWD(4, true);
+  if (lanes) {
+    const unsigned lgrid = (unsigned)((d.groups * tpg + kFrontThreads - 1) / kFrontThreads);
+    if (shfl)
+      msda_frontend_bwd_lanes_kernel<T, true><<<lgrid, kFrontThreads, 0, st>>>(
+          (const T*)off, (const T*)aw, (const T*)ref, tl, (const T*)gloc, (const T*)gaw, (T*)goff,
+          (T*)glogits, (T*)gref, d, tpg);
+    else
+      msda_frontend_bwd_lanes_kernel<T, false><<<lgrid, kFrontThreads, 0, st>>>(
+          (const T*)off, (const T*)aw, (const T*)ref, tl, (const T*)gloc, (const T*)gaw, (T*)goff,
+          (T*)glogits, (T*)gref, d, tpg);
+  } else if (vec && shfl) MSDA_FRONT_BWD(4, true);
   else if (vec) MSDA_FRONT_BWD(4, false);
   else if (shfl) MSDA_FRONT_BWD(1, true);
   else MSDA_FRONT_BWD(1, false);

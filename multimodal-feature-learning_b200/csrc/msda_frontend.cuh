@@ -224,4 +224,113 @@ msda_frontend_bwd_kernel(const T* __restrict__ off, const T* __restrict__ aw,
   }
 }
 
+
+// ---- lane-per-piece variants -------------------------------------------------
+// When L*P/4 (= tpg, threads per group) is a power of two <= 32, thread i takes the
+// i-th 4-element piece of the whole problem: every load and store is a fully
+// coalesced 8/16/32-byte access and each array is touched exactly once; the
+// softmax statistics travel over the tpg lanes of a group with shuffles, and
+// grad_ref over the M heads of a query when those share a warp (M * tpg <= 32).
+template <typename T>
+__global__ void __launch_bounds__(kFrontThreads)
+msda_frontend_fwd_lanes_kernel(const T* __restrict__ off, const T* __restrict__ logits,
+                               const T* __restrict__ ref, const int64_t* __restrict__ t_lvl,
+                               T* __restrict__ loc, T* __restrict__ aw, FrontDims d, int tpg) {
+  using CT = typename AccOf<T>::type;
+  const long long tid = (long long)blockIdx.x * kFrontThreads + threadIdx.x;
+  const bool valid = tid < d.groups * tpg;
+  const unsigned mask = __ballot_sync(0xffffffffu, valid);
+  if (!valid) return;
+  const long long g = tid / tpg;
+  const int c = (int)(tid - g * tpg);             // piece inside the group
+  const int l = c * 4 / d.P;
+  CT v[4], o[4];
+  FrontVec<T, 4>::ld(logits + tid * 4, v);
+  FrontVec<T, 4>::ld(off + tid * 4, o);
+  CT mx = fmax(fmax(v[0], v[1]), fmax(v[2], v[3]));
+  for (int s = tpg >> 1; s > 0; s >>= 1) mx = fmax(mx, __shfl_xor_sync(mask, mx, s));
+#pragma unroll
+  for (int k = 0; k < 4; ++k) v[k] = exp_t<CT>(v[k] - mx);
+  CT sum = (v[0] + v[1]) + (v[2] + v[3]);
+  for (int s = tpg >> 1; s > 0; s >>= 1) sum += __shfl_xor_sync(mask, sum, s);
+  const CT inv = (CT)1 / sum;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) v[k] *= inv;
+  FrontVec<T, 4>::st(aw + tid * 4, v);
+  const T* rf = ref + ((g / d.M) * d.L + l) * d.ref_dim;
+  const CT r0 = to_acc<T>(rf[0]);
+  const CT r1 = d.ref_dim == 2 ? to_acc<T>(rf[1]) : (CT)0;
+  const CT tl = (CT)t_lvl[l];
+  CT x0[4], x1[4];
+  x0[0] = front_x<CT>(o[0], r0, r1, tl, (CT)d.P, d.ref_dim); x0[1] = (CT)0.5;
+  x0[2] = front_x<CT>(o[1], r0, r1, tl, (CT)d.P, d.ref_dim); x0[3] = (CT)0.5;
+  x1[0] = front_x<CT>(o[2], r0, r1, tl, (CT)d.P, d.ref_dim); x1[1] = (CT)0.5;
+  x1[2] = front_x<CT>(o[3], r0, r1, tl, (CT)d.P, d.ref_dim); x1[3] = (CT)0.5;
+  FrontVec<T, 4>::st(loc + tid * 8, x0);
+  FrontVec<T, 4>::st(loc + tid * 8 + 4, x1);
+}
+
+template <typename T, bool SHFL>
+__global__ void __launch_bounds__(kFrontThreads)
+msda_frontend_bwd_lanes_kernel(const T* __restrict__ off, const T* __restrict__ aw,
+                               const T* __restrict__ ref, const int64_t* __restrict__ t_lvl,
+                               const T* __restrict__ gloc, const T* __restrict__ gaw,
+                               T* __restrict__ goff, T* __restrict__ glogits, T* __restrict__ gref,
+                               FrontDims d, int tpg) {
+  using CT = typename AccOf<T>::type;
+  const long long tid = (long long)blockIdx.x * kFrontThreads + threadIdx.x;
+  const bool valid = tid < d.groups * tpg;
+  const unsigned mask = __ballot_sync(0xffffffffu, valid);
+  if (!valid) return;
+  const long long g = tid / tpg;
+  const int c = (int)(tid - g * tpg);
+  const int ppl = d.P / 4;                        // pieces per level
+  const int l = c / ppl;
+  const long long nq = g / d.M;
+  CT a[4], ga[4], o[4], t0[4], t1[4], gx[4];
+  FrontVec<T, 4>::ld(aw + tid * 4, a);
+  FrontVec<T, 4>::ld(gaw + tid * 4, ga);
+  FrontVec<T, 4>::ld(off + tid * 4, o);
+  FrontVec<T, 4>::ld(gloc + tid * 8, t0);
+  FrontVec<T, 4>::ld(gloc + tid * 8 + 4, t1);
+  gx[0] = t0[0]; gx[1] = t0[2]; gx[2] = t1[0]; gx[3] = t1[2];
+  CT dot = (a[0] * ga[0] + a[1] * ga[1]) + (a[2] * ga[2] + a[3] * ga[3]);
+  for (int s = tpg >> 1; s > 0; s >>= 1) dot += __shfl_xor_sync(mask, dot, s);
+  const T* rf = ref + (nq * d.L + l) * d.ref_dim;
+  const CT r1 = d.ref_dim == 2 ? to_acc<T>(rf[1]) : (CT)0;
+  const CT tl = (CT)t_lvl[l];
+  CT s0 = 0, s1 = 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    a[k] = a[k] * (ga[k] - dot);
+    s0 += gx[k];
+    s1 += gx[k] * (CT)0.5 * (o[k] / (CT)d.P);
+    gx[k] = d.ref_dim == 1 ? gx[k] / tl : gx[k] * (CT)0.5 * r1 / (CT)d.P;
+  }
+  FrontVec<T, 4>::st(glogits + tid * 4, a);
+  FrontVec<T, 4>::st(goff + tid * 4, gx);
+  if (gref != nullptr) {
+    // the pieces of one level, then (SHFL) the heads of the query
+    for (int s = ppl >> 1; s > 0; s >>= 1) {
+      s0 += __shfl_xor_sync(mask, s0, s);
+      s1 += __shfl_xor_sync(mask, s1, s);
+    }
+    T* gr = gref + (nq * d.L + l) * d.ref_dim;
+    const bool first_piece = c - l * ppl == 0;
+    if constexpr (SHFL) {
+      for (int s = tpg; s < tpg * d.M; s <<= 1) {
+        s0 += __shfl_xor_sync(mask, s0, s);
+        s1 += __shfl_xor_sync(mask, s1, s);
+      }
+      if (first_piece && g - nq * d.M == 0) {
+        gr[0] = from_acc<T, CT>(s0);
+        if (d.ref_dim == 2) gr[1] = from_acc<T, CT>(s1);
+      }
+    } else if (first_piece) {
+      front_atomic_add<T>(gr, s0);
+      if (d.ref_dim == 2) front_atomic_add<T>(gr + 1, s1);
+    }
+  }
+}
+
 }  // namespace msda
