@@ -167,6 +167,22 @@ int msda_frontend_backward(const void* offsets, const void* aw, const void* ref,
                            int64_t N, int64_t Lq, int64_t M, int64_t L, int64_t P,
                            int ref_dim, int dtype, void* stream);
 
+/*
+ * Decoder attention map (utils/dam.py:20-73 attn_map_to_flat_grid; consumer
+ * models/criterion.py:246-283): the attention weight of every sampling point
+ * scattered onto the flat token grid, summed over queries and points.
+ *   loc [BL,Q,M,L,P,loc_cols] (x in column 0; loc_cols 1 or 2)   aw [BL,Q,M,L,P]
+ *   level_sizes, level_start [L] int64 (device)
+ *   out [BL,M,S] float32, zero-filled inside the call
+ * out[bl,m,start_l + floor(x*T_l)] += aw * (frac - 1),  [.. + 1] += aw * frac,
+ * indices outside [0, T_l) dropped -- the reference's arithmetic, sign included.
+ * BL = batch * decoder layers.  SURVEY.md section 8(f) row 2.
+ */
+int msda_dam_scatter(const void* loc, const void* aw, const int64_t* level_sizes,
+                     const int64_t* level_start, float* out,
+                     int64_t BL, int64_t Q, int64_t M, int64_t L, int64_t P, int64_t S,
+                     int loc_cols, int dtype, void* stream);
+
 /* Last CUDA runtime error code seen by the calling thread inside this library
  * (cudaError_t as int) and its string. */
 int msda_last_cuda_error(void);

@@ -5,6 +5,7 @@
 // ms_deformable_col2im_cuda (ms_deform_im2col_cuda.cuh:957-1328).
 
 #include "../../include/msda_b200.h"
+#include "msda_dam.cuh"
 #include "msda_fast.cuh"
 #include "msda_frontend.cuh"
 #include "msda_generic.cuh"
@@ -519,6 +520,41 @@ int msda_frontend_backward(const void* offsets, const void* aw, const void* ref,
                                     grad_logits, grad_ref, ge, d, st);
   return launch_front_bwd<__nv_bfloat16>(offsets, aw, ref, level_sizes, grad_loc, grad_aw,
                                          grad_offsets, grad_logits, grad_ref, ge, d, st);
+}
+
+
+int msda_dam_scatter(const void* loc, const void* aw, const int64_t* level_sizes,
+                     const int64_t* level_start, float* out, int64_t BL, int64_t Q, int64_t M,
+                     int64_t L, int64_t P, int64_t S, int loc_cols, int dtype, void* stream) {
+  if (BL < 0 || Q < 0 || M <= 0 || L <= 0 || P <= 0 || S < 0) return MSDA_ERR_BAD_SHAPE;
+  if (loc_cols != 1 && loc_cols != 2) return MSDA_ERR_BAD_SHAPE;
+  if (dtype != MSDA_F32 && dtype != MSDA_F64 && dtype != MSDA_BF16) return MSDA_ERR_BAD_DTYPE;
+  if (S >= (int64_t(1) << 31) || M >= (int64_t(1) << 20) || L * P >= (int64_t(1) << 20) ||
+      Q >= (int64_t(1) << 31))
+    return MSDA_ERR_TOO_LARGE;
+  if (BL > 0 && Q > 0 && BL * Q >= (int64_t(1) << 40) / (M * L * P)) return MSDA_ERR_TOO_LARGE;
+  if (BL == 0 || S == 0) return MSDA_OK;
+  if (!out) return MSDA_ERR_NULL_POINTER;
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e = cudaMemsetAsync(out, 0, (size_t)(BL * M * S) * sizeof(float), st);
+  if (e != cudaSuccess) return cuda_fail(e);
+  if (Q == 0) return MSDA_OK;
+  if (!loc || !aw || !level_sizes || !level_start) return MSDA_ERR_NULL_POINTER;
+  DamDims d;
+  d.points = (long long)(BL * Q * M * L * P);
+  d.Q = (int)Q; d.M = (int)M; d.L = (int)L; d.P = (int)P; d.S = (int)S; d.loc_cols = loc_cols;
+  const unsigned grid = (unsigned)((d.points + 255) / 256);
+  if (dtype == MSDA_F32)
+    msda_dam_scatter_kernel<float><<<grid, 256, 0, st>>>((const float*)loc, (const float*)aw,
+                                                         level_sizes, level_start, out, d);
+  else if (dtype == MSDA_F64)
+    msda_dam_scatter_kernel<double><<<grid, 256, 0, st>>>((const double*)loc, (const double*)aw,
+                                                          level_sizes, level_start, out, d);
+  else
+    msda_dam_scatter_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(
+        (const __nv_bfloat16*)loc, (const __nv_bfloat16*)aw, level_sizes, level_start, out, d);
+  e = cudaGetLastError();
+  return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
 }
 
 }  // extern "C"

@@ -5,7 +5,9 @@ on the GPU box):      python tests/golden/make_golden.py
 
 It imports, by file path and unmodified,
   * models/ops/functions/ms_deform_attn_func.py  (ms_deform_attn_core_pytorch, 2-D form, :44-71)
-  * models/modules/attention.py                  (ms_deform_attn_core_pytorch, 1-D live twin, :331-383)
+  * models/modules/attention.py                  (ms_deform_attn_core_pytorch, 1-D live twin, :331-383;
+                                                   MSDeformAttn, the module every transformer builds, :394-511)
+  * utils/dam.py                                 (attn_map_to_flat_grid, :20-73)
 runs them on seeded inputs (the tiny case reproduces models/ops/test.py:23-44:
 N=1, M=2, D=2, Lq=2, L=2, P=2, shapes (6,4),(3,2), torch.manual_seed(3)) and
 stores inputs, outputs and autograd gradients.
@@ -106,7 +108,58 @@ def make_case(name, seed, N, M, D, Lq, P, shapes_hw, dtype, loc_range=(0.0, 1.0)
     print(name, {k: tuple(v.shape) for k, v in rec.items() if k.startswith(("value", "loc"))})
 
 
+def make_module_case(name, seed, rd, with_mask):
+    """The reference's live MSDeformAttn (attention.py:394-511) run on CPU: parameters, inputs,
+    output, the (loc, aw) it returns with is_sparse=True and the gradients of sum(out * g)."""
+    torch.manual_seed(seed)
+    C, L, M, P = 64, 4, 4, 4
+    T = torch.tensor([24, 12, 6, 3], dtype=torch.long)
+    lsi = torch.cat((T.new_zeros(1), T.cumsum(0)[:-1]))
+    N, Lq, S = 2, 17, int(T.sum())
+    mod = ref_live.MSDeformAttn(C, L, M, P)
+    with torch.no_grad():
+        mod.sampling_offsets.weight.normal_(0, 0.05)     # otherwise the offsets do not depend on the query
+    q = torch.randn(N, Lq, C, requires_grad=True)
+    src = torch.randn(N, S, C, requires_grad=True)
+    ref = torch.rand(N, Lq, L, rd)
+    if rd == 2:
+        ref[..., 1] = ref[..., 1] * 0.5 + 0.05
+    ref.requires_grad_(True)
+    mask = None
+    if with_mask:
+        mask = torch.zeros(N, S, dtype=torch.bool)
+        mask[1, -9:] = True
+    out, loc, aw = mod(q, ref, src, T, lsi, mask, is_sparse=True)
+    g = torch.randn_like(out)
+    (out * g).sum().backward()
+    rec = {"param." + k: v.detach() for k, v in mod.state_dict().items()}
+    rec.update(query=q.detach(), src=src.detach(), ref=ref.detach(), T=T, lsi=lsi, g=g, out=out.detach(),
+               loc=loc.detach(), aw=aw.detach(), g_query=q.grad, g_src=src.grad, g_ref=ref.grad,
+               mask=mask if mask is not None else torch.zeros(0, dtype=torch.bool))
+    rec.update({"gparam." + k: p.grad for k, p in mod.named_parameters()})
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), **{k: v.numpy() for k, v in rec.items()})
+    print(name, tuple(out.shape), tuple(loc.shape))
+
+
+def make_dam_case(name, seed):
+    """utils/dam.py:20-73 on seeded decoder-like inputs, locations spilling past both ends."""
+    ref_dam = _load(os.path.join(REF, "utils/dam.py"), "ref_utils_dam")
+    torch.manual_seed(seed)
+    B, NL, Q, M, L, P = 2, 3, 10, 4, 4, 4
+    T = torch.tensor([24, 12, 6, 3], dtype=torch.long)
+    lsi = torch.cat((T.new_zeros(1), T.cumsum(0)[:-1]))
+    loc = torch.rand(B, NL, Q, M, L, P, 1) * 1.3 - 0.15
+    aw = torch.softmax(torch.randn(B, NL, Q, M, L * P), -1).view(B, NL, Q, M, L, P)
+    out = ref_dam.attn_map_to_flat_grid(T, lsi, loc, aw)
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), T=T.numpy(), lsi=lsi.numpy(), loc=loc.numpy(),
+                        aw=aw.numpy(), out=out.numpy())
+    print(name, tuple(out.shape))
+
+
 def main():
+    make_module_case("module_live_ref1_f32", 41, 1, True)
+    make_module_case("module_live_ref2_f32", 42, 2, False)
+    make_dam_case("dam_f32", 51)
     # models/ops/test.py:17-44 (the only shapes/seeds the reference's tests fix)
     make_case("testpy_tiny_f64", 3, 1, 2, 2, 2, 2, [(6, 4), (3, 2)], torch.float64)
     make_case("testpy_tiny_f32", 3, 1, 2, 2, 2, 2, [(6, 4), (3, 2)], torch.float32)
