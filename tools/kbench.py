@@ -27,7 +27,11 @@ def main():
     ap.add_argument("--flags", default="0,4")
     ap.add_argument("--N", type=int, default=0, help="override the workload's batch size")
     ap.add_argument("--ring", type=int, default=4, help="distinct input sets rotated (1 = L2-resident inputs)")
+    ap.add_argument("--lib", default="", help="A/B aid: load this build of libmsda_b200.so instead of the in-tree one")
     args = ap.parse_args()
+    if args.lib:
+        from mfl_b200 import _lib as _l
+        _l.LIB_PATH = os.path.abspath(args.lib)
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(dev)
     peak = 6550.0
