@@ -12,6 +12,7 @@ a non-CUDA input raises (no PyTorch fallback).
 """
 import math
 import warnings
+import weakref
 
 import torch
 import torch.nn.functional as F
@@ -57,6 +58,7 @@ class MSDeformAttn(nn.Module):
         # reference's chain of torch kernels (ms_deform_attn.py:98-117), same results
         self.fused_frontend = True
         self._len_cache = {}
+        self._hw_cache = None   # (weakref to input_spatial_shapes, its version, the [L, 2] (1, T_l) tensor)
 
         self.sampling_offsets = nn.Linear(d_model, n_heads * n_levels * n_points)
         self.attention_weights = nn.Linear(d_model, n_heads * n_levels * n_points)
@@ -85,6 +87,17 @@ class MSDeformAttn(nn.Module):
         constant_(self.value_proj.bias.data, 0.)
         xavier_uniform_(self.output_proj.weight.data)
         constant_(self.output_proj.bias.data, 0.)
+
+    def _shapes_hw(self, input_spatial_shapes):
+        """[T_l] -> [(1, T_l)] (ms_deform_attn.py:116), built once per shapes tensor: the transformer
+        passes the same tensor object to every layer and step."""
+        c = self._hw_cache
+        if c is not None and c[0]() is input_spatial_shapes and c[1] == input_spatial_shapes._version:
+            return c[2]
+        hw = torch.stack((torch.ones_like(input_spatial_shapes), input_spatial_shapes), -1)
+        if not torch.cuda.is_current_stream_capturing():
+            self._hw_cache = (weakref.ref(input_spatial_shapes), input_spatial_shapes._version, hw)
+        return hw
 
     def _check_lengths(self, input_spatial_shapes, Len_in):
         # ms_deform_attn.py:93 syncs the device every call; cache the verdict
@@ -138,7 +151,7 @@ class MSDeformAttn(nn.Module):
                 sampling_locations = ref_t + sampling_offsets / P * reference_points[:, :, None, :, None, 1] * 0.5
             # temporal -> (x = t, y = 0.5) on maps of shape (1, T_l)   (ms_deform_attn.py:114-117)
             loc_xy = torch.stack((sampling_locations, torch.full_like(sampling_locations, 0.5)), -1)
-        shapes_hw = torch.stack((torch.ones_like(input_spatial_shapes), input_spatial_shapes), -1)
+        shapes_hw = self._shapes_hw(input_spatial_shapes)
         output = ms_deform_attn(value, shapes_hw, input_level_start_index, loc_xy.contiguous(),
                                 attention_weights.contiguous(), self.im2col_step, self.padding_mode)
         output = self.output_proj(output)
