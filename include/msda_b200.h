@@ -81,6 +81,14 @@ typedef enum {
 #define MSDA_FLAG_FORCE_WINDOW 8u   /* use them whenever they are instantiated for
                                       the shape, also for short query lists
                                       (default: Lq >= 256) */
+#define MSDA_FLAG_DETERMINISTIC 16u /* msda_backward: bitwise reproducible grad_value.
+                                      Contributions are accumulated as 64-bit fixed
+                                      point with integer atomics (order-independent)
+                                      by the any-D kernels, then converted; needs
+                                      the workspace msda_backward_workspace_bytes_flags
+                                      reports (32 B + 8 B per grad_value element).
+                                      Slower: an optional variant, as the sorted
+                                      scatter of the design brief, without the sort */
 /* bits 8..19: queries-per-tile multiplier override for the vectorised kernels
  * (0 = heuristic); a tuning knob, results do not depend on it. */
 #define MSDA_FLAG_QTILE(k) (((unsigned)(k) & 0xfffu) << 8)
@@ -118,6 +126,11 @@ int msda_forward(const void* value, const int64_t* spatial_shapes,
  * image of grad_value for bf16). */
 size_t msda_backward_workspace_bytes(int64_t N, int64_t S, int64_t M, int64_t D,
                                      int64_t L, int64_t Lq, int64_t P, int dtype);
+
+/* The same for a given `flags` word (MSDA_FLAG_DETERMINISTIC changes the answer). */
+size_t msda_backward_workspace_bytes_flags(int64_t N, int64_t S, int64_t M, int64_t D,
+                                           int64_t L, int64_t Lq, int64_t P, int dtype,
+                                           unsigned flags);
 
 /*
  * Replaces ms_deform_attn_cuda_backward (cuda.cu:83-153) + the col2im kernels

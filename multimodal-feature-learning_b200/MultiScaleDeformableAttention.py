@@ -77,7 +77,10 @@ def ms_deform_attn_forward(value, spatial_shapes, level_start_index, sampling_lo
 
 def ms_deform_attn_backward(value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
                             grad_output, im2col_step, padding_mode="zeros", flags=0):
-    """-> [grad_value, grad_sampling_loc, grad_attn_weight]  (cuda.cu:83-153)."""
+    """-> [grad_value, grad_sampling_loc, grad_attn_weight]  (cuda.cu:83-153).
+    flags |= MSDA_FLAG_DETERMINISTIC (16): bitwise reproducible grad_value (fixed-point
+    accumulation, csrc/msda_det.cuh); the autograd Functions set it when
+    torch.are_deterministic_algorithms_enabled()."""
     N, S, M, D, L, Lq, P = _check_inputs(
         [("value", value), ("spatial_shapes", spatial_shapes),
          ("level_start_index", level_start_index), ("sampling_loc", sampling_loc),
@@ -90,10 +93,10 @@ def ms_deform_attn_backward(value, spatial_shapes, level_start_index, sampling_l
         grad_value = torch.empty_like(value)
         grad_loc = torch.empty_like(sampling_loc)
         grad_aw = torch.empty_like(attn_weight)
-        ws_bytes = lib.msda_backward_workspace_bytes(N, S, M, D, L, Lq, P, dt)
+        ws_bytes = lib.msda_backward_workspace_bytes_flags(N, S, M, D, L, Lq, P, dt, flags)
         ws = None
         if ws_bytes:
-            ws = torch.empty(ws_bytes // 4, dtype=torch.float32, device=value.device)
+            ws = torch.empty((ws_bytes + 3) // 4, dtype=torch.float32, device=value.device)
         _lib.check(lib.msda_backward(
             value.data_ptr(), spatial_shapes.data_ptr(), level_start_index.data_ptr(),
             sampling_loc.data_ptr(), attn_weight.data_ptr(), grad_output.data_ptr(),

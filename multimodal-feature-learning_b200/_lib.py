@@ -19,6 +19,7 @@ MSDA_FLAG_FORCE_GENERIC = 1
 MSDA_FLAG_SKIP_ZERO_FILL = 2
 MSDA_FLAG_NO_WINDOW = 4
 MSDA_FLAG_FORCE_WINDOW = 8
+MSDA_FLAG_DETERMINISTIC = 16
 
 
 def flag_qtile(k):
@@ -34,6 +35,7 @@ EXPORTED_SYMBOLS = (
     "msda_kernel_choice",
     "msda_forward",
     "msda_backward_workspace_bytes",
+    "msda_backward_workspace_bytes_flags",
     "msda_backward",
     "msda_frontend_forward",
     "msda_frontend_backward",
@@ -71,6 +73,8 @@ def _declare(lib):
     lib.msda_forward.argtypes = [vp, vp, vp, vp, vp, vp] + [i64] * 7 + [c.c_int, c.c_int, u32, vp]
     lib.msda_backward_workspace_bytes.restype = c.c_size_t
     lib.msda_backward_workspace_bytes.argtypes = [i64] * 7 + [c.c_int]
+    lib.msda_backward_workspace_bytes_flags.restype = c.c_size_t
+    lib.msda_backward_workspace_bytes_flags.argtypes = [i64] * 7 + [c.c_int, u32]
     lib.msda_backward.restype = c.c_int
     lib.msda_backward.argtypes = (
         [vp] * 9 + [i64] * 7 + [c.c_int, c.c_int, u32, vp, c.c_size_t, vp]

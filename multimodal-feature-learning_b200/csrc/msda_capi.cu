@@ -222,15 +222,39 @@ int launch_fwd_generic(const void* value, const int64_t* shapes, const int64_t* 
 template <typename T, typename GV>
 int launch_bwd_generic(const void* value, const int64_t* shapes, const int64_t* lsi,
                        const void* loc, const void* aw, const void* gout, GV* gvalue, void* gloc,
-                       void* gaw, const Dims& d, cudaStream_t st) {
+                       void* gaw, const Dims& d, cudaStream_t st, const DetHeader* det = nullptr) {
   const int64_t groups = (int64_t)d.N * d.Lq * d.M;
   msda_bwd_generic_kernel<T, GV><<<(unsigned)groups, 128, 0, st>>>(
       (const T*)value, shapes, lsi, (const T*)loc, (const T*)aw, (const T*)gout, gvalue, (T*)gloc,
-      (T*)gaw, d);
+      (T*)gaw, d, det);
   const cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
 }
 
+
+// ---- deterministic backward (msda_det.cuh) ------------------------------------
+template <typename T>
+int backward_deterministic(const void* value, const int64_t* shapes, const int64_t* lsi,
+                           const void* loc, const void* aw, const void* gout, void* gvalue,
+                           void* gloc, void* gaw, const Dims& d, void* workspace, cudaStream_t st) {
+  DetHeader* hdr = (DetHeader*)workspace;
+  long long* acc = (long long*)((char*)workspace + sizeof(DetHeader));
+  const size_t nvalue = (size_t)d.N * d.S * d.M * d.D;
+  const size_t ngo = (size_t)d.N * d.Lq * d.M * d.D, naw = (size_t)d.N * d.Lq * d.M * d.L * d.P;
+  auto blocks = [](size_t n) { size_t b = (n + 255) / 256; return (unsigned)(b > 148u * 8u ? 148u * 8u : b < 1 ? 1 : b); };
+  msda_det_amax_kernel<T><<<blocks(ngo), 256, 0, st>>>((const T*)gout, ngo, &hdr->amax_go);
+  msda_det_amax_kernel<T><<<blocks(naw), 256, 0, st>>>((const T*)aw, naw, &hdr->amax_aw);
+  int log2_addends = 0;
+  while ((int64_t(1) << log2_addends) < (int64_t)d.Lq * d.L * d.P * 4) ++log2_addends;
+  msda_det_scale_kernel<<<1, 1, 0, st>>>(hdr, log2_addends);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(e);
+  const int r = launch_bwd_generic<T, long long>(value, shapes, lsi, loc, aw, gout, acc, gloc, gaw, d, st, hdr);
+  if (r != MSDA_OK) return r;
+  msda_det_convert_kernel<T><<<blocks(nvalue), 256, 0, st>>>(acc, (T*)gvalue, nvalue, hdr);
+  e = cudaGetLastError();
+  return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
+}
 
 // ---- module front-end (msda_frontend.cuh) -----------------------------------
 int check_front(int64_t N, int64_t Lq, int64_t M, int64_t L, int64_t P, int ref_dim, int dtype) {
@@ -390,6 +414,14 @@ size_t msda_backward_workspace_bytes(int64_t N, int64_t S, int64_t M, int64_t D,
   return (size_t)N * S * M * D * sizeof(float);
 }
 
+size_t msda_backward_workspace_bytes_flags(int64_t N, int64_t S, int64_t M, int64_t D, int64_t L,
+                                           int64_t Lq, int64_t P, int dtype, unsigned flags) {
+  if (!(flags & MSDA_FLAG_DETERMINISTIC))
+    return msda_backward_workspace_bytes(N, S, M, D, L, Lq, P, dtype);
+  if (N <= 0 || S <= 0 || M <= 0 || D <= 0) return 0;
+  return sizeof(DetHeader) + (size_t)N * S * M * D * sizeof(long long);
+}
+
 int msda_backward(const void* value, const int64_t* spatial_shapes, const int64_t* level_start_index,
                   const void* sampling_loc, const void* attn_weight, const void* grad_output,
                   void* grad_value, void* grad_sampling_loc, void* grad_attn_weight, int64_t N,
@@ -402,10 +434,37 @@ int msda_backward(const void* value, const int64_t* spatial_shapes, const int64_
   cudaStream_t st = (cudaStream_t)stream;
   const size_t esz = dtype == MSDA_F64 ? 8 : dtype == MSDA_F32 ? 4 : 2;
   const size_t nvalue = (size_t)N * S * M * D;
-  const size_t ws_need = msda_backward_workspace_bytes(N, S, M, D, L, Lq, P, dtype);
+  const size_t ws_need = msda_backward_workspace_bytes_flags(N, S, M, D, L, Lq, P, dtype, flags);
   if (nvalue > 0 && (!grad_value || !value)) return MSDA_ERR_NULL_POINTER;
   if (ws_need > 0 && (!workspace || workspace_bytes < ws_need)) return MSDA_ERR_WORKSPACE;
   if (ws_need > 0 && !aligned16(workspace)) return MSDA_ERR_MISALIGNED;
+
+  if (flags & MSDA_FLAG_DETERMINISTIC) {
+    // fixed-point image + header are always cleared here (MSDA_FLAG_SKIP_ZERO_FILL does not apply)
+    if (ws_need > 0) {
+      const cudaError_t e = cudaMemsetAsync(workspace, 0, ws_need, st);
+      if (e != cudaSuccess) return cuda_fail(e);
+    }
+    if (N == 0 || Lq == 0) {
+      if (nvalue == 0) return MSDA_OK;
+      const cudaError_t e = cudaMemsetAsync(grad_value, 0, nvalue * esz, st);
+      return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
+    }
+    if (!spatial_shapes || !level_start_index || !sampling_loc || !attn_weight || !grad_output ||
+        !grad_sampling_loc || !grad_attn_weight)
+      return MSDA_ERR_NULL_POINTER;
+    if (dtype == MSDA_F32)
+      return backward_deterministic<float>(value, spatial_shapes, level_start_index, sampling_loc,
+                                           attn_weight, grad_output, grad_value, grad_sampling_loc,
+                                           grad_attn_weight, d, workspace, st);
+    if (dtype == MSDA_F64)
+      return backward_deterministic<double>(value, spatial_shapes, level_start_index, sampling_loc,
+                                            attn_weight, grad_output, grad_value, grad_sampling_loc,
+                                            grad_attn_weight, d, workspace, st);
+    return backward_deterministic<__nv_bfloat16>(value, spatial_shapes, level_start_index,
+                                                 sampling_loc, attn_weight, grad_output, grad_value,
+                                                 grad_sampling_loc, grad_attn_weight, d, workspace, st);
+  }
 
   // zero the accumulation target (the reference does this with zeros_like,
   // cuda.cu:121-123; grad_loc / grad_aw are fully written by the kernels)

@@ -5,6 +5,7 @@
 // reference tests with gradcheck (models/ops/test.py:85: 30, 71, 1025, 3096).
 #pragma once
 #include "msda_common.cuh"
+#include "msda_det.cuh"
 
 namespace msda {
 
@@ -52,16 +53,18 @@ template <typename CT> __device__ __forceinline__ CT warp_sum(CT v) {
 }
 
 // one CTA per (b, q, m); threads stride over the D channels.  GV is the
-// grad_value accumulation type (T for f32/f64, float workspace for bf16).
+// grad_value accumulation type (T for f32/f64, float workspace for bf16, int64
+// fixed point with `det` for the deterministic variant).
 template <typename T, typename GV>
 __global__ void __launch_bounds__(128)
 msda_bwd_generic_kernel(const T* __restrict__ value, const int64_t* __restrict__ shapes,
                         const int64_t* __restrict__ lsi, const T* __restrict__ loc,
                         const T* __restrict__ aw, const T* __restrict__ gout,
                         GV* __restrict__ gvalue, T* __restrict__ gloc, T* __restrict__ gaw,
-                        Dims d) {
+                        Dims d, const DetHeader* __restrict__ det) {
   using CT = typename AccOf<T>::type;
   __shared__ CT s_part[4][4];  // [warp][tap]
+  const CT gv_scale = det ? (CT)det->scale : (CT)1;   // fixed-point accumulation (msda_det.cuh)
   const size_t grp = blockIdx.x;
   const int m = (int)(grp % d.M);
   const size_t b = grp / ((size_t)d.M * d.Lq);
@@ -89,7 +92,7 @@ msda_bwd_generic_kernel(const T* __restrict__ value, const int64_t* __restrict__
           if (g.off[k] >= 0) {
             const size_t o = voff + (size_t)g.off[k] * MD + c;
             dot[k] += gc * to_acc(value[o]);
-            atomicAdd(gvalue + o, (GV)(g.w[k] * a * gc));
+            AccAdd<GV, CT>::add(gvalue + o, g.w[k] * a * gc, gv_scale);
           }
         }
       }

@@ -11,6 +11,7 @@ from torch.autograd import Function
 from torch.autograd.function import once_differentiable
 
 from .. import MultiScaleDeformableAttention as MSDA
+from .. import _lib
 
 
 class _MSDeformAttnBase(Function):
@@ -33,9 +34,12 @@ class _MSDeformAttnBase(Function):
     @classmethod
     def _bwd(cls, ctx, grad_output):
         value, shapes, lsi, loc, aw = ctx.saved_tensors
+        # torch.use_deterministic_algorithms(True) selects the order-independent accumulation of
+        # grad_value (the reference's atomicAdd scatter has no such mode)
+        flags = _lib.MSDA_FLAG_DETERMINISTIC if torch.are_deterministic_algorithms_enabled() else 0
         grad_value, grad_loc, grad_aw = MSDA.ms_deform_attn_backward(
             value, shapes, lsi, loc, aw, grad_output, ctx.im2col_step,
-            padding_mode=cls.padding_mode)
+            padding_mode=cls.padding_mode, flags=flags)
         return grad_value, None, None, grad_loc, grad_aw, None
 
 
