@@ -4,6 +4,8 @@
 // (models/ops/src/cuda/ms_deform_attn_cuda.cu:20-153) and the D-dispatch table
 // ms_deformable_col2im_cuda (ms_deform_im2col_cuda.cuh:957-1328).
 
+#include <type_traits>
+
 #include "../../include/msda_b200.h"
 #include "msda_dam.cuh"
 #include "msda_fast.cuh"
@@ -94,16 +96,16 @@ int launch_fwd_fast(const void* value, const int64_t* shapes, const int64_t* lsi
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
 }
 
-template <typename T, int NU, int G>
+template <typename T, int NU, int G, typename GV = float>
 int launch_bwd_fast(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
-                    const void* aw, const void* gout, float* gvalue, void* gloc, void* gaw,
-                    const Dims& d, unsigned flags, cudaStream_t st) {
+                    const void* aw, const void* gout, GV* gvalue, void* gloc, void* gaw,
+                    const Dims& d, unsigned flags, cudaStream_t st, const DetHeader* det = nullptr) {
   const int qtile = pick_qtile(d, G, flags);
   const int nqc = (d.Lq + qtile - 1) / qtile;
   const int64_t tiles = (int64_t)d.N * d.M * nqc;
-  msda_bwd_fast_kernel<T, NU, G><<<(unsigned)tiles, kFastThreads, 0, st>>>(
+  msda_bwd_fast_kernel<T, NU, G, GV><<<(unsigned)tiles, kFastThreads, 0, st>>>(
       (const T*)value, shapes, lsi, (const T*)loc, (const T*)aw, (const T*)gout, gvalue, (T*)gloc,
-      (T*)gaw, d, qtile, nqc);
+      (T*)gaw, d, qtile, nqc, det);
   const cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
 }
@@ -165,20 +167,21 @@ int launch_fwd_win(const void* value, const int64_t* shapes, const int64_t* lsi,
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
 }
 
-template <typename T, int NU, int G>
+template <typename T, int NU, int G, typename GV = float>
 int launch_bwd_win(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
-                   const void* aw, const void* gout, float* gvalue, void* gloc, void* gaw,
-                   const Dims& d, cudaStream_t st) {
+                   const void* aw, const void* gout, GV* gvalue, void* gloc, void* gaw,
+                   const Dims& d, cudaStream_t st, const DetHeader* det = nullptr) {
   constexpr int qpu = (32 / G) * kWinQ;                 // queries per unit (one warp)
   const int nqc = (d.Lq + qpu - 1) / qpu;
   const long long units = (long long)d.N * d.M * nqc;
   constexpr size_t smem = (size_t)(kWinThreads / G) * WinSmem<T, 2, false, 0>::kGroupBytes;
-  auto kern = msda_bwd_win_kernel<T, NU, G>;
+  auto kern = msda_bwd_win_kernel<T, NU, G, GV>;
   int grid = 1;
   const int rc = win_grid(kern, smem, units, &grid);
   if (rc != MSDA_OK) return rc;
   kern<<<grid, kWinThreads, smem, st>>>((const T*)value, shapes, lsi, (const T*)loc, (const T*)aw,
-                                        (const T*)gout, gvalue, (T*)gloc, (T*)gaw, d, nqc, (int)units);
+                                        (const T*)gout, gvalue, (T*)gloc, (T*)gaw, d, nqc, (int)units,
+                                        det);
   const cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
 }
@@ -233,10 +236,13 @@ int launch_bwd_generic(const void* value, const int64_t* shapes, const int64_t* 
 
 
 // ---- deterministic backward (msda_det.cuh) ------------------------------------
-template <typename T>
+// family: 2 = row-window kernels, 1 = per-tap vectorised kernels (both only in their 8-lane
+// instantiations <T, NU, 8>: f32 D = 64 / 32, bf16 D = 64), 0 = any-D kernels
+template <typename T, int NU>
 int backward_deterministic(const void* value, const int64_t* shapes, const int64_t* lsi,
                            const void* loc, const void* aw, const void* gout, void* gvalue,
-                           void* gloc, void* gaw, const Dims& d, void* workspace, cudaStream_t st) {
+                           void* gloc, void* gaw, const Dims& d, void* workspace, int family,
+                           unsigned flags, cudaStream_t st) {
   DetHeader* hdr = (DetHeader*)workspace;
   long long* acc = (long long*)((char*)workspace + sizeof(DetHeader));
   const size_t nvalue = (size_t)d.N * d.S * d.M * d.D;
@@ -249,7 +255,19 @@ int backward_deterministic(const void* value, const int64_t* shapes, const int64
   msda_det_scale_kernel<<<1, 1, 0, st>>>(hdr, log2_addends);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return cuda_fail(e);
-  const int r = launch_bwd_generic<T, long long>(value, shapes, lsi, loc, aw, gout, acc, gloc, gaw, d, st, hdr);
+  int r = MSDA_OK;
+  bool done = false;
+  if constexpr (!std::is_same<T, double>::value) {   // the vectorised kernels have no fp64 form
+    if (family == 2) {
+      r = launch_bwd_win<T, NU, 8, long long>(value, shapes, lsi, loc, aw, gout, acc, gloc, gaw, d, st, hdr);
+      done = true;
+    } else if (family == 1) {
+      r = launch_bwd_fast<T, NU, 8, long long>(value, shapes, lsi, loc, aw, gout, acc, gloc, gaw, d, flags, st, hdr);
+      done = true;
+    }
+  }
+  if (!done)
+    r = launch_bwd_generic<T, long long>(value, shapes, lsi, loc, aw, gout, acc, gloc, gaw, d, st, hdr);
   if (r != MSDA_OK) return r;
   msda_det_convert_kernel<T><<<blocks(nvalue), 256, 0, st>>>(acc, (T*)gvalue, nvalue, hdr);
   e = cudaGetLastError();
@@ -453,17 +471,24 @@ int msda_backward(const void* value, const int64_t* spatial_shapes, const int64_
     if (!spatial_shapes || !level_start_index || !sampling_loc || !attn_weight || !grad_output ||
         !grad_sampling_loc || !grad_attn_weight)
       return MSDA_ERR_NULL_POINTER;
-    if (dtype == MSDA_F32)
-      return backward_deterministic<float>(value, spatial_shapes, level_start_index, sampling_loc,
-                                           attn_weight, grad_output, grad_value, grad_sampling_loc,
-                                           grad_attn_weight, d, workspace, st);
-    if (dtype == MSDA_F64)
-      return backward_deterministic<double>(value, spatial_shapes, level_start_index, sampling_loc,
-                                            attn_weight, grad_output, grad_value, grad_sampling_loc,
-                                            grad_attn_weight, d, workspace, st);
-    return backward_deterministic<__nv_bfloat16>(value, spatial_shapes, level_start_index,
-                                                 sampling_loc, attn_weight, grad_output, grad_value,
-                                                 grad_sampling_loc, grad_attn_weight, d, workspace, st);
+    // the 8-lane vectorised instantiations cover the production head sizes; the 64-bit image
+    // doubles the byte offsets the window kernels keep in 32 bits
+    const bool aligned = aligned16(value) && aligned16(grad_output) && aligned16(sampling_loc) &&
+                         aligned16(attn_weight) && aligned16(grad_sampling_loc) &&
+                         aligned16(grad_attn_weight) && aligned16(workspace);
+    const bool vec8 = aligned && S * M * D < (int64_t(1) << 31) && fast_applies(D, L, dtype, flags) &&
+                      ((dtype == MSDA_F32 && (D == 64 || D == 32)) || (dtype == MSDA_BF16 && D == 64));
+    const int family = !vec8 ? 0
+                       : (win_applies(d, dtype, flags) && S * M * D * 8 < (int64_t(1) << 32)) ? 2 : 1;
+#define MSDA_DET(T_, NU_)                                                                        \
+  return backward_deterministic<T_, NU_>(value, spatial_shapes, level_start_index, sampling_loc,  \
+                                         attn_weight, grad_output, grad_value, grad_sampling_loc, \
+                                         grad_attn_weight, d, workspace, family, flags, st)
+    if (dtype == MSDA_F32 && D == 64) MSDA_DET(float, 2);
+    if (dtype == MSDA_F32) MSDA_DET(float, 1);
+    if (dtype == MSDA_F64) MSDA_DET(double, 1);
+    MSDA_DET(__nv_bfloat16, 1);
+#undef MSDA_DET
   }
 
   // zero the accumulation target (the reference does this with zeros_like,

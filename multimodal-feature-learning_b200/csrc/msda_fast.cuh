@@ -19,6 +19,7 @@
 //     to a 2-tap body.
 #pragma once
 #include "msda_common.cuh"
+#include "msda_det.cuh"
 
 namespace msda {
 
@@ -192,6 +193,28 @@ __device__ __forceinline__ void red_add_f32x4_pred(float* p, bool pred, float a,
                : "memory");
 }
 
+// grad_value accumulation of the vectorised kernels: fp32 reds (default), or 64-bit fixed
+// point with integer atomics for the deterministic variant (msda_det.cuh)
+template <typename GV> struct GvRed;
+template <> struct GvRed<float> {
+  static __device__ __forceinline__ void add4(float* p, bool pred, float a, float b, float c, float d,
+                                              float) {
+    red_add_f32x4_pred(p, pred, a, b, c, d);
+  }
+};
+template <> struct GvRed<long long> {
+  static __device__ __forceinline__ void add4(long long* p, bool pred, float a, float b, float c,
+                                              float d, float scale) {
+    if (pred) {
+      unsigned long long* q = reinterpret_cast<unsigned long long*>(p);
+      atomicAdd(q + 0, (unsigned long long)__float2ll_rn(a * scale));
+      atomicAdd(q + 1, (unsigned long long)__float2ll_rn(b * scale));
+      atomicAdd(q + 2, (unsigned long long)__float2ll_rn(c * scale));
+      atomicAdd(q + 3, (unsigned long long)__float2ll_rn(d * scale));
+    }
+  }
+};
+
 // Which taps a 2-tap (H == 1) body uses: the top pair (0,1) when row h_low is
 // the map's single row, else the bottom pair (2,3).
 template <int NT> __device__ __forceinline__ bool use_bottom_pair(const PointGeom<float>& g) {
@@ -332,13 +355,13 @@ msda_fwd_fast_kernel(const T* __restrict__ value, const int64_t* __restrict__ sh
 // the G points of the chunk and one transpose-reduce hands point j's totals to
 // lane j, which owns that point's geometry and writes its three gradients
 // (.cuh:115-159 for the math).
-template <typename T, int NU, int G, int NT>
+template <typename T, int NU, int G, int NT, typename GV = float>
 __device__ __forceinline__ void bwd_body(const T* __restrict__ value, const T* __restrict__ loc,
                                          const T* __restrict__ aw, const T* __restrict__ gout,
-                                         float* __restrict__ gvalue, T* __restrict__ gloc,
+                                         GV* __restrict__ gvalue, T* __restrict__ gloc,
                                          T* __restrict__ gaw, const Dims& d, int b, int m,
                                          int q_first, int q_end, int q_step, const int* s_lvl,
-                                         TapMeta<NT>* s_meta) {
+                                         TapMeta<NT>* s_meta, float gv_scale = 1.f) {
   constexpr int E = Unit<T>::E;
   const int lane = threadIdx.x & 31;
   const int j = threadIdx.x % G;
@@ -347,7 +370,7 @@ __device__ __forceinline__ void bwd_body(const T* __restrict__ value, const T* _
   const int MD = d.M * d.D;
   const size_t voff = ((size_t)b * d.S * d.M + m) * d.D + j * E;
   const T* vb = value + voff;
-  float* gvb = gvalue + voff;
+  GV* gvb = gvalue + voff;
 
   for (int q = q_first; q < q_end; q += q_step) {
     const size_t grp = ((size_t)b * d.Lq + q) * d.M + m;
@@ -382,9 +405,9 @@ __device__ __forceinline__ void bwd_body(const T* __restrict__ value, const T* _
             for (int c = 0; c < E; ++c) s = fmaf(go[u][c], v[c], s);
 #pragma unroll
             for (int c = 0; c < E; c += 4)
-              red_add_f32x4_pred(gvb + tm.off[k] + u * (G * E) + c, live, tm.w[k] * go[u][c],
-                                 tm.w[k] * go[u][c + 1], tm.w[k] * go[u][c + 2],
-                                 tm.w[k] * go[u][c + 3]);
+              GvRed<GV>::add4(gvb + tm.off[k] + u * (G * E) + c, live, tm.w[k] * go[u][c],
+                              tm.w[k] * go[u][c + 1], tm.w[k] * go[u][c + 2],
+                              tm.w[k] * go[u][c + 3], gv_scale);
           }
           dot[k][i] = s;
         }
@@ -403,13 +426,14 @@ __device__ __forceinline__ void bwd_body(const T* __restrict__ value, const T* _
   }
 }
 
-template <typename T, int NU, int G>
+template <typename T, int NU, int G, typename GV = float>
 __global__ void __launch_bounds__(kFastThreads)
 msda_bwd_fast_kernel(const T* __restrict__ value, const int64_t* __restrict__ shapes,
                      const int64_t* __restrict__ lsi, const T* __restrict__ loc,
                      const T* __restrict__ aw, const T* __restrict__ gout,
-                     float* __restrict__ gvalue, T* __restrict__ gloc, T* __restrict__ gaw, Dims d,
-                     int qtile, int nqc) {
+                     GV* __restrict__ gvalue, T* __restrict__ gloc, T* __restrict__ gaw, Dims d,
+                     int qtile, int nqc, const DetHeader* __restrict__ det) {
+  const float gv_scale = det ? (float)det->scale : 1.f;
   __shared__ int s_lvl[3 * kMaxLevelsFast];
   __shared__ int s_one_d;
   __shared__ TapMeta<4> s_meta[kFastThreads];
@@ -424,11 +448,11 @@ msda_bwd_fast_kernel(const T* __restrict__ value, const int64_t* __restrict__ sh
   constexpr int NG = kFastThreads / G;
   const int gi = threadIdx.x / G;
   if (s_one_d)
-    bwd_body<T, NU, G, 2>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q_begin + gi, q_end, NG,
-                          s_lvl, reinterpret_cast<TapMeta<2>*>(s_meta) + gi * G);
+    bwd_body<T, NU, G, 2, GV>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q_begin + gi, q_end,
+                              NG, s_lvl, reinterpret_cast<TapMeta<2>*>(s_meta) + gi * G, gv_scale);
   else
-    bwd_body<T, NU, G, 4>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q_begin + gi, q_end, NG,
-                          s_lvl, s_meta + gi * G);
+    bwd_body<T, NU, G, 4, GV>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q_begin + gi, q_end,
+                              NG, s_lvl, s_meta + gi * G, gv_scale);
 }
 
 // fp32 accumulation image -> bf16 grad_value

@@ -561,21 +561,22 @@ msda_fwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
 // One step = the two packed rows t, t+1: grad_value rows leave as 128-bit reds,
 // the 2 x 4 dots <grad_out[q], value row> are transpose-reduced over the 8
 // lanes; lane (qi, h) ends with the total for (row t+h, query qi).
-template <typename T, int NU, int G>
+template <typename T, int NU, int G, typename GV = float>
 __device__ __forceinline__ void bwd_win_step(const float4* Wt, float* Gs, char* gvbb, unsigned ro0,
                                              unsigned ro1, int t, int rt, int j,
                                              const typename Unit<T>::Raw (&b0)[NU][4],
                                              const typename Unit<T>::Raw (&b1)[NU][4],
-                                             const float2 (&go)[kWinQ][NU][Unit<T>::E / 2]) {
+                                             const float2 (&go)[kWinQ][NU][Unit<T>::E / 2],
+                                             float gv_scale) {
   constexpr int E = Unit<T>::E;
   constexpr unsigned FULL = 0xffffffffu;
-  constexpr unsigned kAccScale = (unsigned)(sizeof(float) / sizeof(T));  // fp32 image of a T slab
+  constexpr unsigned kAccScale = (unsigned)(sizeof(GV) / sizeof(T));  // accumulation image of a T slab
   float x[2 * kWinQ];
 #pragma unroll
   for (int r = 0; r < 2; ++r) {
     const float4 w = Wt[t + r];
     const float wq[kWinQ] = {w.x, w.y, w.z, w.w};
-    float* gp = reinterpret_cast<float*>(
+    GV* gp = reinterpret_cast<GV*>(
         const_cast<char*>(win_addr(gvbb, (r == 0 ? ro0 : ro1) * kAccScale)));
     const bool real = t + r < rt;
     float2 s[kWinQ];
@@ -593,11 +594,10 @@ __device__ __forceinline__ void bwd_win_step(const float4* Wt, float* Gs, char* 
 #pragma unroll
         for (int c = 0; c < E / 2; ++c) dv[c] = __ffma2_rn(w2, go[q][u][c], dv[c]);
       }
-      if (real) {
 #pragma unroll
-        for (int c = 0; c < E / 2; c += 2)
-          red_add_f32x4(gp + u * (G * E) + 2 * c, dv[c].x, dv[c].y, dv[c + 1].x, dv[c + 1].y);
-      }
+      for (int c = 0; c < E / 2; c += 2)
+        GvRed<GV>::add4(gp + u * (G * E) + 2 * c, real, dv[c].x, dv[c].y, dv[c + 1].x, dv[c + 1].y,
+                        gv_scale);
       // this lane's share of <grad_out[q], value row>
       float v[E];
       Unit<T>::unpack_raw(r == 0 ? b0[u] : b1[u], v);
@@ -615,13 +615,14 @@ __device__ __forceinline__ void bwd_win_step(const float4* Wt, float* Gs, char* 
   Gs[t * 4 + j] = tot;   // (row t + (j >> 2), query j & 3)
 }
 
-template <typename T, int NU, int G>
+template <typename T, int NU, int G, typename GV = float>
 __global__ void __launch_bounds__(kWinThreads, 4)
 msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ shapes,
                     const int64_t* __restrict__ lsi, const T* __restrict__ loc,
                     const T* __restrict__ aw, const T* __restrict__ gout,
-                    float* __restrict__ gvalue, T* __restrict__ gloc, T* __restrict__ gaw, Dims d,
-                    int nqc, int units) {
+                    GV* __restrict__ gvalue, T* __restrict__ gloc, T* __restrict__ gaw, Dims d,
+                    int nqc, int units, const DetHeader* __restrict__ det) {
+  const float gv_scale = det ? (float)det->scale : 1.f;   // fixed-point accumulation (msda_det.cuh)
   static_assert(G == 8, "two rows x four queries are transpose-reduced over 8 lanes");
   using Raw = typename Unit<T>::Raw;
   constexpr int E = Unit<T>::E;
@@ -652,8 +653,9 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
   if (!one_d) {
     for (; w.u < uend; w = win_next_unit(w, ust, nqc, d.M)) {
       const int q0 = w.q0(QPU) + gq;
-      bwd_body<T, NU, G, 4>(value, loc, aw, gout, gvalue, gloc, gaw, d, w.b, w.m, q0,
-                            min(q0 + kWinQ, d.Lq), 1, s_lvl, reinterpret_cast<TapMeta<4>*>(s_grp));
+      bwd_body<T, NU, G, 4, GV>(value, loc, aw, gout, gvalue, gloc, gaw, d, w.b, w.m, q0,
+                                min(q0 + kWinQ, d.Lq), 1, s_lvl, reinterpret_cast<TapMeta<4>*>(s_grp),
+                                gv_scale);
       __syncwarp();
     }
     return;
@@ -717,10 +719,10 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
     win_load_row_first<T, NU, G>(vbb, rc.w, buf[3]);
     for (int t = 0; t < wmax; t += NS) {
       const uint4 rn = *reinterpret_cast<const uint4*>(rowoff + t + NS);
-      bwd_win_step<T, NU, G>(Wt, Gs, gvbb, rc.x, rc.y, t, rr, j, buf[0], buf[1], go);
+      bwd_win_step<T, NU, G, GV>(Wt, Gs, gvbb, rc.x, rc.y, t, rr, j, buf[0], buf[1], go, gv_scale);
       win_load_row<T, NU, G>(vbb, rn.x, t + NS + 0 < rl, buf[0]);
       win_load_row<T, NU, G>(vbb, rn.y, t + NS + 1 < rl, buf[1]);
-      bwd_win_step<T, NU, G>(Wt, Gs, gvbb, rc.z, rc.w, t + 2, rr, j, buf[2], buf[3], go);
+      bwd_win_step<T, NU, G, GV>(Wt, Gs, gvbb, rc.z, rc.w, t + 2, rr, j, buf[2], buf[3], go, gv_scale);
       win_load_row<T, NU, G>(vbb, rn.z, t + NS + 2 < rl, buf[2]);
       win_load_row<T, NU, G>(vbb, rn.w, t + NS + 3 < rl, buf[3]);
       rc = rn;
@@ -759,8 +761,8 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
           WinPts<T>::st(gloc + (grp_me * LP + l * kWinP) * 2, gaw + grp_me * LP + l * kWinP, gx, gy, ga);
       }
     } else {
-      bwd_body<T, NU, G, 2>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q0, q0 + nq, 1, s_lvl,
-                            reinterpret_cast<TapMeta<2>*>(s_grp));
+      bwd_body<T, NU, G, 2, GV>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q0, q0 + nq, 1, s_lvl,
+                                reinterpret_cast<TapMeta<2>*>(s_grp), gv_scale);
     }
     __syncwarp();
     cur ^= 1;
