@@ -131,7 +131,8 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    steps, warmup = min(args.steps, 20), min(args.warmup, 3)
+    # at least one untimed step: the first one pays thread-pool start-up and first-touch of ~1 GB
+    steps, warmup = min(args.steps, 20), max(1, min(args.warmup, 3))
     qps, ms, cores, sample = cpu_leg(args.workload, steps, warmup, args.dist)
     from mfl_b200 import synthetic
     w = synthetic.WORKLOADS[args.workload]
