@@ -196,6 +196,18 @@ int msda_dam_scatter(const void* loc, const void* aw, const int64_t* level_sizes
                      int64_t BL, int64_t Q, int64_t M, int64_t L, int64_t P, int64_t S,
                      int loc_cols, int dtype, void* stream);
 
+/*
+ * Encoder reference points (DeformableTransformerEncoder.get_reference_points,
+ * models/deformable/unimodal_deformable_transformer.py:259-276 and its copies in
+ * the multimodal and sparse encoders):
+ *   out[n, s, l] = (t + 0.5) / (valid_ratios[n, k] * T_k) * valid_ratios[n, l]
+ * for token s = level_start_k + t.  level_sizes [L] int64 and valid_ratios [N,L]
+ * fp32 on the device; out [N,S,L] fp32 (the reference returns it as [N,S,L,1]).
+ * SURVEY.md section 8(f) row 4.
+ */
+int msda_encoder_reference_points(const int64_t* level_sizes, const float* valid_ratios,
+                                  float* out, int64_t N, int64_t S, int64_t L, void* stream);
+
 /* Last CUDA runtime error code seen by the calling thread inside this library
  * (cudaError_t as int) and its string. */
 int msda_last_cuda_error(void);

@@ -641,4 +641,19 @@ int msda_dam_scatter(const void* loc, const void* aw, const int64_t* level_sizes
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
 }
 
+
+int msda_encoder_reference_points(const int64_t* level_sizes, const float* valid_ratios, float* out,
+                                  int64_t N, int64_t S, int64_t L, void* stream) {
+  if (N < 0 || S < 0 || L <= 0) return MSDA_ERR_BAD_SHAPE;
+  if (S >= (int64_t(1) << 31) || L >= (int64_t(1) << 20) || (N > 0 && S > 0 && N >= (int64_t(1) << 40) / S))
+    return MSDA_ERR_TOO_LARGE;
+  if (N == 0 || S == 0) return MSDA_OK;
+  if (!level_sizes || !valid_ratios || !out) return MSDA_ERR_NULL_POINTER;
+  const long long total = (long long)(N * S);
+  msda_reference_points_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      level_sizes, valid_ratios, out, total, (int)S, (int)L);
+  const cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
+}
+
 }  // extern "C"

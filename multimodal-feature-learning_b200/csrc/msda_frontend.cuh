@@ -333,4 +333,30 @@ msda_frontend_bwd_lanes_kernel(const T* __restrict__ off, const T* __restrict__ 
   }
 }
 
+
+// ---- encoder reference points -------------------------------------------------
+// DeformableTransformerEncoder.get_reference_points
+// (models/deformable/unimodal_deformable_transformer.py:259-276; same code in the
+// multimodal and sparse encoders): token t of level k, for every level l,
+//   ref[n, s, l] = (t + 0.5) / (valid_ratio[n, k] * T_k) * valid_ratio[n, l]
+// The reference builds it with a Python loop over a device tensor of level sizes
+// (one host sync and four small kernels per level, every forward); here one
+// thread per (batch item, token).
+__global__ void __launch_bounds__(256)
+msda_reference_points_kernel(const int64_t* __restrict__ t_lvl, const float* __restrict__ vr,
+                             float* __restrict__ out, long long total, int S, int L) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= total) return;
+  const long long n = i / S;
+  int t = (int)(i - n * S), k = 0, T = (int)t_lvl[0];
+  while (k + 1 < L && t >= T) {
+    t -= T;
+    ++k;
+    T = (int)t_lvl[k];
+  }
+  const float* v = vr + n * L;
+  const float base = ((float)t + 0.5f) / (v[k] * (float)T);
+  for (int l = 0; l < L; ++l) out[i * L + l] = base * v[l];
+}
+
 }  // namespace msda

@@ -1,4 +1,6 @@
-# mirrors the part of the reference's utils/ that touches the hot path's data (utils/dam.py)
+# mirrors the parts of the reference that feed the hot path directly: utils/dam.py and the
+# encoders' get_reference_points
 from .dam import attn_map_to_flat_grid, compute_corr, idx_to_flat_grid
+from .reference_points import get_reference_points
 
-__all__ = ["attn_map_to_flat_grid", "compute_corr", "idx_to_flat_grid"]
+__all__ = ["attn_map_to_flat_grid", "compute_corr", "idx_to_flat_grid", "get_reference_points"]

@@ -49,3 +49,16 @@ def frontend_pytorch(sampling_offsets, attention_logits, reference_points, level
         raise ValueError("Last dim of reference_points must be 1 or 2")
     loc = torch.stack((x, 0.5 * x.new_ones(x.shape)), -1)
     return loc, aw
+
+
+def reference_points_pytorch(temporal_shapes, valid_ratios):
+    """Restatement of DeformableTransformerEncoder.get_reference_points
+    (models/deformable/unimodal_deformable_transformer.py:259-276): token t of level k gets, for
+    every level l, (t + 0.5) / (valid_ratio_k * T_k) * valid_ratio_l.  Oracle for
+    msda_encoder_reference_points."""
+    cols = []
+    for k, t_k in enumerate(int(t) for t in temporal_shapes.tolist()):
+        centre = torch.arange(t_k, dtype=torch.float32, device=valid_ratios.device) + 0.5
+        cols.append(centre[None] / (valid_ratios[:, None, k] * t_k))
+    ref = torch.cat(cols, 1)
+    return (ref[:, :, None] * valid_ratios[:, None])[..., None]

@@ -8,6 +8,7 @@ It imports, by file path and unmodified,
   * models/modules/attention.py                  (ms_deform_attn_core_pytorch, 1-D live twin, :331-383;
                                                    MSDeformAttn, the module every transformer builds, :394-511)
   * utils/dam.py                                 (attn_map_to_flat_grid, :20-73)
+  * models/deformable/unimodal_deformable_transformer.py (get_reference_points, :259-276)
 runs them on seeded inputs (the tiny case reproduces models/ops/test.py:23-44:
 N=1, M=2, D=2, Lq=2, L=2, P=2, shapes (6,4),(3,2), torch.manual_seed(3)) and
 stores inputs, outputs and autograd gradients.
@@ -156,7 +157,26 @@ def make_dam_case(name, seed):
     print(name, tuple(out.shape))
 
 
+def make_refpoints_case(name, seed):
+    """DeformableTransformerEncoder.get_reference_points
+    (models/deformable/unimodal_deformable_transformer.py:259-276), imported through a stub
+    `models` package (models/__init__.py pulls in dependencies this container lacks)."""
+    import importlib
+    import types
+    stub = types.ModuleType("models")
+    stub.__path__ = [os.path.join(REF, "models")]
+    sys.modules["models"] = stub
+    udt = importlib.import_module("models.deformable.unimodal_deformable_transformer")
+    torch.manual_seed(seed)
+    T = torch.tensor([24, 12, 6, 3], dtype=torch.long)
+    vr = torch.rand(3, 4) * 0.6 + 0.4
+    out = udt.DeformableTransformerEncoder.get_reference_points(T, vr, "cpu")
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), T=T.numpy(), vr=vr.numpy(), out=out.numpy())
+    print(name, tuple(out.shape))
+
+
 def main():
+    make_refpoints_case("refpoints_f32", 61)
     make_module_case("module_live_ref1_f32", 41, 1, True)
     make_module_case("module_live_ref2_f32", 42, 2, False)
     make_dam_case("dam_f32", 51)
