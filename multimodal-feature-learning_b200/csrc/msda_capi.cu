@@ -96,14 +96,14 @@ int launch_fwd_fast(const void* value, const int64_t* shapes, const int64_t* lsi
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
 }
 
-template <typename T, int NU, int G, typename GV = float>
+template <typename T, int NU, int G, typename GV = float, typename U = Unit<T>>
 int launch_bwd_fast(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
                     const void* aw, const void* gout, GV* gvalue, void* gloc, void* gaw,
                     const Dims& d, unsigned flags, cudaStream_t st, const DetHeader* det = nullptr) {
   const int qtile = pick_qtile(d, G, flags);
   const int nqc = (d.Lq + qtile - 1) / qtile;
   const int64_t tiles = (int64_t)d.N * d.M * nqc;
-  msda_bwd_fast_kernel<T, NU, G, GV><<<(unsigned)tiles, kFastThreads, 0, st>>>(
+  msda_bwd_fast_kernel<T, NU, G, GV, U><<<(unsigned)tiles, kFastThreads, 0, st>>>(
       (const T*)value, shapes, lsi, (const T*)loc, (const T*)aw, (const T*)gout, gvalue, (T*)gloc,
       (T*)gaw, d, qtile, nqc, det);
   const cudaError_t e = cudaGetLastError();
@@ -167,7 +167,7 @@ int launch_fwd_win(const void* value, const int64_t* shapes, const int64_t* lsi,
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
 }
 
-template <typename T, int NU, int G, typename GV = float>
+template <typename T, int NU, int G, typename GV = float, typename U = Unit<T>>
 int launch_bwd_win(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
                    const void* aw, const void* gout, GV* gvalue, void* gloc, void* gaw,
                    const Dims& d, cudaStream_t st, const DetHeader* det = nullptr) {
@@ -175,7 +175,7 @@ int launch_bwd_win(const void* value, const int64_t* shapes, const int64_t* lsi,
   const int nqc = (d.Lq + qpu - 1) / qpu;
   const long long units = (long long)d.N * d.M * nqc;
   constexpr size_t smem = (size_t)(kWinThreads / G) * WinSmem<T, 2, false, 0>::kGroupBytes;
-  auto kern = msda_bwd_win_kernel<T, NU, G, GV>;
+  auto kern = msda_bwd_win_kernel<T, NU, G, GV, U>;
   int grid = 1;
   const int rc = win_grid(kern, smem, units, &grid);
   if (rc != MSDA_OK) return rc;
@@ -510,9 +510,10 @@ int msda_backward(const void* value, const int64_t* spatial_shapes, const int64_
   int r = MSDA_OK;
   if (fast && win_applies(d, dtype, flags)) {
     if (dtype == MSDA_BF16)
-      r = launch_bwd_win<__nv_bfloat16, 1, 8>(value, spatial_shapes, level_start_index,
-                                              sampling_loc, attn_weight, grad_output, (float*)acc,
-                                              grad_sampling_loc, grad_attn_weight, d, st);
+      // two 8-byte units per lane: dense 128-byte reds into the fp32 image (msda_fast.cuh)
+      r = launch_bwd_win<__nv_bfloat16, 2, 8, float, UnitBf16x4>(
+          value, spatial_shapes, level_start_index, sampling_loc, attn_weight, grad_output,
+          (float*)acc, grad_sampling_loc, grad_attn_weight, d, st);
     else if (D == 64)
       r = launch_bwd_win<float, 2, 8>(value, spatial_shapes, level_start_index, sampling_loc,
                                       attn_weight, grad_output, (float*)acc, grad_sampling_loc,
@@ -525,6 +526,10 @@ int msda_backward(const void* value, const int64_t* spatial_shapes, const int64_
     r = [&]() -> int {
       FastPlan plan;
       fast_plan(D, dtype, &plan);
+      if (dtype == MSDA_BF16 && plan.nu == 1 && plan.g == 8)   // D = 64: dense reds, as above
+        return launch_bwd_fast<__nv_bfloat16, 2, 8, float, UnitBf16x4>(
+            value, spatial_shapes, level_start_index, sampling_loc, attn_weight, grad_output,
+            (float*)acc, grad_sampling_loc, grad_attn_weight, d, flags, st);
       MSDA_DISPATCH_FAST(dtype, launch_bwd_fast, value, spatial_shapes, level_start_index,
                          sampling_loc, attn_weight, grad_output, (float*)acc, grad_sampling_loc,
                          grad_attn_weight, d, flags, st);

@@ -101,6 +101,8 @@ template <> struct LocLoad<__nv_bfloat16> {
 template <typename T> struct Unit;
 template <> struct Unit<float> {
   static constexpr int E = 4;
+  static constexpr int RW = 4;      // raw 32-bit words of a unit as loaded
+  static constexpr int BYTES = 16;
   static __device__ __forceinline__ void ldg(const float* p, bool pred, float (&v)[4]) {
     asm("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
         "mov.f32 %0, 0f00000000;\n\tmov.f32 %1, 0f00000000;\n\t"
@@ -139,6 +141,8 @@ template <> struct Unit<float> {
 };
 template <> struct Unit<__nv_bfloat16> {
   static constexpr int E = 8;
+  static constexpr int RW = 4;
+  static constexpr int BYTES = 16;
   static __device__ __forceinline__ void unpack(const uint32_t (&w)[4], float (&v)[8]) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
@@ -181,6 +185,47 @@ template <> struct Unit<__nv_bfloat16> {
   }
   static __device__ __forceinline__ void st_stream(__nv_bfloat16* p, const float (&v)[8]) {
     VecIO<__nv_bfloat16, 8>::st_stream(p, v);
+  }
+};
+
+// 8-byte units of 4 bf16, for the backward kernels: with two of them per lane (NU = 2, 32
+// channels apart) a lane's slice of the fp32 accumulation image is two 16-byte pieces 128 bytes
+// apart, so each 128-bit red of an 8-lane group covers a dense 128 bytes.  (With the 16-byte
+// unit a lane owns 32 contiguous bytes of the image and every red instruction half-fills eight
+// 32-byte sectors: twice the L2 atomic work for the same bytes.)
+struct UnitBf16x4 {
+  static constexpr int E = 4;
+  static constexpr int RW = 2;
+  static constexpr int BYTES = 8;
+  using Raw = uint32_t;
+  static __device__ __forceinline__ void unpack(const uint32_t (&w)[2], float (&v)[4]) {
+    v[0] = __uint_as_float(w[0] << 16); v[1] = __uint_as_float(w[0] & 0xffff0000u);
+    v[2] = __uint_as_float(w[1] << 16); v[3] = __uint_as_float(w[1] & 0xffff0000u);
+  }
+  static __device__ __forceinline__ void ldg(const __nv_bfloat16* p, bool pred, float (&v)[4]) {
+    uint32_t w[2];
+    asm("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %3, 0;\n\t"
+        "mov.b32 %0, 0;\n\tmov.b32 %1, 0;\n\t"
+        "@p ld.global.nc.v2.b32 {%0, %1}, [%2];\n\t}"
+        : "=&r"(w[0]), "=&r"(w[1])
+        : "l"(p), "r"((int)pred));
+    unpack(w, v);
+  }
+  static __device__ __forceinline__ void ldg_keep(const char* p, bool pred, uint32_t (&w)[2]) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %3, 0;\n\t"
+                 "@p ld.global.nc.v2.b32 {%0, %1}, [%2];\n\t}"
+                 : "+r"(w[0]), "+r"(w[1])
+                 : "l"(p), "r"((int)pred));
+  }
+  static __device__ __forceinline__ void ldg_raw(const char* p, uint32_t (&w)[2]) {
+    const uint2 t = __ldg(reinterpret_cast<const uint2*>(p));
+    w[0] = t.x; w[1] = t.y;
+  }
+  static __device__ __forceinline__ void unpack_raw(const uint32_t (&w)[2], float (&v)[4]) { unpack(w, v); }
+  static __device__ __forceinline__ void ld_stream(const __nv_bfloat16* p, float (&v)[4]) {
+    const uint2 t = __ldcs(reinterpret_cast<const uint2*>(p));
+    const uint32_t w[2] = {t.x, t.y};
+    unpack(w, v);
   }
 };
 
@@ -355,14 +400,14 @@ msda_fwd_fast_kernel(const T* __restrict__ value, const int64_t* __restrict__ sh
 // the G points of the chunk and one transpose-reduce hands point j's totals to
 // lane j, which owns that point's geometry and writes its three gradients
 // (.cuh:115-159 for the math).
-template <typename T, int NU, int G, int NT, typename GV = float>
+template <typename T, int NU, int G, int NT, typename GV = float, typename U = Unit<T>>
 __device__ __forceinline__ void bwd_body(const T* __restrict__ value, const T* __restrict__ loc,
                                          const T* __restrict__ aw, const T* __restrict__ gout,
                                          GV* __restrict__ gvalue, T* __restrict__ gloc,
                                          T* __restrict__ gaw, const Dims& d, int b, int m,
                                          int q_first, int q_end, int q_step, const int* s_lvl,
                                          TapMeta<NT>* s_meta, float gv_scale = 1.f) {
-  constexpr int E = Unit<T>::E;
+  constexpr int E = U::E;
   const int lane = threadIdx.x & 31;
   const int j = threadIdx.x % G;
   const unsigned mask = group_mask<G>(lane);
@@ -378,7 +423,7 @@ __device__ __forceinline__ void bwd_body(const T* __restrict__ value, const T* _
     const T* aw_g = aw + grp * LP;
     float go[NU][E];
 #pragma unroll
-    for (int u = 0; u < NU; ++u) Unit<T>::ld_stream(gout + grp * d.D + u * (G * E) + j * E, go[u]);
+    for (int u = 0; u < NU; ++u) U::ld_stream(gout + grp * d.D + u * (G * E) + j * E, go[u]);
 
     for (int base = 0; base < LP; base += G) {
       const int pt = base + j;
@@ -400,7 +445,7 @@ __device__ __forceinline__ void bwd_body(const T* __restrict__ value, const T* _
 #pragma unroll
           for (int u = 0; u < NU; ++u) {
             float v[E];
-            Unit<T>::ldg(vb + tm.off[k] + u * (G * E), live, v);
+            U::ldg(vb + tm.off[k] + u * (G * E), live, v);
 #pragma unroll
             for (int c = 0; c < E; ++c) s = fmaf(go[u][c], v[c], s);
 #pragma unroll
@@ -426,7 +471,7 @@ __device__ __forceinline__ void bwd_body(const T* __restrict__ value, const T* _
   }
 }
 
-template <typename T, int NU, int G, typename GV = float>
+template <typename T, int NU, int G, typename GV = float, typename U = Unit<T>>
 __global__ void __launch_bounds__(kFastThreads)
 msda_bwd_fast_kernel(const T* __restrict__ value, const int64_t* __restrict__ shapes,
                      const int64_t* __restrict__ lsi, const T* __restrict__ loc,
@@ -448,10 +493,10 @@ msda_bwd_fast_kernel(const T* __restrict__ value, const int64_t* __restrict__ sh
   constexpr int NG = kFastThreads / G;
   const int gi = threadIdx.x / G;
   if (s_one_d)
-    bwd_body<T, NU, G, 2, GV>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q_begin + gi, q_end,
+    bwd_body<T, NU, G, 2, GV, U>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q_begin + gi, q_end,
                               NG, s_lvl, reinterpret_cast<TapMeta<2>*>(s_meta) + gi * G, gv_scale);
   else
-    bwd_body<T, NU, G, 4, GV>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q_begin + gi, q_end,
+    bwd_body<T, NU, G, 4, GV, U>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q_begin + gi, q_end,
                               NG, s_lvl, s_meta + gi * G, gv_scale);
 }
 

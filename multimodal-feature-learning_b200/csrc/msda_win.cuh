@@ -405,23 +405,23 @@ __device__ __forceinline__ bool win_build(const char* pts, const Dims& d, bool h
 // One value row (this lane's NU 16-byte units) as loaded: kept raw until used.
 // The load is predicated WITHOUT zero-fill: a skipped load leaves the previous
 // (finite) contents, which only ever meet zero weights.
-template <typename T, int NU, int G>
+template <typename T, int NU, int G, typename U = Unit<T>>
 __device__ __forceinline__ void win_load_row(const char* vbb, unsigned off, bool pred,
-                                             typename Unit<T>::Raw (&buf)[NU][4]) {
+                                             typename U::Raw (&buf)[NU][U::RW]) {
   const char* p = win_addr(vbb, off);
 #pragma unroll
-  for (int u = 0; u < NU; ++u) Unit<T>::ldg_keep(p + u * (G * 16), pred, buf[u]);
+  for (int u = 0; u < NU; ++u) U::ldg_keep(p + u * (G * U::BYTES), pred, buf[u]);
 }
 
 // The first kWinStages rows of a plan: rowoff always holds a valid row there
 // (win_build pads with the block's last row, or row 0 of the slab), so these
 // loads need no predicate and the buffers no initial value.
-template <typename T, int NU, int G>
+template <typename T, int NU, int G, typename U = Unit<T>>
 __device__ __forceinline__ void win_load_row_first(const char* vbb, unsigned off,
-                                                   typename Unit<T>::Raw (&buf)[NU][4]) {
+                                                   typename U::Raw (&buf)[NU][U::RW]) {
   const char* p = win_addr(vbb, off);
 #pragma unroll
-  for (int u = 0; u < NU; ++u) Unit<T>::ldg_raw(p + u * (G * 16), buf[u]);
+  for (int u = 0; u < NU; ++u) U::ldg_raw(p + u * (G * U::BYTES), buf[u]);
 }
 
 constexpr int kWinStages = 4;   // value rows in flight per lane (8 measured the same: 53.7 us at ENC)
@@ -561,14 +561,14 @@ msda_fwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
 // One step = the two packed rows t, t+1: grad_value rows leave as 128-bit reds,
 // the 2 x 4 dots <grad_out[q], value row> are transpose-reduced over the 8
 // lanes; lane (qi, h) ends with the total for (row t+h, query qi).
-template <typename T, int NU, int G, typename GV = float>
+template <typename T, int NU, int G, typename GV = float, typename U = Unit<T>>
 __device__ __forceinline__ void bwd_win_step(const float4* Wt, float* Gs, char* gvbb, unsigned ro0,
                                              unsigned ro1, int t, int rt, int j,
-                                             const typename Unit<T>::Raw (&b0)[NU][4],
-                                             const typename Unit<T>::Raw (&b1)[NU][4],
-                                             const float2 (&go)[kWinQ][NU][Unit<T>::E / 2],
+                                             const typename U::Raw (&b0)[NU][U::RW],
+                                             const typename U::Raw (&b1)[NU][U::RW],
+                                             const float2 (&go)[kWinQ][NU][U::E / 2],
                                              float gv_scale) {
-  constexpr int E = Unit<T>::E;
+  constexpr int E = U::E;
   constexpr unsigned FULL = 0xffffffffu;
   constexpr unsigned kAccScale = (unsigned)(sizeof(GV) / sizeof(T));  // accumulation image of a T slab
   float x[2 * kWinQ];
@@ -600,7 +600,7 @@ __device__ __forceinline__ void bwd_win_step(const float4* Wt, float* Gs, char* 
                         gv_scale);
       // this lane's share of <grad_out[q], value row>
       float v[E];
-      Unit<T>::unpack_raw(r == 0 ? b0[u] : b1[u], v);
+      U::unpack_raw(r == 0 ? b0[u] : b1[u], v);
 #pragma unroll
       for (int q = 0; q < kWinQ; ++q)
 #pragma unroll
@@ -615,7 +615,7 @@ __device__ __forceinline__ void bwd_win_step(const float4* Wt, float* Gs, char* 
   Gs[t * 4 + j] = tot;   // (row t + (j >> 2), query j & 3)
 }
 
-template <typename T, int NU, int G, typename GV = float>
+template <typename T, int NU, int G, typename GV = float, typename U = Unit<T>>
 __global__ void __launch_bounds__(kWinThreads, 4)
 msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ shapes,
                     const int64_t* __restrict__ lsi, const T* __restrict__ loc,
@@ -624,8 +624,8 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
                     int nqc, int units, const DetHeader* __restrict__ det) {
   const float gv_scale = det ? (float)det->scale : 1.f;   // fixed-point accumulation (msda_det.cuh)
   static_assert(G == 8, "two rows x four queries are transpose-reduced over 8 lanes");
-  using Raw = typename Unit<T>::Raw;
-  constexpr int E = Unit<T>::E;
+  using Raw = typename U::Raw;
+  constexpr int E = U::E;
   using SM = WinSmem<T, 2, false, 0>;
   constexpr int NH = G / 4;
   constexpr int NS = 4;
@@ -653,7 +653,7 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
   if (!one_d) {
     for (; w.u < uend; w = win_next_unit(w, ust, nqc, d.M)) {
       const int q0 = w.q0(QPU) + gq;
-      bwd_body<T, NU, G, 4, GV>(value, loc, aw, gout, gvalue, gloc, gaw, d, w.b, w.m, q0,
+      bwd_body<T, NU, G, 4, GV, U>(value, loc, aw, gout, gvalue, gloc, gaw, d, w.b, w.m, q0,
                                 min(q0 + kWinQ, d.Lq), 1, s_lvl, reinterpret_cast<TapMeta<4>*>(s_grp),
                                 gv_scale);
       __syncwarp();
@@ -670,18 +670,18 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
     const char* pts = pts_buf + cur * SM::kPtsBytes;
     // grad_out of the 4 queries (this lane's channels): requested first, used
     // after the window build, whose work covers their way from HBM
-    Raw gor[kWinQ][NU][4];
+    Raw gor[kWinQ][NU][U::RW];
     {
       const char* gb = reinterpret_cast<const char*>(
-          gout + (((size_t)b * d.Lq + q0) * d.M + m) * d.D) + j * 16;
+          gout + (((size_t)b * d.Lq + q0) * d.M + m) * d.D) + j * U::BYTES;
       const unsigned qstride = (unsigned)(d.M * d.D) * (unsigned)sizeof(T);
 #pragma unroll
       for (int q = 0; q < kWinQ; ++q)
 #pragma unroll
         for (int uu = 0; uu < NU; ++uu) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) gor[q][uu][k] = Raw(0);
-          Unit<T>::ldg_keep(win_addr(gb, q * qstride) + uu * (G * 16), q < nq, gor[q][uu]);
+          for (int k = 0; k < U::RW; ++k) gor[q][uu][k] = Raw(0);
+          U::ldg_keep(win_addr(gb, q * qstride) + uu * (G * U::BYTES), q < nq, gor[q][uu]);
         }
     }
     win_cp_wait_all();
@@ -699,32 +699,32 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
 #pragma unroll
       for (int uu = 0; uu < NU; ++uu) {
         float t[E];
-        Unit<T>::unpack_raw(gor[q][uu], t);
+        U::unpack_raw(gor[q][uu], t);
 #pragma unroll
         for (int c = 0; c < E / 2; ++c) go[q][uu][c] = make_float2(t[2 * c], t[2 * c + 1]);
       }
 
     const size_t voff = ((size_t)b * d.S * d.M + m) * d.D;
-    const char* vbb = reinterpret_cast<const char*>(value + voff) + j * 16;
+    const char* vbb = reinterpret_cast<const char*>(value + voff) + j * U::BYTES;
     char* gvbb = reinterpret_cast<char*>(gvalue + voff + j * E);
 
     // NS rows in flight per lane
     const int rl = rt;
-    Raw buf[NS][NU][4];
+    Raw buf[NS][NU][U::RW];
     const int rr = rt;                      // rows whose grad_value reds are issued
     uint4 rc = *reinterpret_cast<const uint4*>(rowoff);
-    win_load_row_first<T, NU, G>(vbb, rc.x, buf[0]);
-    win_load_row_first<T, NU, G>(vbb, rc.y, buf[1]);
-    win_load_row_first<T, NU, G>(vbb, rc.z, buf[2]);
-    win_load_row_first<T, NU, G>(vbb, rc.w, buf[3]);
+    win_load_row_first<T, NU, G, U>(vbb, rc.x, buf[0]);
+    win_load_row_first<T, NU, G, U>(vbb, rc.y, buf[1]);
+    win_load_row_first<T, NU, G, U>(vbb, rc.z, buf[2]);
+    win_load_row_first<T, NU, G, U>(vbb, rc.w, buf[3]);
     for (int t = 0; t < wmax; t += NS) {
       const uint4 rn = *reinterpret_cast<const uint4*>(rowoff + t + NS);
-      bwd_win_step<T, NU, G, GV>(Wt, Gs, gvbb, rc.x, rc.y, t, rr, j, buf[0], buf[1], go, gv_scale);
-      win_load_row<T, NU, G>(vbb, rn.x, t + NS + 0 < rl, buf[0]);
-      win_load_row<T, NU, G>(vbb, rn.y, t + NS + 1 < rl, buf[1]);
-      bwd_win_step<T, NU, G, GV>(Wt, Gs, gvbb, rc.z, rc.w, t + 2, rr, j, buf[2], buf[3], go, gv_scale);
-      win_load_row<T, NU, G>(vbb, rn.z, t + NS + 2 < rl, buf[2]);
-      win_load_row<T, NU, G>(vbb, rn.w, t + NS + 3 < rl, buf[3]);
+      bwd_win_step<T, NU, G, GV, U>(Wt, Gs, gvbb, rc.x, rc.y, t, rr, j, buf[0], buf[1], go, gv_scale);
+      win_load_row<T, NU, G, U>(vbb, rn.x, t + NS + 0 < rl, buf[0]);
+      win_load_row<T, NU, G, U>(vbb, rn.y, t + NS + 1 < rl, buf[1]);
+      bwd_win_step<T, NU, G, GV, U>(Wt, Gs, gvbb, rc.z, rc.w, t + 2, rr, j, buf[2], buf[3], go, gv_scale);
+      win_load_row<T, NU, G, U>(vbb, rn.z, t + NS + 2 < rl, buf[2]);
+      win_load_row<T, NU, G, U>(vbb, rn.w, t + NS + 3 < rl, buf[3]);
       rc = rn;
     }
     __syncwarp();
@@ -761,7 +761,7 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
           WinPts<T>::st(gloc + (grp_me * LP + l * kWinP) * 2, gaw + grp_me * LP + l * kWinP, gx, gy, ga);
       }
     } else {
-      bwd_body<T, NU, G, 2, GV>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q0, q0 + nq, 1, s_lvl,
+      bwd_body<T, NU, G, 2, GV, U>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, q0, q0 + nq, 1, s_lvl,
                                 reinterpret_cast<TapMeta<2>*>(s_grp), gv_scale);
     }
     __syncwarp();
