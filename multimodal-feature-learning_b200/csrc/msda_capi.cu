@@ -174,7 +174,7 @@ int launch_bwd_win(const void* value, const int64_t* shapes, const int64_t* lsi,
   constexpr int qpu = (32 / G) * kWinQ;                 // queries per unit (one warp)
   const int nqc = (d.Lq + qpu - 1) / qpu;
   const long long units = (long long)d.N * d.M * nqc;
-  constexpr size_t smem = (size_t)(kWinThreads / G) * WinSmem<T, 2, false, 0>::kGroupBytes;
+  constexpr size_t smem = (size_t)(kWinThreads / G) * WinSmem<T, 1, false, 0>::kGroupBytes;
   auto kern = msda_bwd_win_kernel<T, NU, G, GV, U>;
   int grid = 1;
   const int rc = win_grid(kern, smem, units, &grid);

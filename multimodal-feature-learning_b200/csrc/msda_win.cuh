@@ -41,7 +41,7 @@ namespace msda {
 constexpr int kWinQ = 4;         // queries per block
 constexpr int kWinP = 4;         // points per level (template-free fast case)
 constexpr int kWinMaxL = 4;      // levels
-constexpr int kWinCap = 88;      // packed rows per block, multiple of 4
+constexpr int kWinCap = 72;      // packed rows per block, multiple of 8 (the encoder shape peaks at 70 rows)
 constexpr int kWinFillPad = 8;   // the row loops run to a multiple of this and read that far ahead
 constexpr int kWinRows = kWinCap + kWinFillPad;  // + padding rows read by the software pipeline
 constexpr int kWinThreads = 128;     // 4 warps = 4 adjacent units per CTA (they share rows in L1)
@@ -626,7 +626,7 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
   static_assert(G == 8, "two rows x four queries are transpose-reduced over 8 lanes");
   using Raw = typename U::Raw;
   constexpr int E = U::E;
-  using SM = WinSmem<T, 2, false, 0>;
+  using SM = WinSmem<T, 1, false, 0>;
   constexpr int NH = G / 4;
   constexpr int NS = 4;
   constexpr int LPL = (kWinMaxL * 4 + G - 1) / G;
@@ -643,7 +643,7 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
   const int gq = (gi % (32 / G)) * kWinQ;
   const int qi = j & 3, h = j >> 2;
   char* s_grp = s_dyn + gi * SM::kGroupBytes;
-  char* pts_buf = s_grp + SM::kPlanBytes;                       // two buffers of kPtsBytes
+  char* pts_buf = s_grp + SM::kPlanBytes;   // one staging buffer: less shared memory = more L1
   const float4* Wt = reinterpret_cast<const float4*>(s_grp);
   float* Gs = reinterpret_cast<float*>(s_grp);  // the dots G[t][qi] overwrite Wt[t][qi] step by step
   const unsigned* rowoff = reinterpret_cast<const unsigned*>(s_grp + 16 * kWinRows);
@@ -660,14 +660,13 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
     }
     return;
   }
-  int cur = 0;
   if (w.u < uend) win_fetch_points<T>(loc, aw, d, w.b, w.m, w.q0(QPU) + gq, pts_buf, j);
   win_cp_commit();
   while (w.u < uend) {
     const int b = w.b, m = w.m, q0 = w.q0(QPU) + gq;
     const int nq = max(min(kWinQ, d.Lq - q0), 0);
     const bool have_q = qi < nq;
-    const char* pts = pts_buf + cur * SM::kPtsBytes;
+    const char* pts = pts_buf;
     // grad_out of the 4 queries (this lane's channels): requested first, used
     // after the window build, whose work covers their way from HBM
     Raw gor[kWinQ][NU][U::RW];
@@ -688,10 +687,11 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
     __syncwarp();
     int tb[LPL], rt, wmax;
     const bool ok = win_build<T, G>(pts, d, have_q, s_lvl, s_grp, j, lane & ~(G - 1), tb, rt, wmax);
-    // next unit's points into the other buffer
+    // win_build has consumed the staged points: the buffer takes the next unit's; the epilogue
+    // reads this unit's points again from global memory (L2 hits)
     const WinUnit wn = win_next_unit(w, ust, nqc, d.M);
     if (wn.u < uend)
-      win_fetch_points<T>(loc, aw, d, wn.b, wn.m, wn.q0(QPU) + gq, pts_buf + (cur ^ 1) * SM::kPtsBytes, j);
+      win_fetch_points<T>(loc, aw, d, wn.b, wn.m, wn.q0(QPU) + gq, pts_buf, j);
     win_cp_commit();
     float2 go[kWinQ][NU][E / 2];
 #pragma unroll
@@ -739,7 +739,8 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
         const bool active = have_q && l < d.L;
         const int ls = l < d.L ? l : 0;
         float x[4], y[4], a[4];
-        WinPts<T>::ld_smem(win_pts_loc<T>(pts, d.L, qi, ls), win_pts_aw<T>(pts, d.L, qi, ls), x, y, a);
+        // the staging buffer already belongs to the next unit: the points come from L2 again
+        WinPts<T>::ld(loc + (grp_me * LP + ls * kWinP) * 2, aw + grp_me * LP + ls * kWinP, x, y, a);
         const int W = s_lvl[3 * ls + 1], start = s_lvl[3 * ls + 2];
         float gx[4], gy[4], ga[4];
 #pragma unroll
@@ -765,7 +766,6 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
                                 reinterpret_cast<TapMeta<2>*>(s_grp), gv_scale);
     }
     __syncwarp();
-    cur ^= 1;
     w = wn;
   }
 }
