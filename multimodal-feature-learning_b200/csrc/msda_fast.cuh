@@ -119,6 +119,13 @@ template <> struct Unit<float> {
                  : "+f"(v[0]), "+f"(v[1]), "+f"(v[2]), "+f"(v[3])
                  : "l"(p), "r"((int)pred));
   }
+  // the same for data read once (grad_out): do not displace value rows from L1
+  static __device__ __forceinline__ void ldg_keep_stream(const char* p, bool pred, float (&v)[4]) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+                 "@p ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];\n\t}"
+                 : "+f"(v[0]), "+f"(v[1]), "+f"(v[2]), "+f"(v[3])
+                 : "l"(p), "r"((int)pred));
+  }
   static __device__ __forceinline__ void ldg_raw(const char* p, float (&v)[4]) {
     const float4 t = __ldg(reinterpret_cast<const float4*>(p));
     v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
@@ -163,6 +170,12 @@ template <> struct Unit<__nv_bfloat16> {
   static __device__ __forceinline__ void ldg_keep(const char* p, bool pred, uint32_t (&w)[4]) {
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
                  "@p ld.global.nc.v4.b32 {%0, %1, %2, %3}, [%4];\n\t}"
+                 : "+r"(w[0]), "+r"(w[1]), "+r"(w[2]), "+r"(w[3])
+                 : "l"(p), "r"((int)pred));
+  }
+  static __device__ __forceinline__ void ldg_keep_stream(const char* p, bool pred, uint32_t (&w)[4]) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+                 "@p ld.global.nc.L1::no_allocate.v4.b32 {%0, %1, %2, %3}, [%4];\n\t}"
                  : "+r"(w[0]), "+r"(w[1]), "+r"(w[2]), "+r"(w[3])
                  : "l"(p), "r"((int)pred));
   }
@@ -214,6 +227,12 @@ struct UnitBf16x4 {
   static __device__ __forceinline__ void ldg_keep(const char* p, bool pred, uint32_t (&w)[2]) {
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %3, 0;\n\t"
                  "@p ld.global.nc.v2.b32 {%0, %1}, [%2];\n\t}"
+                 : "+r"(w[0]), "+r"(w[1])
+                 : "l"(p), "r"((int)pred));
+  }
+  static __device__ __forceinline__ void ldg_keep_stream(const char* p, bool pred, uint32_t (&w)[2]) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %3, 0;\n\t"
+                 "@p ld.global.nc.L1::no_allocate.v2.b32 {%0, %1}, [%2];\n\t}"
                  : "+r"(w[0]), "+r"(w[1])
                  : "l"(p), "r"((int)pred));
   }

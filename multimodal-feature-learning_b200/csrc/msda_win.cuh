@@ -102,6 +102,16 @@ template <> struct WinPts<float> {
     x[2] = l1.x; y[2] = l1.y; x[3] = l1.z; y[3] = l1.w;
     a[0] = w.x; a[1] = w.y; a[2] = w.z; a[3] = w.w;
   }
+  // read-once variant: no L1 allocation
+  static __device__ __forceinline__ void ld_stream(const float* loc2, const float* awp, float (&x)[4],
+                                                   float (&y)[4], float (&a)[4]) {
+    const float4 l0 = __ldcs(reinterpret_cast<const float4*>(loc2));
+    const float4 l1 = __ldcs(reinterpret_cast<const float4*>(loc2) + 1);
+    const float4 w = __ldcs(reinterpret_cast<const float4*>(awp));
+    x[0] = l0.x; y[0] = l0.y; x[1] = l0.z; y[1] = l0.w;
+    x[2] = l1.x; y[2] = l1.y; x[3] = l1.z; y[3] = l1.w;
+    a[0] = w.x; a[1] = w.y; a[2] = w.z; a[3] = w.w;
+  }
   static __device__ __forceinline__ void ld_smem(const float* loc2, const float* awp, float (&x)[4],
                                                  float (&y)[4], float (&a)[4]) {
     const float4 l0 = *reinterpret_cast<const float4*>(loc2);
@@ -123,6 +133,19 @@ template <> struct WinPts<__nv_bfloat16> {
                                             float (&x)[4], float (&y)[4], float (&a)[4]) {
     const uint4 l = __ldg(reinterpret_cast<const uint4*>(loc2));
     const uint2 w = __ldg(reinterpret_cast<const uint2*>(awp));
+    const uint32_t lw[4] = {l.x, l.y, l.z, l.w};
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      x[p] = __uint_as_float(lw[p] << 16);
+      y[p] = __uint_as_float(lw[p] & 0xffff0000u);
+    }
+    a[0] = __uint_as_float(w.x << 16); a[1] = __uint_as_float(w.x & 0xffff0000u);
+    a[2] = __uint_as_float(w.y << 16); a[3] = __uint_as_float(w.y & 0xffff0000u);
+  }
+  static __device__ __forceinline__ void ld_stream(const __nv_bfloat16* loc2, const __nv_bfloat16* awp,
+                                                   float (&x)[4], float (&y)[4], float (&a)[4]) {
+    const uint4 l = __ldcs(reinterpret_cast<const uint4*>(loc2));
+    const uint2 w = __ldcs(reinterpret_cast<const uint2*>(awp));
     const uint32_t lw[4] = {l.x, l.y, l.z, l.w};
 #pragma unroll
     for (int p = 0; p < 4; ++p) {
@@ -680,7 +703,7 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
         for (int uu = 0; uu < NU; ++uu) {
 #pragma unroll
           for (int k = 0; k < U::RW; ++k) gor[q][uu][k] = Raw(0);
-          U::ldg_keep(win_addr(gb, q * qstride) + uu * (G * U::BYTES), q < nq, gor[q][uu]);
+          U::ldg_keep_stream(win_addr(gb, q * qstride) + uu * (G * U::BYTES), q < nq, gor[q][uu]);
         }
     }
     win_cp_wait_all();
@@ -740,7 +763,7 @@ msda_bwd_win_kernel(const T* __restrict__ value, const int64_t* __restrict__ sha
         const int ls = l < d.L ? l : 0;
         float x[4], y[4], a[4];
         // the staging buffer already belongs to the next unit: the points come from L2 again
-        WinPts<T>::ld(loc + (grp_me * LP + ls * kWinP) * 2, aw + grp_me * LP + ls * kWinP, x, y, a);
+        WinPts<T>::ld_stream(loc + (grp_me * LP + ls * kWinP) * 2, aw + grp_me * LP + ls * kWinP, x, y, a);
         const int W = s_lvl[3 * ls + 1], start = s_lvl[3 * ls + 2];
         float gx[4], gy[4], ga[4];
 #pragma unroll
