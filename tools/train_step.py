@@ -10,8 +10,9 @@ It exists to time the op in the step it serves and the 1 -> N GPU scaling of tha
 step; it is a measurement harness, not a model zoo: no captioning heads, no
 matcher, no dataset.  Per SURVEY.md section 8(d): synthetic features, per-GPU batch 16
 (weak scaling), loss = mean of the decoder outputs squared, AdamW 1e-4, gradient clip
-0.1, DistributedDataParallel over NCCL (one gradient all-reduce per step, bucketed
-and overlapped with the backward).
+0.1, one NCCL gradient all-reduce per step: over a flat buffer all .grad tensors are views
+of (default), or DistributedDataParallel (--sync ddp).  --cuda-graph records the whole
+step once and replays it.
 
   python tools/train_step.py [--steps 20] [--warmup 5] [--batch 16] [--layers 6]
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
