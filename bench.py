@@ -167,28 +167,42 @@ class OpBuffers:
         self.skip = _lib.MSDA_FLAG_SKIP_ZERO_FILL
         self.out = torch.empty(self.N, self.Lq, self.M * self.D, dtype=v.dtype, device=v.device)
         self.gv, self.gl, self.ga = torch.empty_like(v), torch.empty_like(loc), torch.empty_like(aw)
-        self.ws_bytes = self.lib.msda_backward_workspace_bytes(self.N, self.S, self.M, self.D, self.L,
-                                                               self.Lq, self.P, self.dt)
-        self.ws = torch.empty(max(self.ws_bytes // 4, 1), dtype=torch.float32, device=v.device)
         self.dims = (self.N, self.S, self.M, self.D, self.L, self.Lq, self.P)
+        self.set_flags(self.flags)
         self.check = _lib.check
+
+    def set_flags(self, flags):
+        """(Re)size the workspaces for a flags word: the forward's plan (time order of the queries,
+        reused by the backward) and the backward's accumulation image (bf16 only)."""
+        import torch
+        self.flags = flags
+        dev = self.out.device
+        self.plan_bytes = self.lib.msda_forward_workspace_bytes(*self.dims, self.dt, flags)
+        self.plan = torch.empty(max(self.plan_bytes // 4, 1), dtype=torch.int32, device=dev)
+        # the backward's REQUIRED workspace only (an fp32 image of grad_value for bf16); its optional
+        # tail, room for the plan, is not needed: the plan comes from the forward
+        self.ws_bytes = self.N * self.S * self.M * self.D * 4 if self.dt == 2 else 0
+        self.ws = torch.empty(max(self.ws_bytes // 4, 1), dtype=torch.float32, device=dev)
 
     def fwd(self, stream):
         i = self.inp
-        self.check(self.lib.msda_forward(i["value"].data_ptr(), i["shapes"].data_ptr(), i["lsi"].data_ptr(),
-                                         i["loc"].data_ptr(), i["aw"].data_ptr(), self.out.data_ptr(),
-                                         *self.dims, self.dt, self.pad, self.flags, stream))
+        self.check(self.lib.msda_forward_ex(i["value"].data_ptr(), i["shapes"].data_ptr(), i["lsi"].data_ptr(),
+                                            i["loc"].data_ptr(), i["aw"].data_ptr(), self.out.data_ptr(),
+                                            *self.dims, self.dt, self.pad, self.flags,
+                                            self.plan.data_ptr() if self.plan_bytes else None, self.plan_bytes,
+                                            stream))
 
     def zero(self):
         (self.ws if self.ws_bytes else self.gv).zero_()
 
     def bwd(self, stream):
         i = self.inp
-        self.check(self.lib.msda_backward(
+        self.check(self.lib.msda_backward_ex(
             i["value"].data_ptr(), i["shapes"].data_ptr(), i["lsi"].data_ptr(), i["loc"].data_ptr(),
             i["aw"].data_ptr(), i["grad_out"].data_ptr(), self.gv.data_ptr(), self.gl.data_ptr(),
             self.ga.data_ptr(), *self.dims, self.dt, self.pad, self.flags | self.skip,
-            self.ws.data_ptr() if self.ws_bytes else None, self.ws_bytes, stream))
+            self.ws.data_ptr() if self.ws_bytes else None, self.ws_bytes,
+            self.plan.data_ptr() if self.plan_bytes else None, stream))
 
 
 def time_device(bufs, steps, warmup, dist_sync):

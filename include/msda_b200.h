@@ -42,7 +42,7 @@
 extern "C" {
 #endif
 
-#define MSDA_B200_ABI_VERSION 1
+#define MSDA_B200_ABI_VERSION 2
 
 /* element type of value / sampling_loc / attn_weight / output / all grads */
 typedef enum {
@@ -67,7 +67,10 @@ typedef enum {
   MSDA_ERR_TOO_LARGE = -5,      /* exceeds the 2^31 row / group index range */
   MSDA_ERR_WORKSPACE = -6,      /* workspace missing or too small */
   MSDA_ERR_CUDA = -7,           /* CUDA runtime error (see msda_last_cuda_error) */
-  MSDA_ERR_MISALIGNED = -8      /* a data pointer is not 16-byte aligned */
+  MSDA_ERR_MISALIGNED = -8,     /* a data pointer is not 16-byte aligned */
+  MSDA_ERR_NO_TMA = -9          /* internal: the TMA descriptor could not be encoded; the
+                                   entry points fall back to the row-window kernels and
+                                   never return it */
 } msda_status;
 
 /* flags for msda_forward / msda_backward (bitwise or) */
@@ -84,11 +87,22 @@ typedef enum {
 #define MSDA_FLAG_DETERMINISTIC 16u /* msda_backward: bitwise reproducible grad_value.
                                       Contributions are accumulated as 64-bit fixed
                                       point with integer atomics (order-independent)
-                                      by the any-D kernels, then converted; needs
-                                      the workspace msda_backward_workspace_bytes_flags
-                                      reports (32 B + 8 B per grad_value element).
-                                      Slower: an optional variant, as the sorted
-                                      scatter of the design brief, without the sort */
+                                      by the kernel family the shape selects (tile,
+                                      row-window, per-tap or any-D), then converted;
+                                      needs the workspace
+                                      msda_backward_workspace_bytes_flags reports
+                                      (32 B + 8 B per grad_value element).  A
+                                      non-finite grad_output / attn_weight makes the
+                                      whole grad_value NaN.  Slower: an optional
+                                      variant, as the sorted scatter of the design
+                                      brief, without the sort */
+#define MSDA_FLAG_NO_TILE 32u       /* never use the CTA-tile kernels (msda_tile.cuh:
+                                      time-sorted query tiles, TMA-filled shared
+                                      memory); the row-window kernels run instead */
+#define MSDA_FLAG_NO_PLAN 64u       /* CTA-tile path as ONE kernel per direction (msda_tile.cuh)
+                                      instead of the plan kernel + apply kernels of
+                                      msda_plan.cuh; the workspace then only holds the
+                                      query order */
 /* bits 8..19: queries-per-tile multiplier override for the vectorised kernels
  * (0 = heuristic); a tuning knob, results do not depend on it. */
 #define MSDA_FLAG_QTILE(k) (((unsigned)(k) & 0xfffu) << 8)
@@ -99,7 +113,13 @@ const char* msda_error_string(int status);
 /* Name of the kernel family msda_forward/backward would pick:
  * "fast" (vectorised, warp-cooperative) or "generic". */
 const char* msda_kernel_family(int64_t D, int dtype, unsigned flags);
-/* Kernel family for a full problem shape (16-byte aligned pointers assumed):
+/* Kernel family for a full problem shape (16-byte aligned pointers assumed, and for
+ * "tile" a plan workspace: msda_forward_ex / msda_backward_ex):
+ * "tile"    CTA-tile kernels msda_{fwd,bwd}_tile_kernel (the same shape class as
+ *           "window"): 64 time-adjacent queries per CTA -- the queries are taken
+ *           in time order, whatever their index order --, the value rows they tap
+ *           brought to shared memory by TMA; a tile whose rows do not fit runs the
+ *           per-tap body,
  * "window"  row-window kernels msda_{fwd,bwd}_win_kernel (temporal maps, P = 4,
  *           L <= 4, long query lists; per block of 4 queries they fall back to
  *           the per-tap body when the block has no compact window),
@@ -122,8 +142,29 @@ int msda_forward(const void* value, const int64_t* spatial_shapes,
                  int64_t Lq, int64_t P,
                  int dtype, int padding, unsigned flags, void* stream);
 
-/* Bytes of scratch msda_backward needs (0 for f32/f64; an fp32 accumulation
- * image of grad_value for bf16). */
+/*
+ * The same with a caller-provided workspace of msda_forward_workspace_bytes() bytes
+ * (16-byte aligned device memory, borrowed for the call).  For the "tile" shape class
+ * the call first writes the PLAN there -- the time order of each batch item's queries,
+ * int32 [N][Lq] -- and runs the CTA-tile kernels; the same buffer, untouched, can be
+ * handed to msda_backward_ex as `plan` so that the backward does not sort again.
+ * Without a workspace (or with one that is too small) the call is msda_forward.
+ */
+size_t msda_forward_workspace_bytes(int64_t N, int64_t S, int64_t M, int64_t D, int64_t L,
+                                    int64_t Lq, int64_t P, int dtype, unsigned flags);
+int msda_forward_ex(const void* value, const int64_t* spatial_shapes,
+                    const int64_t* level_start_index, const void* sampling_loc,
+                    const void* attn_weight, void* output,
+                    int64_t N, int64_t S, int64_t M, int64_t D, int64_t L,
+                    int64_t Lq, int64_t P,
+                    int dtype, int padding, unsigned flags,
+                    void* workspace, size_t workspace_bytes, void* stream);
+
+/* Bytes of scratch msda_backward takes.  REQUIRED part: nothing for f32/f64, an fp32
+ * accumulation image of grad_value for bf16 (the deterministic variant: see the
+ * _flags form).  OPTIONAL part, for the "tile" shape class: room for the plan behind
+ * it (256-byte aligned); a workspace without that room selects the row-window
+ * kernels. */
 size_t msda_backward_workspace_bytes(int64_t N, int64_t S, int64_t M, int64_t D,
                                      int64_t L, int64_t Lq, int64_t P, int dtype);
 
@@ -146,6 +187,19 @@ int msda_backward(const void* value, const int64_t* spatial_shapes,
                   int64_t Lq, int64_t P,
                   int dtype, int padding, unsigned flags,
                   void* workspace, size_t workspace_bytes, void* stream);
+
+/* msda_backward with the plan msda_forward_ex left in its workspace for the SAME
+ * sampling_loc (NULL: the plan is computed into the workspace tail, as msda_backward
+ * does).  What MSDeformAttnFunction.backward calls (ms_deform_attn_func.py:33-41):
+ * autograd keeps the forward's plan next to the saved tensors. */
+int msda_backward_ex(const void* value, const int64_t* spatial_shapes,
+                     const int64_t* level_start_index, const void* sampling_loc,
+                     const void* attn_weight, const void* grad_output,
+                     void* grad_value, void* grad_sampling_loc, void* grad_attn_weight,
+                     int64_t N, int64_t S, int64_t M, int64_t D, int64_t L,
+                     int64_t Lq, int64_t P,
+                     int dtype, int padding, unsigned flags,
+                     void* workspace, size_t workspace_bytes, const void* plan, void* stream);
 
 /*
  * Module front-end: what MSDeformAttn.forward does between its Linear layers and

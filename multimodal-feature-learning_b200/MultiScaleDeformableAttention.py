@@ -58,29 +58,40 @@ def _stream(t):
 
 
 def ms_deform_attn_forward(value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
-                           im2col_step, padding_mode="zeros", flags=0):
-    """value[N,S,M,D] ... -> output[N,Lq,M*D]  (cuda.cu:20-80)."""
+                           im2col_step, padding_mode="zeros", flags=0, return_plan=False):
+    """value[N,S,M,D] ... -> output[N,Lq,M*D]  (cuda.cu:20-80).
+    return_plan=True also returns the plan workspace of msda_forward_ex (the time order of the
+    queries; None when the shape does not use the CTA-tile kernels), which
+    ms_deform_attn_backward(plan=...) reuses instead of sorting again."""
     N, S, M, D, L, Lq, P = _check_inputs(
         [("value", value), ("spatial_shapes", spatial_shapes),
          ("level_start_index", level_start_index), ("sampling_loc", sampling_loc),
          ("attn_weight", attn_weight)], im2col_step)
     lib = _lib.load()
+    dt = _DTYPES[value.dtype]
     with torch.cuda.device_of(value):
         out = torch.empty((N, Lq, M * D), dtype=value.dtype, device=value.device)
-        _lib.check(lib.msda_forward(
+        ws_bytes = lib.msda_forward_workspace_bytes(N, S, M, D, L, Lq, P, dt, flags)
+        ws = torch.empty(ws_bytes // 4, dtype=torch.int32, device=value.device) if ws_bytes else None
+        _lib.check(lib.msda_forward_ex(
             value.data_ptr(), spatial_shapes.data_ptr(), level_start_index.data_ptr(),
             sampling_loc.data_ptr(), attn_weight.data_ptr(), out.data_ptr(),
-            N, S, M, D, L, Lq, P, _DTYPES[value.dtype], _lib.PADDING_MODES[padding_mode],
-            flags, _stream(value)))
-    return out
+            N, S, M, D, L, Lq, P, dt, _lib.PADDING_MODES[padding_mode],
+            flags, ws.data_ptr() if ws is not None else None, ws_bytes, _stream(value)))
+        if ws is not None:
+            ws.record_stream(torch.cuda.current_stream(value.device))
+    return (out, ws) if return_plan else out
 
 
 def ms_deform_attn_backward(value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
-                            grad_output, im2col_step, padding_mode="zeros", flags=0):
+                            grad_output, im2col_step, padding_mode="zeros", flags=0, plan=None,
+                            grad_value=None):
     """-> [grad_value, grad_sampling_loc, grad_attn_weight]  (cuda.cu:83-153).
     flags |= MSDA_FLAG_DETERMINISTIC (16): bitwise reproducible grad_value (fixed-point
     accumulation, csrc/msda_det.cuh); the autograd Functions set it when
-    torch.are_deterministic_algorithms_enabled()."""
+    torch.are_deterministic_algorithms_enabled().
+    plan: the forward's plan workspace (same sampling_loc).  grad_value: an already ZEROED
+    buffer to accumulate into (pass flags |= MSDA_FLAG_SKIP_ZERO_FILL with it; f32/f64 only)."""
     N, S, M, D, L, Lq, P = _check_inputs(
         [("value", value), ("spatial_shapes", spatial_shapes),
          ("level_start_index", level_start_index), ("sampling_loc", sampling_loc),
@@ -90,19 +101,21 @@ def ms_deform_attn_backward(value, spatial_shapes, level_start_index, sampling_l
     lib = _lib.load()
     dt = _DTYPES[value.dtype]
     with torch.cuda.device_of(value):
-        grad_value = torch.empty_like(value)
+        if grad_value is None:
+            grad_value = torch.empty_like(value)
         grad_loc = torch.empty_like(sampling_loc)
         grad_aw = torch.empty_like(attn_weight)
         ws_bytes = lib.msda_backward_workspace_bytes_flags(N, S, M, D, L, Lq, P, dt, flags)
         ws = None
         if ws_bytes:
             ws = torch.empty((ws_bytes + 3) // 4, dtype=torch.float32, device=value.device)
-        _lib.check(lib.msda_backward(
+        _lib.check(lib.msda_backward_ex(
             value.data_ptr(), spatial_shapes.data_ptr(), level_start_index.data_ptr(),
             sampling_loc.data_ptr(), attn_weight.data_ptr(), grad_output.data_ptr(),
             grad_value.data_ptr(), grad_loc.data_ptr(), grad_aw.data_ptr(),
             N, S, M, D, L, Lq, P, dt, _lib.PADDING_MODES[padding_mode], flags,
-            ws.data_ptr() if ws is not None else None, ws_bytes, _stream(value)))
+            ws.data_ptr() if ws is not None else None, ws_bytes,
+            plan.data_ptr() if plan is not None else None, _stream(value)))
         if ws is not None:
             ws.record_stream(torch.cuda.current_stream(value.device))
     return [grad_value, grad_loc, grad_aw]

@@ -20,6 +20,9 @@ MSDA_FLAG_SKIP_ZERO_FILL = 2
 MSDA_FLAG_NO_WINDOW = 4
 MSDA_FLAG_FORCE_WINDOW = 8
 MSDA_FLAG_DETERMINISTIC = 16
+MSDA_FLAG_NO_TILE = 32
+MSDA_FLAG_NO_PLAN = 64
+ABI_VERSION = 2
 
 
 def flag_qtile(k):
@@ -34,9 +37,12 @@ EXPORTED_SYMBOLS = (
     "msda_kernel_family",
     "msda_kernel_choice",
     "msda_forward",
+    "msda_forward_workspace_bytes",
+    "msda_forward_ex",
     "msda_backward_workspace_bytes",
     "msda_backward_workspace_bytes_flags",
     "msda_backward",
+    "msda_backward_ex",
     "msda_frontend_forward",
     "msda_frontend_backward",
     "msda_dam_scatter",
@@ -72,6 +78,15 @@ def _declare(lib):
     lib.msda_last_cuda_error_string.argtypes = []
     lib.msda_forward.restype = c.c_int
     lib.msda_forward.argtypes = [vp, vp, vp, vp, vp, vp] + [i64] * 7 + [c.c_int, c.c_int, u32, vp]
+    lib.msda_forward_workspace_bytes.restype = c.c_size_t
+    lib.msda_forward_workspace_bytes.argtypes = [i64] * 7 + [c.c_int, u32]
+    lib.msda_forward_ex.restype = c.c_int
+    lib.msda_forward_ex.argtypes = ([vp, vp, vp, vp, vp, vp] + [i64] * 7 +
+                                    [c.c_int, c.c_int, u32, vp, c.c_size_t, vp])
+    lib.msda_backward_ex.restype = c.c_int
+    lib.msda_backward_ex.argtypes = (
+        [vp] * 9 + [i64] * 7 + [c.c_int, c.c_int, u32, vp, c.c_size_t, vp, vp]
+    )
     lib.msda_backward_workspace_bytes.restype = c.c_size_t
     lib.msda_backward_workspace_bytes.argtypes = [i64] * 7 + [c.c_int]
     lib.msda_backward_workspace_bytes_flags.restype = c.c_size_t

@@ -4,6 +4,7 @@
 // (models/ops/src/cuda/ms_deform_attn_cuda.cu:20-153) and the D-dispatch table
 // ms_deformable_col2im_cuda (ms_deform_im2col_cuda.cuh:957-1328).
 
+#include <atomic>
 #include <type_traits>
 
 #include "../../include/msda_b200.h"
@@ -11,6 +12,8 @@
 #include "msda_fast.cuh"
 #include "msda_frontend.cuh"
 #include "msda_generic.cuh"
+#include "msda_plan.cuh"
+#include "msda_tile.cuh"
 #include "msda_win.cuh"
 
 using namespace msda;
@@ -186,6 +189,181 @@ int launch_bwd_win(const void* value, const int64_t* shapes, const int64_t* lsi,
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
 }
 
+// ---- CTA-tile kernels (msda_tile.cuh) -----------------------------------------
+// The value tensor as a 2-D TMA tensor: [N*S rows][M*D channels], box = 8 rows x D channels of
+// one head.  cuTensorMapEncodeTiled is resolved through the runtime (no link against libcuda);
+// the descriptor is plain host arithmetic, rebuilt per call and passed as a kernel parameter,
+// so the library keeps no state about the caller's buffers.
+typedef CUresult (*TileEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                 const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                 CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                 CUtensorMapFloatOOBfill);
+
+TileEncodeFn tile_encoder() {
+  static const TileEncodeFn fn = []() -> TileEncodeFn {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q = cudaDriverEntryPointSymbolNotFound;
+    const cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q);
+    if (e != cudaSuccess || q != cudaDriverEntryPointSuccess || !p) {
+      (void)cudaGetLastError();
+      return nullptr;
+    }
+    return reinterpret_cast<TileEncodeFn>(p);
+  }();
+  return fn;
+}
+
+bool tile_value_map(CUtensorMap* map, const void* base, int dtype, const Dims& d) {
+  const TileEncodeFn enc = tile_encoder();
+  if (!enc) return false;
+  const cuuint64_t esz = dtype == MSDA_BF16 ? 2 : 4;
+  const cuuint64_t gdim[2] = {(cuuint64_t)d.M * d.D, (cuuint64_t)d.N * d.S};
+  const cuuint64_t gstride[1] = {(cuuint64_t)d.M * d.D * esz};
+  const cuuint32_t box[2] = {(cuuint32_t)d.D, (cuuint32_t)kTileBoxRows};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = enc(map, dtype == MSDA_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
+                         2, const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
+}
+
+// Same shape class as the row-window kernels, plus what TMA wants.  The query order comes from a
+// workspace (msda_forward_ex / msda_backward_ex); without one the row-window kernels run.
+inline bool tile_applies(const Dims& d, int dtype, unsigned flags) {
+  if (flags & MSDA_FLAG_NO_TILE) return false;
+  if (!win_applies(d, dtype, flags)) return false;
+  if ((int64_t)d.N * d.S >= (int64_t(1) << 31) || (int64_t)d.N * d.S < kTileBoxRows) return false;
+  if ((int64_t)d.N * d.M * ((d.Lq + kTileQ - 1) / kTileQ) >= (int64_t(1) << 31)) return false;
+  return true;
+}
+
+inline size_t tile_plan_bytes(int64_t N, int64_t Lq) {
+  return ((size_t)N * Lq * sizeof(int) + 255) & ~size_t(255);
+}
+
+// opt in to > 48 KB of dynamic shared memory, once per kernel and device
+template <typename K>
+int tile_smem_attr(K kern, size_t smem, std::atomic<unsigned long long>& done) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_fail(e);
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (dev < 64 && (done.load(std::memory_order_acquire) & bit)) return MSDA_OK;
+  e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return cuda_fail(e);
+  if (dev < 64) done.fetch_or(bit, std::memory_order_release);
+  return MSDA_OK;
+}
+
+template <typename T>
+int launch_sort(const void* loc, int* perm, const Dims& d, cudaStream_t st) {
+  int hk_shift = 0;
+  // heads averaged into the sort key: 2 (one CTA sorts a batch item, and one SM pulls ~50 GB/s:
+  // 8 heads of 1500 queries are 30 us of sector fetches, 2 heads give the same order)
+  while (hk_shift < 1 && (2 << hk_shift) <= d.M) ++hk_shift;
+  msda_sort_kernel<T><<<(unsigned)d.N, kSortThreads, 0, st>>>((const T*)loc, perm, d, hk_shift);
+  const cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
+}
+
+// Launch a tile kernel as a programmatic dependent of the kernel before it in the stream (the
+// sort, when this call computed the plan): its CTAs are scheduled while that kernel drains and
+// wait in griddepcontrol.wait before they read the plan.
+template <typename... KArgs, typename... Args>
+int launch_pdl(void (*kern)(KArgs...), unsigned grid, unsigned block, size_t smem, cudaStream_t st,
+               bool dependent, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(block);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = dependent ? 1 : 0;
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+  return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
+}
+int launch_sort_dtype(int dtype, const void* loc, int* perm, const Dims& d, cudaStream_t st) {
+  return dtype == MSDA_BF16 ? launch_sort<__nv_bfloat16>(loc, perm, d, st) : launch_sort<float>(loc, perm, d, st);
+}
+
+template <typename T, int NU>
+int launch_fwd_tile(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
+                    const void* aw, const int* perm, void* out, const Dims& d, int dtype,
+                    cudaStream_t st, bool after_sort) {
+  static std::atomic<unsigned long long> attr_done{0};
+  CUtensorMap map;
+  if (!tile_value_map(&map, value, dtype, d)) return MSDA_ERR_NO_TMA;
+  auto kern = msda_fwd_tile_kernel<T, NU>;
+  constexpr size_t smem = TileSmem<T, NU>::kBytes;
+  const int rc = tile_smem_attr(kern, smem, attr_done);
+  if (rc != MSDA_OK) return rc;
+  const int nchunks = (d.Lq + kTileQ - 1) / kTileQ;
+  const unsigned grid = (unsigned)((int64_t)d.N * d.M * nchunks);
+  return launch_pdl(kern, grid, kTileThreads, smem, st, after_sort, map, (const T*)value, shapes, lsi,
+                    (const T*)loc, (const T*)aw, perm, (T*)out, d, nchunks);
+}
+
+template <typename T, int NU, typename GV = float, typename U = Unit<T>>
+int launch_bwd_tile(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
+                    const void* aw, const void* gout, const int* perm, GV* gvalue, void* gloc,
+                    void* gaw, const Dims& d, int dtype, cudaStream_t st,
+                    const DetHeader* det = nullptr, bool after_sort = false) {
+  static std::atomic<unsigned long long> attr_done{0};
+  CUtensorMap map;
+  if (!tile_value_map(&map, value, dtype, d)) return MSDA_ERR_NO_TMA;
+  auto kern = msda_bwd_tile_kernel<T, NU, GV, U>;
+  constexpr size_t smem = (size_t)kTileCapRows * NU * 8 * U::BYTES + (size_t)kTileBlocks * kTileBlkRows * 16 + 128;
+  const int rc = tile_smem_attr(kern, smem, attr_done);
+  if (rc != MSDA_OK) return rc;
+  const int nchunks = (d.Lq + kTileQ - 1) / kTileQ;
+  const unsigned grid = (unsigned)((int64_t)d.N * d.M * nchunks);
+  return launch_pdl(kern, grid, kTileThreads, smem, st, after_sort, map, (const T*)value, shapes, lsi,
+                    (const T*)loc, (const T*)aw, (const T*)gout, perm, gvalue, (T*)gloc, (T*)gaw, d,
+                    nchunks, det);
+}
+
+// ---- plan / apply split (msda_plan.cuh) ---------------------------------------------
+// workspace of the split path: [query order: int32 N*Lq, 256-byte rounded][plan: tiles * kPlanStride]
+inline size_t plan_tiles(int64_t N, int64_t M, int64_t Lq) {
+  return (size_t)N * M * ((Lq + kTileQ - 1) / kTileQ);
+}
+inline size_t plan_ws_bytes(int64_t N, int64_t M, int64_t Lq) {
+  return tile_plan_bytes(N, Lq) + plan_tiles(N, M, Lq) * kPlanStride;
+}
+inline char* plan_of(void* workspace, int64_t N, int64_t Lq) {
+  return (char*)workspace + tile_plan_bytes(N, Lq);
+}
+
+template <typename T>
+int launch_plan(const int64_t* shapes, const int64_t* lsi, const void* loc, const void* aw,
+                const int* perm, char* plan, const Dims& d, cudaStream_t st) {
+  const int nchunks = (d.Lq + kTileQ - 1) / kTileQ;
+  const unsigned grid = (unsigned)((int64_t)d.N * d.M * nchunks);
+  return launch_pdl(msda_plan_kernel<T>, grid, kTileThreads, 0, st, true, shapes, lsi, (const T*)loc,
+                    (const T*)aw, perm, plan, d, nchunks);
+}
+
+template <typename T, int NU>
+int launch_fwd_apply(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
+                     const void* aw, const char* plan, void* out, const Dims& d, int dtype,
+                     cudaStream_t st, bool after_plan) {
+  static std::atomic<unsigned long long> attr_done{0};
+  CUtensorMap map;
+  if (!tile_value_map(&map, value, dtype, d)) return MSDA_ERR_NO_TMA;
+  auto kern = msda_fwd_apply_kernel<T, NU>;
+  constexpr size_t smem = ApplySmem<T, NU>::kBytes;
+  const int rc = tile_smem_attr(kern, smem, attr_done);
+  if (rc != MSDA_OK) return rc;
+  const int nchunks = (d.Lq + kTileQ - 1) / kTileQ;
+  const unsigned grid = (unsigned)((int64_t)d.N * d.M * nchunks);
+  return launch_pdl(kern, grid, kTileThreads, smem, st, after_plan, map, (const T*)value, shapes, lsi,
+                    (const T*)loc, (const T*)aw, plan, (T*)out, d, nchunks);
+}
+
 // (dtype, NU, G) -> instantiation.  FN is launch_fwd_fast / launch_bwd_fast.
 #define MSDA_CASE(T, NU_, G_, FN, ...) \
   if (plan.nu == NU_ && plan.g == G_) return FN<T, NU_, G_>(__VA_ARGS__)
@@ -236,13 +414,14 @@ int launch_bwd_generic(const void* value, const int64_t* shapes, const int64_t* 
 
 
 // ---- deterministic backward (msda_det.cuh) ------------------------------------
-// family: 2 = row-window kernels, 1 = per-tap vectorised kernels (both only in their 8-lane
-// instantiations <T, NU, 8>: f32 D = 64 / 32, bf16 D = 64), 0 = any-D kernels
+// family: 3 = CTA-tile kernels (perm = the time order of the queries), 2 = row-window kernels,
+// 1 = per-tap vectorised kernels (all only in their 8-lane instantiations: f32 D = 64 / 32,
+// bf16 D = 64), 0 = any-D kernels
 template <typename T, int NU>
 int backward_deterministic(const void* value, const int64_t* shapes, const int64_t* lsi,
                            const void* loc, const void* aw, const void* gout, void* gvalue,
                            void* gloc, void* gaw, const Dims& d, void* workspace, int family,
-                           unsigned flags, cudaStream_t st) {
+                           unsigned flags, cudaStream_t st, const int* perm, int dtype) {
   DetHeader* hdr = (DetHeader*)workspace;
   long long* acc = (long long*)((char*)workspace + sizeof(DetHeader));
   const size_t nvalue = (size_t)d.N * d.S * d.M * d.D;
@@ -258,7 +437,10 @@ int backward_deterministic(const void* value, const int64_t* shapes, const int64
   int r = MSDA_OK;
   bool done = false;
   if constexpr (!std::is_same<T, double>::value) {   // the vectorised kernels have no fp64 form
-    if (family == 2) {
+    if (family == 3) {
+      r = launch_bwd_tile<T, NU, long long>(value, shapes, lsi, loc, aw, gout, perm, acc, gloc, gaw, d, dtype, st, hdr);
+      done = true;
+    } else if (family == 2) {
       r = launch_bwd_win<T, NU, 8, long long>(value, shapes, lsi, loc, aw, gout, acc, gloc, gaw, d, st, hdr);
       done = true;
     } else if (family == 1) {
@@ -360,6 +542,7 @@ const char* msda_error_string(int status) {
     case MSDA_ERR_WORKSPACE: return "workspace missing or smaller than msda_backward_workspace_bytes()";
     case MSDA_ERR_CUDA: return "CUDA runtime error (see msda_last_cuda_error_string)";
     case MSDA_ERR_MISALIGNED: return "data pointer not aligned to its element size";
+    case MSDA_ERR_NO_TMA: return "TMA tensor map could not be encoded (driver entry point missing or rejected)";
     default: return "unknown msda status";
   }
 }
@@ -373,18 +556,35 @@ const char* msda_kernel_choice(int64_t N, int64_t S, int64_t M, int64_t D, int64
   if (check_common(N, S, M, D, L, Lq, P, dtype, MSDA_PAD_ZEROS) != MSDA_OK) return "invalid";
   const bool fast = S * M * D < (int64_t(1) << 31) && fast_applies(D, L, dtype, flags);
   if (!fast) return "generic";
-  return win_applies(make_dims(N, S, M, D, L, Lq, P, MSDA_PAD_ZEROS), dtype, flags) ? "window" : "fast";
+  const Dims d = make_dims(N, S, M, D, L, Lq, P, MSDA_PAD_ZEROS);
+  if (tile_applies(d, dtype, flags)) return "tile";
+  return win_applies(d, dtype, flags) ? "window" : "fast";
 }
+
+#ifdef MSDA_TILE_TIMING
+int msda_debug_tile_times(unsigned long long* host, int n) {
+  return (int)cudaMemcpyFromSymbol(host, g_tile_times, (size_t)n * sizeof(unsigned long long));
+}
+#endif
 
 int msda_last_cuda_error(void) { return t_last_cuda_error; }
 const char* msda_last_cuda_error_string(void) {
   return cudaGetErrorString((cudaError_t)t_last_cuda_error);
 }
 
-int msda_forward(const void* value, const int64_t* spatial_shapes, const int64_t* level_start_index,
-                 const void* sampling_loc, const void* attn_weight, void* output, int64_t N,
-                 int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq, int64_t P, int dtype,
-                 int padding, unsigned flags, void* stream) {
+size_t msda_forward_workspace_bytes(int64_t N, int64_t S, int64_t M, int64_t D, int64_t L,
+                                    int64_t Lq, int64_t P, int dtype, unsigned flags) {
+  if (check_common(N, S, M, D, L, Lq, P, dtype, MSDA_PAD_ZEROS) != MSDA_OK || N == 0 || Lq == 0) return 0;
+  const bool fast = S * M * D < (int64_t(1) << 31) && fast_applies(D, L, dtype, flags);
+  if (!fast || !tile_applies(make_dims(N, S, M, D, L, Lq, P, MSDA_PAD_ZEROS), dtype, flags)) return 0;
+  return (flags & MSDA_FLAG_NO_PLAN) ? tile_plan_bytes(N, Lq) : plan_ws_bytes(N, M, Lq);
+}
+
+int msda_forward_ex(const void* value, const int64_t* spatial_shapes, const int64_t* level_start_index,
+                    const void* sampling_loc, const void* attn_weight, void* output, int64_t N,
+                    int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq, int64_t P, int dtype,
+                    int padding, unsigned flags, void* workspace, size_t workspace_bytes,
+                    void* stream) {
   const int rc = check_common(N, S, M, D, L, Lq, P, dtype, padding);
   if (rc != MSDA_OK) return rc;
   if (N == 0 || Lq == 0) return MSDA_OK;  // empty output
@@ -396,6 +596,42 @@ int msda_forward(const void* value, const int64_t* spatial_shapes, const int64_t
   const bool fits32 = S * M * D < (int64_t(1) << 31);
   const bool fast = fits32 && fast_applies(D, L, dtype, flags) && aligned16(value) && aligned16(output) &&
                     aligned16(sampling_loc) && aligned16(attn_weight);
+  // CTA tiles in time order: needs the plan workspace (the query permutation) and TMA
+  if (fast && tile_applies(d, dtype, flags) && workspace && aligned16(workspace) &&
+      workspace_bytes >= tile_plan_bytes(N, Lq) && tile_encoder()) {
+    int* perm = (int*)workspace;
+    int r = launch_sort_dtype(dtype, sampling_loc, perm, d, st);
+    if (r != MSDA_OK) return r;
+    if (!(flags & MSDA_FLAG_NO_PLAN) && workspace_bytes >= plan_ws_bytes(N, M, Lq) &&
+        (tile_plan_bytes(N, Lq) % 128) == 0 && (reinterpret_cast<uintptr_t>(workspace) & 127u) == 0) {
+      // plan kernel + apply kernel
+      char* plan = plan_of(workspace, N, Lq);
+      r = dtype == MSDA_BF16
+              ? launch_plan<__nv_bfloat16>(spatial_shapes, level_start_index, sampling_loc, attn_weight, perm, plan, d, st)
+              : launch_plan<float>(spatial_shapes, level_start_index, sampling_loc, attn_weight, perm, plan, d, st);
+      if (r != MSDA_OK) return r;
+      if (dtype == MSDA_BF16)
+        r = launch_fwd_apply<__nv_bfloat16, 1>(value, spatial_shapes, level_start_index, sampling_loc,
+                                               attn_weight, plan, output, d, dtype, st, true);
+      else if (D == 64)
+        r = launch_fwd_apply<float, 2>(value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
+                                       plan, output, d, dtype, st, true);
+      else
+        r = launch_fwd_apply<float, 1>(value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
+                                       plan, output, d, dtype, st, true);
+      if (r != MSDA_ERR_NO_TMA) return r;
+    }
+    if (dtype == MSDA_BF16)
+      r = launch_fwd_tile<__nv_bfloat16, 1>(value, spatial_shapes, level_start_index, sampling_loc,
+                                            attn_weight, perm, output, d, dtype, st, true);
+    else if (D == 64)
+      r = launch_fwd_tile<float, 2>(value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
+                                    perm, output, d, dtype, st, true);
+    else
+      r = launch_fwd_tile<float, 1>(value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
+                                    perm, output, d, dtype, st, true);
+    if (r != MSDA_ERR_NO_TMA) return r;   // descriptor rejected: the row-window kernels take over
+  }
   if (fast && win_applies(d, dtype, flags)) {
     if (dtype == MSDA_BF16)
       return launch_fwd_win<__nv_bfloat16, 1, 8>(value, spatial_shapes, level_start_index,
@@ -425,47 +661,86 @@ int msda_forward(const void* value, const int64_t* spatial_shapes, const int64_t
   }
 }
 
-size_t msda_backward_workspace_bytes(int64_t N, int64_t S, int64_t M, int64_t D, int64_t L,
-                                     int64_t Lq, int64_t P, int dtype) {
-  (void)L; (void)Lq; (void)P;
-  if (dtype != MSDA_BF16 || N <= 0 || S <= 0 || M <= 0 || D <= 0) return 0;
+int msda_forward(const void* value, const int64_t* spatial_shapes, const int64_t* level_start_index,
+                 const void* sampling_loc, const void* attn_weight, void* output, int64_t N,
+                 int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq, int64_t P, int dtype,
+                 int padding, unsigned flags, void* stream) {
+  return msda_forward_ex(value, spatial_shapes, level_start_index, sampling_loc, attn_weight, output,
+                         N, S, M, D, L, Lq, P, dtype, padding, flags, nullptr, 0, stream);
+}
+
+}  // extern "C"
+
+namespace {
+// the part of the backward workspace that is REQUIRED: the fp32 accumulation image of a bf16
+// grad_value, or the fixed-point image + header of the deterministic variant
+size_t ws_main_bytes(int64_t N, int64_t S, int64_t M, int64_t D, int dtype, unsigned flags) {
+  if (N <= 0 || S <= 0 || M <= 0 || D <= 0) return 0;
+  if (flags & MSDA_FLAG_DETERMINISTIC) return sizeof(DetHeader) + (size_t)N * S * M * D * sizeof(long long);
+  if (dtype != MSDA_BF16) return 0;
   return (size_t)N * S * M * D * sizeof(float);
 }
+inline size_t round256(size_t x) { return (x + 255) & ~size_t(255); }
+}  // namespace
+
+extern "C" {
 
 size_t msda_backward_workspace_bytes_flags(int64_t N, int64_t S, int64_t M, int64_t D, int64_t L,
                                            int64_t Lq, int64_t P, int dtype, unsigned flags) {
-  if (!(flags & MSDA_FLAG_DETERMINISTIC))
-    return msda_backward_workspace_bytes(N, S, M, D, L, Lq, P, dtype);
-  if (N <= 0 || S <= 0 || M <= 0 || D <= 0) return 0;
-  return sizeof(DetHeader) + (size_t)N * S * M * D * sizeof(long long);
+  const size_t main_bytes = ws_main_bytes(N, S, M, D, dtype, flags);
+  // + the plan of the CTA-tile kernels (optional: without it the row-window kernels run)
+  const size_t plan = msda_forward_workspace_bytes(N, S, M, D, L, Lq, P, dtype, flags | MSDA_FLAG_NO_PLAN);
+  return plan ? round256(main_bytes) + plan : main_bytes;
 }
 
-int msda_backward(const void* value, const int64_t* spatial_shapes, const int64_t* level_start_index,
-                  const void* sampling_loc, const void* attn_weight, const void* grad_output,
-                  void* grad_value, void* grad_sampling_loc, void* grad_attn_weight, int64_t N,
-                  int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq, int64_t P, int dtype,
-                  int padding, unsigned flags, void* workspace, size_t workspace_bytes,
-                  void* stream) {
+size_t msda_backward_workspace_bytes(int64_t N, int64_t S, int64_t M, int64_t D, int64_t L,
+                                     int64_t Lq, int64_t P, int dtype) {
+  return msda_backward_workspace_bytes_flags(N, S, M, D, L, Lq, P, dtype, 0);
+}
+
+int msda_backward_ex(const void* value, const int64_t* spatial_shapes, const int64_t* level_start_index,
+                     const void* sampling_loc, const void* attn_weight, const void* grad_output,
+                     void* grad_value, void* grad_sampling_loc, void* grad_attn_weight, int64_t N,
+                     int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq, int64_t P, int dtype,
+                     int padding, unsigned flags, void* workspace, size_t workspace_bytes,
+                     const void* plan, void* stream) {
   const int rc = check_common(N, S, M, D, L, Lq, P, dtype, padding);
   if (rc != MSDA_OK) return rc;
   Dims d = make_dims(N, S, M, D, L, Lq, P, padding);
   cudaStream_t st = (cudaStream_t)stream;
   const size_t esz = dtype == MSDA_F64 ? 8 : dtype == MSDA_F32 ? 4 : 2;
   const size_t nvalue = (size_t)N * S * M * D;
-  const size_t ws_need = msda_backward_workspace_bytes_flags(N, S, M, D, L, Lq, P, dtype, flags);
+  if (nvalue == 0) flags &= ~MSDA_FLAG_DETERMINISTIC;   // nothing to accumulate: the plain kernels do
+  const size_t ws_need = ws_main_bytes(N, S, M, D, dtype, flags);
   if (nvalue > 0 && (!grad_value || !value)) return MSDA_ERR_NULL_POINTER;
   if (ws_need > 0 && (!workspace || workspace_bytes < ws_need)) return MSDA_ERR_WORKSPACE;
   if (ws_need > 0 && !aligned16(workspace)) return MSDA_ERR_MISALIGNED;
 
+  // CTA-tile kernels: the query order is the caller's plan (the workspace msda_forward_ex filled
+  // for the same sampling locations) or is computed here into the tail of the workspace
+  const bool fits32 = S * M * D < (int64_t(1) << 31);
+  const bool aligned = aligned16(value) && aligned16(grad_output) && aligned16(grad_value) &&
+                       aligned16(sampling_loc) && aligned16(attn_weight) &&
+                       aligned16(grad_sampling_loc) && aligned16(grad_attn_weight);
+  const bool fast = fits32 && fast_applies(D, L, dtype, flags) && aligned;
+  const int* perm = nullptr;
+  bool need_sort = false;
+  if (N > 0 && Lq > 0 && fast && tile_applies(d, dtype, flags) && tile_encoder()) {
+    if (plan && aligned16(plan)) {
+      perm = (const int*)plan;
+    } else if (workspace && aligned16(workspace) &&
+               workspace_bytes >= round256(ws_need) + tile_plan_bytes(N, Lq)) {
+      perm = (const int*)((char*)workspace + round256(ws_need));
+      need_sort = true;
+    }
+  }
+
   if (flags & MSDA_FLAG_DETERMINISTIC) {
     // fixed-point image + header are always cleared here (MSDA_FLAG_SKIP_ZERO_FILL does not apply)
-    if (ws_need > 0) {
-      const cudaError_t e = cudaMemsetAsync(workspace, 0, ws_need, st);
-      if (e != cudaSuccess) return cuda_fail(e);
-    }
+    cudaError_t e = cudaMemsetAsync(workspace, 0, ws_need, st);
+    if (e != cudaSuccess) return cuda_fail(e);
     if (N == 0 || Lq == 0) {
-      if (nvalue == 0) return MSDA_OK;
-      const cudaError_t e = cudaMemsetAsync(grad_value, 0, nvalue * esz, st);
+      e = cudaMemsetAsync(grad_value, 0, nvalue * esz, st);
       return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
     }
     if (!spatial_shapes || !level_start_index || !sampling_loc || !attn_weight || !grad_output ||
@@ -473,17 +748,18 @@ int msda_backward(const void* value, const int64_t* spatial_shapes, const int64_
       return MSDA_ERR_NULL_POINTER;
     // the 8-lane vectorised instantiations cover the production head sizes; the 64-bit image
     // doubles the byte offsets the window kernels keep in 32 bits
-    const bool aligned = aligned16(value) && aligned16(grad_output) && aligned16(sampling_loc) &&
-                         aligned16(attn_weight) && aligned16(grad_sampling_loc) &&
-                         aligned16(grad_attn_weight) && aligned16(workspace);
-    const bool vec8 = aligned && S * M * D < (int64_t(1) << 31) && fast_applies(D, L, dtype, flags) &&
-                      ((dtype == MSDA_F32 && (D == 64 || D == 32)) || (dtype == MSDA_BF16 && D == 64));
+    const bool vec8 = fast && ((dtype == MSDA_F32 && (D == 64 || D == 32)) || (dtype == MSDA_BF16 && D == 64));
     const int family = !vec8 ? 0
+                       : perm ? 3
                        : (win_applies(d, dtype, flags) && S * M * D * 8 < (int64_t(1) << 32)) ? 2 : 1;
+    if (family == 3 && need_sort) {
+      const int r = launch_sort_dtype(dtype, sampling_loc, const_cast<int*>(perm), d, st);
+      if (r != MSDA_OK) return r;
+    }
 #define MSDA_DET(T_, NU_)                                                                        \
   return backward_deterministic<T_, NU_>(value, spatial_shapes, level_start_index, sampling_loc,  \
                                          attn_weight, grad_output, grad_value, grad_sampling_loc, \
-                                         grad_attn_weight, d, workspace, family, flags, st)
+                                         grad_attn_weight, d, workspace, family, flags, st, perm, dtype)
     if (dtype == MSDA_F32 && D == 64) MSDA_DET(float, 2);
     if (dtype == MSDA_F32) MSDA_DET(float, 1);
     if (dtype == MSDA_F64) MSDA_DET(double, 1);
@@ -498,17 +774,41 @@ int msda_backward(const void* value, const int64_t* spatial_shapes, const int64_
     const cudaError_t e = cudaMemsetAsync(acc, 0, ws_need ? ws_need : nvalue * esz, st);
     if (e != cudaSuccess) return cuda_fail(e);
   }
-  if (N == 0 || Lq == 0) return MSDA_OK;
+  if (N == 0 || Lq == 0) {
+    // no query: grad_value is all zeros (for bf16 the image is not grad_value itself)
+    if (nvalue > 0 && acc != grad_value) {
+      const cudaError_t e = cudaMemsetAsync(grad_value, 0, nvalue * esz, st);
+      if (e != cudaSuccess) return cuda_fail(e);
+    }
+    return MSDA_OK;
+  }
   if (!spatial_shapes || !level_start_index || !sampling_loc || !attn_weight || !grad_output ||
       !grad_sampling_loc || !grad_attn_weight)
     return MSDA_ERR_NULL_POINTER;
 
-  const bool fits32 = S * M * D < (int64_t(1) << 31);
-  const bool fast = fits32 && fast_applies(D, L, dtype, flags) && aligned16(value) && aligned16(grad_output) &&
-                    aligned16(grad_value) && aligned16(sampling_loc) && aligned16(attn_weight) &&
-                    aligned16(grad_sampling_loc) && aligned16(grad_attn_weight);
-  int r = MSDA_OK;
-  if (fast && win_applies(d, dtype, flags)) {
+  int r = MSDA_ERR_NO_TMA;
+  if (perm) {
+    if (need_sort) {
+      r = launch_sort_dtype(dtype, sampling_loc, const_cast<int*>(perm), d, st);
+      if (r != MSDA_OK) return r;
+    }
+    if (dtype == MSDA_BF16)
+      // two 8-byte units per lane: dense 128-byte reds into the fp32 image (msda_fast.cuh)
+      r = launch_bwd_tile<__nv_bfloat16, 2, float, UnitBf16x4>(
+          value, spatial_shapes, level_start_index, sampling_loc, attn_weight, grad_output, perm,
+          (float*)acc, grad_sampling_loc, grad_attn_weight, d, dtype, st, nullptr, need_sort);
+    else if (D == 64)
+      r = launch_bwd_tile<float, 2>(value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
+                                    grad_output, perm, (float*)acc, grad_sampling_loc, grad_attn_weight,
+                                    d, dtype, st, nullptr, need_sort);
+    else
+      r = launch_bwd_tile<float, 1>(value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
+                                    grad_output, perm, (float*)acc, grad_sampling_loc, grad_attn_weight,
+                                    d, dtype, st, nullptr, need_sort);
+  }
+  if (r != MSDA_ERR_NO_TMA) {
+    // done by the tile kernels (or failed)
+  } else if (fast && win_applies(d, dtype, flags)) {
     if (dtype == MSDA_BF16)
       // two 8-byte units per lane: dense 128-byte reds into the fp32 image (msda_fast.cuh)
       r = launch_bwd_win<__nv_bfloat16, 2, 8, float, UnitBf16x4>(
@@ -567,6 +867,17 @@ int msda_backward(const void* value, const int64_t* spatial_shapes, const int64_
     if (e != cudaSuccess) return cuda_fail(e);
   }
   return MSDA_OK;
+}
+
+int msda_backward(const void* value, const int64_t* spatial_shapes, const int64_t* level_start_index,
+                  const void* sampling_loc, const void* attn_weight, const void* grad_output,
+                  void* grad_value, void* grad_sampling_loc, void* grad_attn_weight, int64_t N,
+                  int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq, int64_t P, int dtype,
+                  int padding, unsigned flags, void* workspace, size_t workspace_bytes,
+                  void* stream) {
+  return msda_backward_ex(value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
+                          grad_output, grad_value, grad_sampling_loc, grad_attn_weight, N, S, M, D, L,
+                          Lq, P, dtype, padding, flags, workspace, workspace_bytes, nullptr, stream);
 }
 
 

@@ -22,7 +22,7 @@ namespace msda {
 struct DetHeader {
   unsigned amax_go, amax_aw;   // bit patterns of max|x| as fp32 (>= 0: ordered like integers)
   int e;                       // scale = 2^e
-  int pad;
+  int nonfinite;               // max|grad_out| * max|attn_weight| is NaN or inf: grad_value becomes NaN
   double scale, inv_scale;
 };
 static_assert(sizeof(DetHeader) == 32, "workspace layout");
@@ -52,6 +52,7 @@ __global__ void msda_det_scale_kernel(DetHeader* h, int log2_addends) {
     e = e > 120 ? 120 : e < -120 ? -120 : e;
   }
   h->e = e;
+  h->nonfinite = !(bound <= 3.0e38f);     // NaN or inf (the reference's float atomics propagate them too)
   h->scale = ldexp(1.0, e);
   h->inv_scale = ldexp(1.0, -e);
 }
@@ -76,7 +77,7 @@ __global__ void __launch_bounds__(256)
 msda_det_convert_kernel(const long long* __restrict__ acc, T* __restrict__ gv, size_t n,
                         const DetHeader* __restrict__ h) {
   using CT = typename AccOf<T>::type;
-  const double inv = h->inv_scale;
+  const double inv = h->nonfinite ? __longlong_as_double(0x7ff8000000000000ll) : h->inv_scale;
   for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (size_t)gridDim.x * 256)
     gv[i] = from_acc<T, CT>((CT)((double)acc[i] * inv));
 }

@@ -327,9 +327,11 @@ template <typename T, int NU, int G, int NT>
 __device__ __forceinline__ void fwd_body(const T* __restrict__ value, const T* __restrict__ loc,
                                          const T* __restrict__ aw, T* __restrict__ out,
                                          const Dims& d, int b, int m, int q_first, int q_end,
-                                         int q_step, const int* s_lvl, TapMeta<NT>* s_meta) {
-  // the group handles queries q_first, q_first + q_step, ... < q_end of (b, m);
-  // s_meta = G entries private to the group
+                                         int q_step, const int* s_lvl, TapMeta<NT>* s_meta,
+                                         const int* qlist = nullptr) {
+  // the group handles queries q_first, q_first + q_step, ... < q_end of (b, m) -- or, with a
+  // query list (the time-sorted tiles of msda_tile.cuh), the queries qlist[q_first], ...,
+  // negative entries skipped; s_meta = G entries private to the group
   constexpr int E = Unit<T>::E;
   const int lane = threadIdx.x & 31;
   const int j = threadIdx.x % G;
@@ -338,7 +340,9 @@ __device__ __forceinline__ void fwd_body(const T* __restrict__ value, const T* _
   const int MD = d.M * d.D;
   const T* vb = value + ((size_t)b * d.S * d.M + m) * d.D + j * E;
 
-  for (int q = q_first; q < q_end; q += q_step) {
+  for (int qq = q_first; qq < q_end; qq += q_step) {
+    const int q = qlist ? qlist[qq] : qq;
+    if (q < 0) continue;
     const size_t grp = ((size_t)b * d.Lq + q) * d.M + m;
     const T* loc_g = loc + grp * LP * 2;
     const T* aw_g = aw + grp * LP;
@@ -425,7 +429,8 @@ __device__ __forceinline__ void bwd_body(const T* __restrict__ value, const T* _
                                          GV* __restrict__ gvalue, T* __restrict__ gloc,
                                          T* __restrict__ gaw, const Dims& d, int b, int m,
                                          int q_first, int q_end, int q_step, const int* s_lvl,
-                                         TapMeta<NT>* s_meta, float gv_scale = 1.f) {
+                                         TapMeta<NT>* s_meta, float gv_scale = 1.f,
+                                         const int* qlist = nullptr) {
   constexpr int E = U::E;
   const int lane = threadIdx.x & 31;
   const int j = threadIdx.x % G;
@@ -436,7 +441,9 @@ __device__ __forceinline__ void bwd_body(const T* __restrict__ value, const T* _
   const T* vb = value + voff;
   GV* gvb = gvalue + voff;
 
-  for (int q = q_first; q < q_end; q += q_step) {
+  for (int qq = q_first; qq < q_end; qq += q_step) {
+    const int q = qlist ? qlist[qq] : qq;
+    if (q < 0) continue;
     const size_t grp = ((size_t)b * d.Lq + q) * d.M + m;
     const T* loc_g = loc + grp * LP * 2;
     const T* aw_g = aw + grp * LP;

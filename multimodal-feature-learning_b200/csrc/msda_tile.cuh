@@ -1,0 +1,716 @@
+// msda_tile.cuh -- CTA-tile MSDeformAttn kernels for temporal (H == 1) maps: the
+// encoder path of round 2.
+//
+// What changed against the warp-level row windows of msda_win.cuh:
+//   * queries are processed in TIME ORDER, not in index order.  A small pre-pass
+//     (msda_sort_kernel) bins the queries of each batch item by the mean x of their
+//     level-0 points and writes a permutation.  The encoder's query list is the
+//     concatenation of its levels (models/deformable/unimodal_deformable_transformer.py:
+//     90-134), the sparse encoders hand the op score-ordered top-k tokens
+//     (models/sparse/unimodal_sparse_deformable_transformer.py:218, 425-431): in time
+//     order four neighbouring queries share their rows whatever the index order was
+//     (18.8 packed rows per 4-query block at the encoder shape instead of 30.7).
+//   * a TILE = 64 time-adjacent queries of one (batch, head), owned by a CTA of 128
+//     threads.  The union of the rows the tile taps is, per level, one contiguous run
+//     of value rows (~85 rows of 256 B at the encoder shape): it is brought to shared
+//     memory ONCE by TMA (cp.async.bulk.tensor.2d boxes of 8 rows x D channels behind
+//     an mbarrier, issued by one thread while the others build their plans) and all 16
+//     blocks of the CTA read their rows with LDS.128.  No register ring of in-flight
+//     global rows, no L1 dependence, value rows cross L2 -> SM ~1.3 times instead of ~6.
+//   * the 4-query BLOCK of msda_win.cuh survives: 8 lanes, lane j owns channels
+//     [4j, 4j+4) and [32+4j, 32+4j+4), weights merged per (row, query) in a small
+//     shared-memory matrix, four queries sharing each row read.
+// Tiles whose union window does not fit (random locations) and launches with H != 1
+// run the per-tap body of msda_fast.cuh on the tile's query list.
+//
+// Semantics note (as msda_win.cuh): a row inside a block's window meets zero weights of
+// the block's other queries, so a non-finite value row poisons up to 3 neighbours in time
+// through 0 * inf; MSDA_FLAG_NO_WINDOW selects the per-tap kernels, which never read a row
+// they do not tap.
+#pragma once
+#include <cuda.h>   // CUtensorMap (the type only; the encoder is resolved at run time)
+#include <type_traits>
+
+#include "msda_win.cuh"
+
+namespace msda {
+
+// tuning knobs (overridable at build time for A/B runs: build.sh -DMSDA_TILE_WARPS=8 ...)
+#ifndef MSDA_TILE_WARPS
+#define MSDA_TILE_WARPS 4
+#endif
+#ifndef MSDA_TILE_CAP
+#define MSDA_TILE_CAP 160
+#endif
+#ifndef MSDA_TILE_BLK
+#define MSDA_TILE_BLK 48
+#endif
+#ifndef MSDA_TILE_FWD_CTAS
+#define MSDA_TILE_FWD_CTAS 4
+#endif
+#ifndef MSDA_TILE_BWD_CTAS
+#define MSDA_TILE_BWD_CTAS 3
+#endif
+constexpr int kTileWarps = MSDA_TILE_WARPS;
+constexpr int kTileThreads = kTileWarps * 32;
+constexpr int kTileBlocks = kTileThreads / 8;        // 4-query blocks per tile
+constexpr int kTileQ = kTileBlocks * kWinQ;          // queries per tile (64 with 4 warps)
+constexpr int kTileBoxRows = 8;                      // value rows per TMA box
+constexpr int kTileCapRows = MSDA_TILE_CAP;          // value rows per tile (multiple of the box)
+constexpr int kTileBlkRows = MSDA_TILE_BLK;          // packed rows per block (plan capacity)
+constexpr int kSortBins = 4096;
+constexpr int kSortThreads = 1024;
+constexpr int kTileBig = 0x3fffffff;
+
+// ---- optional phase timing (debug builds: -DMSDA_TILE_TIMING) -------------------
+#ifdef MSDA_TILE_TIMING
+__device__ unsigned long long g_tile_times[8 * 8192];
+__device__ __forceinline__ void tile_stamp(int k) {
+  if (threadIdx.x == 0 && blockIdx.x < 8192) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    g_tile_times[blockIdx.x * 8 + k] = t;
+  }
+}
+#else
+__device__ __forceinline__ void tile_stamp(int) {}
+#endif
+
+// ---- query order ---------------------------------------------------------------
+// sum of the x coordinates of the 4 level-0 points of one (query, head)
+template <typename T> struct SortKey;
+template <> struct SortKey<float> {
+  static __device__ __forceinline__ float sum4(const float* p) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(p));
+    const float4 b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+    return (a.x + a.z) + (b.x + b.z);
+  }
+};
+template <> struct SortKey<__nv_bfloat16> {
+  static __device__ __forceinline__ float sum4(const __nv_bfloat16* p) {
+    const uint4 l = __ldg(reinterpret_cast<const uint4*>(p));
+    return (__uint_as_float(l.x << 16) + __uint_as_float(l.y << 16)) +
+           (__uint_as_float(l.z << 16) + __uint_as_float(l.w << 16));
+  }
+};
+
+// One CTA per batch item: counting sort of its Lq queries by time bin.  perm[b][i] = index of
+// the i-th query in time order (ties in arbitrary order: no result depends on the order inside
+// a bin, the forward is bitwise independent of the permutation).  P == 4.
+// HK lanes share a query (one head each, the first HK = min(M, 2) heads), so all loads of a pass are in flight together; the bin of a query is kept in shared
+// memory between the two passes when Lq allows it.
+constexpr int kSortStash = 8192;
+
+template <typename T>
+__global__ void __launch_bounds__(kSortThreads)
+msda_sort_kernel(const T* __restrict__ loc, int* __restrict__ perm, Dims d, int hk_shift) {
+  __shared__ int s_hist[kSortBins];
+  __shared__ int s_warp[32];
+  __shared__ unsigned short s_bin[kSortStash];
+  // let the dependent (tile) kernel's CTAs be scheduled right away: they wait for this grid's
+  // completion (griddepcontrol.wait) before they read the permutation
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  const int b = blockIdx.x, tid = threadIdx.x;
+  for (int i = tid; i < kSortBins; i += kSortThreads) s_hist[i] = 0;
+  __syncthreads();
+  const int HK = 1 << hk_shift;
+  const size_t hstride = (size_t)d.L * d.P * 2;
+  const T* lb = loc + (size_t)b * d.Lq * d.M * hstride;
+  const float scale = (float)kSortBins / (float)(4 * HK);
+  const bool stash = d.Lq <= kSortStash;
+  const int items = d.Lq << hk_shift;
+  const int items_up = (items + kSortThreads - 1) / kSortThreads * kSortThreads;
+  auto bin_of = [&](int item) -> int {   // all lanes of a warp call it together
+    const int q = item >> hk_shift, hd = item & (HK - 1);
+    float s = item < items ? SortKey<T>::sum4(lb + ((size_t)q * d.M + hd) * hstride) : 0.f;
+    for (int o = 1; o < HK; o <<= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    // NaN -> bin 0 (fmaxf drops it), +-inf clamp
+    return __float2int_rd(fminf(fmaxf(s * scale, 0.f), (float)(kSortBins - 1)));
+  };
+#pragma unroll 4
+  for (int item = tid; item < items_up; item += kSortThreads) {
+    const int bin = bin_of(item);
+    if (item < items && (item & (HK - 1)) == 0) {
+      atomicAdd(&s_hist[bin], 1);
+      if (stash) s_bin[item >> hk_shift] = (unsigned short)bin;
+    }
+  }
+  __syncthreads();
+  // exclusive scan of the histogram: 4 bins per thread, shuffle scan per warp, then over warps
+  constexpr int PER = kSortBins / kSortThreads;
+  int v[PER], sum = 0;
+#pragma unroll
+  for (int k = 0; k < PER; ++k) { v[k] = s_hist[tid * PER + k]; sum += v[k]; }
+  int inc = sum;
+#pragma unroll
+  for (int s = 1; s < 32; s <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, inc, s);
+    if ((tid & 31) >= s) inc += t;
+  }
+  if ((tid & 31) == 31) s_warp[tid >> 5] = inc;
+  __syncthreads();
+  if (tid < 32) {
+    int w = s_warp[tid], wi = w;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, wi, s);
+      if (tid >= s) wi += t;
+    }
+    s_warp[tid] = wi - w;
+  }
+  __syncthreads();
+  int run = s_warp[tid >> 5] + inc - sum;
+#pragma unroll
+  for (int k = 0; k < PER; ++k) { s_hist[tid * PER + k] = run; run += v[k]; }
+  __syncthreads();
+  int* pb = perm + (size_t)b * d.Lq;
+  if (stash) {
+    for (int q = tid; q < d.Lq; q += kSortThreads) pb[atomicAdd(&s_hist[s_bin[q]], 1)] = q;
+  } else {
+#pragma unroll 4
+    for (int item = tid; item < items_up; item += kSortThreads) {
+      const int bin = bin_of(item);
+      if (item < items && (item & (HK - 1)) == 0) pb[atomicAdd(&s_hist[bin], 1)] = item >> hk_shift;
+    }
+  }
+}
+
+// Loads of data the PRECEDING kernel of a programmatic dependent launch produced (the query order,
+// the plan): plain ld.global behind griddepcontrol.wait.  A __ldg / const __restrict__ load is
+// "invariant" to the compiler and may be hoisted above the wait.
+__device__ __forceinline__ void tile_grid_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ int tile_ld_dep(const int* p) {
+  int v;
+  asm volatile("ld.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ int4 tile_ld_dep4(const void* p) {
+  int4 v;
+  asm volatile("ld.global.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+
+// ---- mbarrier / TMA ------------------------------------------------------------
+__device__ __forceinline__ unsigned tile_smem_u32(const void* p) {
+  return (unsigned)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void tile_mbar_init(unsigned long long* mbar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(tile_smem_u32(mbar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void tile_mbar_expect_tx(unsigned long long* mbar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(tile_smem_u32(mbar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void tile_mbar_wait(unsigned long long* mbar, unsigned parity) {
+  const unsigned a = tile_smem_u32(mbar);
+  unsigned ok, spins = 0;
+  do {
+    // a TMA box that never lands (a rejected descriptor) must fault, not hang the device
+    if (++spins > (1u << 22)) __trap();
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(a), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+// one box (kTileBoxRows rows x D channels) of the value tensor viewed as [N*S rows][M*D]
+__device__ __forceinline__ void tile_tma_load(void* smem_dst, const CUtensorMap* map, int col, int row,
+                                              unsigned long long* mbar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+      ::"r"(tile_smem_u32(smem_dst)), "l"(reinterpret_cast<unsigned long long>(map)), "r"(col), "r"(row),
+      "r"(tile_smem_u32(mbar))
+      : "memory");
+}
+
+// a unit of a value row from the shared-memory tile
+template <typename U>
+__device__ __forceinline__ void tile_lds(const char* p, typename U::Raw (&buf)[U::RW]) {
+  using Raw = typename U::Raw;
+  if constexpr (U::RW == 4) {
+    const uint4 t = *reinterpret_cast<const uint4*>(p);
+    if constexpr (std::is_same<Raw, float>::value) {
+      buf[0] = __uint_as_float(t.x); buf[1] = __uint_as_float(t.y);
+      buf[2] = __uint_as_float(t.z); buf[3] = __uint_as_float(t.w);
+    } else {
+      buf[0] = t.x; buf[1] = t.y; buf[2] = t.z; buf[3] = t.w;
+    }
+  } else {
+    const uint2 t = *reinterpret_cast<const uint2*>(p);
+    buf[0] = t.x; buf[1] = t.y;
+  }
+}
+
+// ---- the tile's plan ------------------------------------------------------------
+// Everything a thread knows after the prologue.  Block = the 8 lanes that share g = tid / 8;
+// lane (qi = j & 3, h = j >> 2) owns the points of query qi at levels h and h + 2.
+struct TilePlan {
+  int blo[kWinMaxL];     // first slab row of the block's window per level
+  int brows[kWinMaxL];   // rows of the block's window per level (0: none)
+  int wrows[kWinMaxL];   // the largest brows of the warp's 4 blocks (PAIR: rounded up to even): the
+                         // warp-uniform trip count; rows past brows carry zero weights
+  int wmax[kWinMaxL];    // the same before rounding (what a forward over a PAIR plan loops to)
+  int bpoff[kWinMaxL];   // packed position of the level inside the block's plan (warp-uniform)
+  int trow[kWinMaxL];    // row of the shared-memory tile that holds slab row blo[l] (0 if none)
+  int tlo[kWinMaxL];     // first slab row of the TILE's window per level
+  int tbase[kWinMaxL];   // row of the shared-memory tile where that level starts
+  int rt;                // packed rows of the block's plan (warp-uniform)
+  int total;             // rows of the shared-memory tile in use (multiple of the box)
+  bool ok;               // false: the tile runs the per-tap body
+};
+
+// Geometry of the thread's points, block and tile windows, TMA issue, weight scatter.
+// PAIR: row loops run over pairs of rows (backward): every level of a plan is padded to an even
+// row count.
+// On return (plan.ok) the block's weights are in Wt, the value boxes are in flight on mbar.
+template <typename T, bool PAIR, bool ISSUE = true>
+__device__ __forceinline__ void tile_prologue(const CUtensorMap* vmap, const T* __restrict__ loc,
+                                              const T* __restrict__ aw, const Dims& d, int b, int m,
+                                              int q, const int* s_lvl, int* s_win, char* vtile,
+                                              unsigned row_bytes, float4* Wt,
+                                              unsigned long long* mbar, TilePlan& pl) {
+  constexpr unsigned FULL = 0xffffffffu;
+  const int tid = threadIdx.x, j = tid & 7, qi = j & 3, h = j >> 2;
+  const int gbase = (tid & 31) & ~7;
+  const bool have_q = q >= 0;
+  const int LP = d.L * kWinP;
+  const size_t grp = ((size_t)b * d.Lq + (have_q ? q : 0)) * d.M + m;
+
+  int r0[2][4];
+  float w0[2][4], w1[2][4];
+  int lo[2], hi[2];
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int l = h + 2 * i;
+    const bool active = have_q && l < d.L;
+    const int ls = l < d.L ? l : 0;
+    float x[4], y[4], a[4];
+    WinPts<T>::ld(loc + (grp * LP + ls * kWinP) * 2, aw + grp * LP + ls * kWinP, x, y, a);
+    const int W = s_lvl[3 * ls + 1], start = s_lvl[3 * ls + 2];
+    lo[i] = kTileBig; hi[i] = -kTileBig;
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      WinCoef c;
+      bool live, v0, v1;
+      win_point<false>(x[p], y[p], a[p], W, start, d.border != 0, active, r0[i][p], w0[i][p], w1[i][p],
+                       live, v0, v1, c);
+      lo[i] = min(lo[i], live ? r0[i][p] : kTileBig);
+      hi[i] = max(hi[i], live ? r0[i][p] + 1 : -kTileBig);
+    }
+    // a live point has -1 <= w_low <= W - 1: clip the pair to the map
+    lo[i] = max(lo[i], start);
+    hi[i] = min(hi[i], start + W - 1);
+  }
+  // the block's window per level: agree over its 4 queries
+#pragma unroll
+  for (int s = 1; s <= 2; s <<= 1)
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      lo[i] = min(lo[i], __shfl_xor_sync(FULL, lo[i], s));
+      hi[i] = max(hi[i], __shfl_xor_sync(FULL, hi[i], s));
+    }
+  // the tile's window per level
+  if (qi == 0) {
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+      if (hi[i] >= lo[i]) {
+        atomicMin(&s_win[h + 2 * i], lo[i]);
+        atomicMax(&s_win[kWinMaxL + h + 2 * i], hi[i]);
+      }
+  }
+  // every lane learns all levels of its block; pack them back to back
+  int rt = 0;
+#pragma unroll
+  for (int l = 0; l < kWinMaxL; ++l) {
+    const int src = gbase + (l & 1) * 4;
+    const int llo = __shfl_sync(FULL, lo[l >> 1], src);
+    const int lhi = __shfl_sync(FULL, hi[l >> 1], src);
+    const int rows = max(lhi - llo + 1, 0);
+    const int wmax = __reduce_max_sync(FULL, rows);
+    pl.blo[l] = llo;
+    pl.brows[l] = rows;
+    pl.wmax[l] = wmax;
+    pl.wrows[l] = PAIR ? (wmax + 1) & ~1 : wmax;
+    pl.bpoff[l] = rt;
+    rt += pl.wrows[l];
+  }
+  tile_stamp(2);
+  const bool over = __syncthreads_or(rt > kTileBlkRows) != 0;
+  tile_stamp(3);
+
+  int tlo[kWinMaxL], tbase[kWinMaxL];
+  int total = 0;
+#pragma unroll
+  for (int l = 0; l < kWinMaxL; ++l) {
+    const int llo = s_win[l], lhi = s_win[kWinMaxL + l];
+    const int rows = lhi >= llo ? lhi - llo + 1 : 0;
+    tlo[l] = llo;
+    tbase[l] = total;
+    total += (rows + kTileBoxRows - 1) / kTileBoxRows * kTileBoxRows;
+  }
+  pl.total = total;
+  pl.rt = rt;
+#pragma unroll
+  for (int l = 0; l < kWinMaxL; ++l) { pl.tlo[l] = tlo[l]; pl.tbase[l] = tbase[l]; }
+  pl.ok = !over && total <= kTileCapRows;
+  if (!pl.ok) return;
+#pragma unroll
+  for (int l = 0; l < kWinMaxL; ++l) pl.trow[l] = pl.brows[l] > 0 ? tbase[l] + pl.blo[l] - tlo[l] : 0;
+
+  if (ISSUE && tid == 0 && total > 0) {
+    tile_mbar_expect_tx(mbar, (unsigned)total * row_bytes);
+#pragma unroll
+    for (int l = 0; l < kWinMaxL; ++l) {
+      const int nb = ((l + 1 < kWinMaxL ? tbase[l + 1] : total) - tbase[l]) / kTileBoxRows;
+      for (int k = 0; k < nb; ++k)
+        tile_tma_load(vtile + (size_t)(tbase[l] + k * kTileBoxRows) * row_bytes, vmap, m * d.D,
+                      b * d.S + tlo[l] + k * kTileBoxRows, mbar);
+    }
+  }
+
+  // the block's weight matrix: zero, then every lane scatters its own columns (level, qi)
+  for (int t = j; t < rt; t += 8) Wt[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+  __syncwarp();
+  float* Wf = reinterpret_cast<float*>(Wt);
+  int tb[2];
+  tb[0] = h ? pl.bpoff[1] - pl.blo[1] : pl.bpoff[0] - pl.blo[0];
+  tb[1] = h ? pl.bpoff[3] - pl.blo[3] : pl.bpoff[2] - pl.blo[2];
+#pragma unroll
+  for (int p = 0; p < 4; ++p) {
+    float c0[2], c1[2];
+    int t0[2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      t0[i] = (r0[i][p] + tb[i]) * 4 + qi;
+      c0[i] = w0[i][p] != 0.f ? Wf[t0[i]] : 0.f;
+      c1[i] = w1[i][p] != 0.f ? Wf[t0[i] + 4] : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      if (w0[i][p] != 0.f) Wf[t0[i]] = c0[i] + w0[i][p];
+      if (w1[i][p] != 0.f) Wf[t0[i] + 4] = c1[i] + w1[i][p];
+    }
+  }
+  __syncwarp();
+}
+
+// shared state every tile kernel sets up before the prologue; returns whether all maps have H == 1
+__device__ __forceinline__ bool tile_setup(const int64_t* __restrict__ shapes,
+                                           const int64_t* __restrict__ lsi,
+                                           const int* __restrict__ perm, const Dims& d, int b, int chunk,
+                                           int* s_lvl, int* s_win, int* s_q,
+                                           unsigned long long* mbar) {
+  const int tid = threadIdx.x;
+  if (tid < 2 * kWinMaxL) s_win[tid] = tid < kWinMaxL ? kTileBig : -kTileBig;
+  if (tid == 0) tile_mbar_init(mbar, 1);
+  // programmatic dependent launch: this grid may start while the sort grid still runs; its
+  // results (and everything before it in the stream) are visible after this wait
+  tile_grid_wait();
+  if (tid < kTileQ) {
+    const int pos = chunk * kTileQ + tid;
+    s_q[tid] = pos < d.Lq ? tile_ld_dep(perm + (size_t)b * d.Lq + pos) : -1;
+  }
+  return win_stage_levels(shapes, lsi, d.L, s_lvl);   // one barrier
+}
+
+// The per-tap bodies as out-of-line functions: they are the rare path and must not shape the
+// register allocation of the tile path.
+template <typename T, int NU, int NT>
+__device__ __noinline__ void tile_fallback_fwd(const T* value, const T* loc, const T* aw, T* out, Dims d,
+                                               int b, int m, const int* s_lvl, char* scratch,
+                                               const int* s_q) {
+  const int g = threadIdx.x >> 3;
+  fwd_body<T, NU, 8, NT>(value, loc, aw, out, d, b, m, g, kTileQ, kTileBlocks, s_lvl,
+                         reinterpret_cast<TapMeta<NT>*>(scratch) + g * 8, s_q);
+}
+template <typename T, int NU, int NT, typename GV, typename U>
+__device__ __noinline__ void tile_fallback_bwd(const T* value, const T* loc, const T* aw, const T* gout,
+                                               GV* gvalue, T* gloc, T* gaw, Dims d, int b, int m,
+                                               const int* s_lvl, char* scratch, float gv_scale,
+                                               const int* s_q) {
+  const int g = threadIdx.x >> 3;
+  bwd_body<T, NU, 8, NT, GV, U>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, g, kTileQ, kTileBlocks,
+                                s_lvl, reinterpret_cast<TapMeta<NT>*>(scratch) + g * 8, gv_scale, s_q);
+}
+
+template <typename T, int NU>
+struct TileSmem {
+  static constexpr int kRowBytes = NU * 8 * 16;                        // D * sizeof(T)
+  static constexpr int kValueBytes = kTileCapRows * kRowBytes;
+  static constexpr int kPlanBytes = kTileBlocks * kTileBlkRows * 16;
+  static constexpr int kBytes = kValueBytes + kPlanBytes + 128;         // + alignment slack
+};
+
+// ------------------------------- forward ------------------------------------
+template <typename T, int NU>
+__global__ void __launch_bounds__(kTileThreads, MSDA_TILE_FWD_CTAS)
+msda_fwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restrict__ value,
+                     const int64_t* __restrict__ shapes, const int64_t* __restrict__ lsi,
+                     const T* __restrict__ loc, const T* __restrict__ aw,
+                     const int* __restrict__ perm, T* __restrict__ out, Dims d, int nchunks) {
+  using U = Unit<T>;
+  using Raw = typename U::Raw;
+  using SM = TileSmem<T, NU>;
+  constexpr int G = 8;
+  constexpr int E = U::E;
+  constexpr int RB = SM::kRowBytes;
+  __shared__ int s_lvl[3 * kWinMaxL];
+  __shared__ int s_win[2 * kWinMaxL];
+  __shared__ int s_q[kTileQ];
+  __shared__ __align__(8) unsigned long long s_mbar;
+  extern __shared__ __align__(128) char s_raw[];   // TMA destination: 128-byte aligned
+  char* vtile = s_raw;
+  char* s_plan = vtile + SM::kValueBytes;
+
+  const int tid = threadIdx.x, g = tid >> 3, j = tid & 7;
+  const int m = blockIdx.x % d.M;
+  const int t2 = blockIdx.x / d.M;
+  const int chunk = t2 % nchunks, b = t2 / nchunks;
+  tile_stamp(0);
+  const bool one_d = tile_setup(shapes, lsi, perm, d, b, chunk, s_lvl, s_win, s_q, &s_mbar);
+  tile_stamp(1);
+  if (!one_d) {
+    tile_fallback_fwd<T, NU, 4>(value, loc, aw, out, d, b, m, s_lvl, s_plan, s_q);
+    return;
+  }
+  float4* Wt = reinterpret_cast<float4*>(s_plan) + g * kTileBlkRows;
+  TilePlan pl;
+  tile_prologue<T, false>(&vmap, loc, aw, d, b, m, s_q[g * kWinQ + (j & 3)], s_lvl, s_win, vtile, RB, Wt,
+                          &s_mbar, pl);
+  if (!pl.ok) {
+    tile_fallback_fwd<T, NU, 2>(value, loc, aw, out, d, b, m, s_lvl, s_plan, s_q);
+    return;
+  }
+  tile_stamp(4);
+  if (pl.total > 0) tile_mbar_wait(&s_mbar, 0);
+  tile_stamp(5);
+
+  float2 acc[kWinQ][NU][E / 2];
+#pragma unroll
+  for (int q = 0; q < kWinQ; ++q)
+#pragma unroll
+    for (int uu = 0; uu < NU; ++uu)
+#pragma unroll
+      for (int c = 0; c < E / 2; ++c) acc[q][uu][c] = make_float2(0.f, 0.f);
+
+  // warp-uniform row loops: a block past its own rows re-reads its last row against zero weights
+#pragma unroll
+  for (int l = 0; l < kWinMaxL; ++l) {
+    const char* vr = vtile + pl.trow[l] * RB + j * 16;
+    const float4* wl = Wt + pl.bpoff[l];
+    const int n = pl.wrows[l], nb = pl.brows[l];
+#pragma unroll 2
+    for (int i = 0; i < n; ++i) {
+      const float4 wv = wl[i];
+      const float wq[kWinQ] = {wv.x, wv.y, wv.z, wv.w};
+#pragma unroll
+      for (int uu = 0; uu < NU; ++uu) {
+        Raw raw[U::RW];
+        tile_lds<U>(vr + uu * (G * 16), raw);
+        float v[E];
+        U::unpack_raw(raw, v);
+#pragma unroll
+        for (int q = 0; q < kWinQ; ++q) {
+          const float2 w2 = make_float2(wq[q], wq[q]);
+#pragma unroll
+          for (int c = 0; c < E / 2; ++c)
+            acc[q][uu][c] = __ffma2_rn(w2, make_float2(v[2 * c], v[2 * c + 1]), acc[q][uu][c]);
+        }
+      }
+      if (i + 1 < nb) vr += RB;
+    }
+  }
+  tile_stamp(6);
+#pragma unroll
+  for (int q = 0; q < kWinQ; ++q) {
+    const int qq = s_q[g * kWinQ + q];
+    if (qq >= 0) {
+      T* og = out + (((size_t)b * d.Lq + qq) * d.M + m) * d.D + j * E;
+#pragma unroll
+      for (int uu = 0; uu < NU; ++uu) {
+        float o[E];
+#pragma unroll
+        for (int c = 0; c < E / 2; ++c) { o[2 * c] = acc[q][uu][c].x; o[2 * c + 1] = acc[q][uu][c].y; }
+        U::st_stream(og + uu * (G * E), o);
+      }
+    }
+  }
+  tile_stamp(7);
+}
+
+// ------------------------------- backward -----------------------------------
+// Rows come from the shared-memory tile; grad_value rows leave as 128-bit reds (one per row,
+// unit and lane of a block, 4.7 rows per query in time order); the dots <grad_out, value row>
+// are transpose-reduced over the 8 lanes for two rows at a time and stored over the weights;
+// the epilogue reads the points again (L2) and forms grad_attn_weight / grad_sampling_loc.
+template <typename T, int NU, typename GV = float, typename U = Unit<T>>
+__global__ void __launch_bounds__(kTileThreads, MSDA_TILE_BWD_CTAS)
+msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restrict__ value,
+                     const int64_t* __restrict__ shapes, const int64_t* __restrict__ lsi,
+                     const T* __restrict__ loc, const T* __restrict__ aw,
+                     const T* __restrict__ gout, const int* __restrict__ perm,
+                     GV* __restrict__ gvalue, T* __restrict__ gloc, T* __restrict__ gaw, Dims d,
+                     int nchunks, const DetHeader* __restrict__ det) {
+  const float gv_scale = det ? (float)det->scale : 1.f;
+  using Raw = typename U::Raw;
+  constexpr int G = 8;
+  constexpr int E = U::E;
+  constexpr int RB = NU * G * U::BYTES;          // D * sizeof(T)
+  constexpr int kValueBytes = kTileCapRows * RB;
+  __shared__ int s_lvl[3 * kWinMaxL];
+  __shared__ int s_win[2 * kWinMaxL];
+  __shared__ int s_q[kTileQ];
+  __shared__ __align__(8) unsigned long long s_mbar;
+  extern __shared__ __align__(128) char s_raw[];   // TMA destination: 128-byte aligned
+  char* vtile = s_raw;
+  char* s_plan = vtile + kValueBytes;
+
+  const int tid = threadIdx.x, g = tid >> 3, j = tid & 7, qi = j & 3, h = j >> 2;
+  const int m = blockIdx.x % d.M;
+  const int t2 = blockIdx.x / d.M;
+  const int chunk = t2 % nchunks, b = t2 / nchunks;
+  const bool one_d = tile_setup(shapes, lsi, perm, d, b, chunk, s_lvl, s_win, s_q, &s_mbar);
+  if (!one_d) {
+    tile_fallback_bwd<T, NU, 4, GV, U>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, s_lvl, s_plan,
+                                       gv_scale, s_q);
+    return;
+  }
+  // grad_out of the block's 4 queries (this lane's channels): requested first, used after the
+  // prologue, whose work covers their way from HBM
+  Raw gor[kWinQ][NU][U::RW];
+  {
+    const unsigned qstride = (unsigned)(d.M * d.D);
+    const T* gb = gout + ((size_t)b * d.Lq * d.M + m) * d.D + j * E;
+#pragma unroll
+    for (int q = 0; q < kWinQ; ++q) {
+      const int qq = s_q[g * kWinQ + q];
+#pragma unroll
+      for (int uu = 0; uu < NU; ++uu) {
+#pragma unroll
+        for (int k = 0; k < U::RW; ++k) gor[q][uu][k] = Raw(0);
+        U::ldg_keep_stream(reinterpret_cast<const char*>(gb + (size_t)(qq >= 0 ? qq : 0) * qstride +
+                                                         uu * (G * E)),
+                           qq >= 0, gor[q][uu]);
+      }
+    }
+  }
+  const int my_q = s_q[g * kWinQ + qi];
+  float4* Wt = reinterpret_cast<float4*>(s_plan) + g * kTileBlkRows;
+  float* Gs = reinterpret_cast<float*>(Wt);   // the dots G[t][qi] overwrite Wt[t][qi] pair by pair
+  TilePlan pl;
+  tile_prologue<T, true>(&vmap, loc, aw, d, b, m, my_q, s_lvl, s_win, vtile, RB, Wt, &s_mbar, pl);
+  if (!pl.ok) {
+    tile_fallback_bwd<T, NU, 2, GV, U>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, s_lvl, s_plan,
+                                       gv_scale, s_q);
+    return;
+  }
+  float2 go[kWinQ][NU][E / 2];
+#pragma unroll
+  for (int q = 0; q < kWinQ; ++q)
+#pragma unroll
+    for (int uu = 0; uu < NU; ++uu) {
+      float t[E];
+      U::unpack_raw(gor[q][uu], t);
+#pragma unroll
+      for (int c = 0; c < E / 2; ++c) go[q][uu][c] = make_float2(t[2 * c], t[2 * c + 1]);
+    }
+  if (pl.total > 0) tile_mbar_wait(&s_mbar, 0);
+
+  const int MD = d.M * d.D;
+  GV* gvb = gvalue + ((size_t)b * d.S * d.M + m) * d.D + j * E;
+  // warp-uniform row loops over pairs of rows: a block past its own rows re-reads its last row
+  // against zero weights and issues no reds
+#pragma unroll
+  for (int l = 0; l < kWinMaxL; ++l) {
+    const char* vr = vtile + pl.trow[l] * RB + j * U::BYTES;
+    const float4* wl = Wt + pl.bpoff[l];
+    float* gl = Gs + pl.bpoff[l] * 4 + j;
+    GV* gp = gvb + (size_t)pl.blo[l] * MD;
+    const int n = pl.wrows[l], nb = pl.brows[l];
+    for (int i = 0; i < n; i += 2) {
+      float x[2 * kWinQ];
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        const float4 w = wl[i + r];
+        const float wq[kWinQ] = {w.x, w.y, w.z, w.w};
+        const bool real = i + r < nb;
+        float2 s[kWinQ];
+#pragma unroll
+        for (int u = 0; u < NU; ++u) {
+          // grad_value row: sum_q Wt[t][q] * grad_out[q]
+          float2 dv[E / 2];
+#pragma unroll
+          for (int q = 0; q < kWinQ; ++q) {
+            const float2 w2 = make_float2(wq[q], wq[q]);
+#pragma unroll
+            for (int c = 0; c < E / 2; ++c)
+              dv[c] = q == 0 ? __fmul2_rn(w2, go[q][u][c]) : __ffma2_rn(w2, go[q][u][c], dv[c]);
+          }
+#pragma unroll
+          for (int c = 0; c < E / 2; c += 2)
+            GvRed<GV>::add4(gp + u * (G * E) + 2 * c, real, dv[c].x, dv[c].y, dv[c + 1].x, dv[c + 1].y,
+                            gv_scale);
+          // this lane's share of <grad_out[q], value row>
+          Raw raw[U::RW];
+          tile_lds<U>(vr + u * (G * U::BYTES), raw);
+          float v[E];
+          U::unpack_raw(raw, v);
+#pragma unroll
+          for (int q = 0; q < kWinQ; ++q)
+#pragma unroll
+            for (int c = 0; c < E / 2; ++c) {
+              const float2 v2 = make_float2(v[2 * c], v[2 * c + 1]);
+              s[q] = (u == 0 && c == 0) ? __fmul2_rn(go[q][u][c], v2) : __ffma2_rn(go[q][u][c], v2, s[q]);
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < kWinQ; ++q) x[r * kWinQ + q] = s[q].x + s[q].y;
+        gp += MD;
+        if (i + r + 1 < nb) vr += RB;
+      }
+      const float tot = transpose_reduce<8>(x, j, 0xffffffffu);
+      gl[i * 4] = tot;   // (row i + (j >> 2), query j & 3)
+    }
+  }
+  __syncwarp();
+
+  // per-point gradients: the points again, the geometry again, the dots
+  const bool have_q = my_q >= 0;
+  const int LP = d.L * kWinP;
+  const size_t grp_me = ((size_t)b * d.Lq + (have_q ? my_q : 0)) * d.M + m;
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int l = h + 2 * i;
+    const bool active = have_q && l < d.L;
+    const int ls = l < d.L ? l : 0;
+    float x[4], y[4], a[4];
+    WinPts<T>::ld_stream(loc + (grp_me * LP + ls * kWinP) * 2, aw + grp_me * LP + ls * kWinP, x, y, a);
+    const int W = s_lvl[3 * ls + 1], start = s_lvl[3 * ls + 2];
+    const int tb = i == 0 ? (h ? pl.bpoff[1] - pl.blo[1] : pl.bpoff[0] - pl.blo[0])
+                          : (h ? pl.bpoff[3] - pl.blo[3] : pl.bpoff[2] - pl.blo[2]);
+    float gx[4], gy[4], ga[4];
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      int r0;
+      float w0, w1;
+      bool live, v0, v1;
+      WinCoef c;
+      win_point<true>(x[p], y[p], a[p], W, start, d.border != 0, active, r0, w0, w1, live, v0, v1, c);
+      const int t0 = (r0 + tb) * 4 + qi;
+      const float g0 = v0 ? Gs[t0] : 0.f;
+      const float g1 = v1 ? Gs[t0 + 4] : 0.f;
+      ga[p] = fmaf(c.k0, g0, c.k1 * g1);
+      gx[p] = c.fx * (g1 - g0);
+      gy[p] = fmaf(c.cy0, g0, c.cy1 * g1);
+    }
+    if (active)
+      WinPts<T>::st(gloc + (grp_me * LP + l * kWinP) * 2, gaw + grp_me * LP + l * kWinP, gx, gy, ga);
+  }
+}
+
+}  // namespace msda

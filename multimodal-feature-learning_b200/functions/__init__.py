@@ -1,7 +1,9 @@
-# mirrors models/ops/functions/__init__.py:9 (the PyTorch fallback
-# ms_deform_attn_core_pytorch is NOT re-exported: this package has no CPU path;
-# its restatement lives in oracle/ as test infrastructure only)
+# mirrors models/ops/functions/__init__.py:9.  ms_deform_attn_core_pytorch keeps its name and
+# signature but has no PyTorch/grid_sample body here: it runs the `border`-mode kernels (CUDA only);
+# the grid_sample restatement lives in oracle/ as test infrastructure.
 from .frontend import MSDeformFrontendFunction, msdeform_frontend
-from .ms_deform_attn_func import MSDeformAttnFunction, ms_deform_attn
+from .ms_deform_attn_func import (MSDeformAttnBorderFunction, MSDeformAttnFunction, ms_deform_attn,
+                                  ms_deform_attn_core_pytorch)
 
-__all__ = ["MSDeformAttnFunction", "ms_deform_attn", "MSDeformFrontendFunction", "msdeform_frontend"]
+__all__ = ["MSDeformAttnFunction", "MSDeformAttnBorderFunction", "ms_deform_attn",
+           "ms_deform_attn_core_pytorch", "MSDeformFrontendFunction", "msdeform_frontend"]

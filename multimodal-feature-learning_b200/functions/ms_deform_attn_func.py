@@ -24,11 +24,12 @@ class _MSDeformAttnBase(Function):
     def _fwd(cls, ctx, value, value_spatial_shapes, value_level_start_index,
              sampling_locations, attention_weights, im2col_step):
         ctx.im2col_step = im2col_step
-        output = MSDA.ms_deform_attn_forward(
+        output, plan = MSDA.ms_deform_attn_forward(
             value, value_spatial_shapes, value_level_start_index, sampling_locations,
-            attention_weights, ctx.im2col_step, padding_mode=cls.padding_mode)
+            attention_weights, ctx.im2col_step, padding_mode=cls.padding_mode, return_plan=True)
         ctx.save_for_backward(value, value_spatial_shapes, value_level_start_index,
                               sampling_locations, attention_weights)
+        ctx.msda_plan = plan     # time order of the queries (6 KB per batch item at the encoder shape)
         return output
 
     @classmethod
@@ -39,7 +40,7 @@ class _MSDeformAttnBase(Function):
         flags = _lib.MSDA_FLAG_DETERMINISTIC if torch.are_deterministic_algorithms_enabled() else 0
         grad_value, grad_loc, grad_aw = MSDA.ms_deform_attn_backward(
             value, shapes, lsi, loc, aw, grad_output, ctx.im2col_step,
-            padding_mode=cls.padding_mode, flags=flags)
+            padding_mode=cls.padding_mode, flags=flags, plan=getattr(ctx, "msda_plan", None))
         return grad_value, None, None, grad_loc, grad_aw, None
 
 
@@ -87,3 +88,22 @@ def ms_deform_attn(value, value_spatial_shapes, value_level_start_index, samplin
     fn = {"zeros": MSDeformAttnFunction, "border": MSDeformAttnBorderFunction}[padding_mode]
     return fn.apply(value, value_spatial_shapes, value_level_start_index, sampling_locations,
                     attention_weights, im2col_step)
+
+
+def ms_deform_attn_core_pytorch(value, value_spatial_shapes, sampling_locations, attention_weights,
+                                return_value=False):
+    """The name the reference exports next to the autograd Function
+    (models/ops/functions/__init__.py:9; imported by models/ops/test.py:18 and
+    models/ops/modules/ms_deform_attn.py:21).  There it is the grid_sample (`border` padding)
+    restatement of the op; here the same function -- same arguments, same [N, Lq, M*D] result,
+    differentiable -- runs the `border`-mode kernels (MSDeformAttnBorderFunction).  CUDA tensors
+    only: CPU tensors raise "Not implemented on the CPU" like everything else in this package.
+    `return_value=True` (the per-point sampled values, MSDeformAttnCap) is out of scope."""
+    if return_value:
+        raise NotImplementedError("return_value=True (MSDeformAttnCap) is outside this package's hot path")
+    shapes = torch.as_tensor(value_spatial_shapes, dtype=torch.long, device=value.device).reshape(-1, 2)
+    sizes = shapes[:, 0] * shapes[:, 1]
+    lsi = torch.cat((sizes.new_zeros((1,)), sizes.cumsum(0)[:-1]))
+    return MSDeformAttnBorderFunction.apply(value.contiguous(), shapes.contiguous(), lsi,
+                                            sampling_locations.contiguous(),
+                                            attention_weights.contiguous(), 64)

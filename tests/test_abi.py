@@ -29,7 +29,7 @@ def test_header_symbols_exported(lib):
 
 
 def test_abi_version_and_strings(lib):
-    assert lib.msda_abi_version() == 1
+    assert lib.msda_abi_version() == _lib.ABI_VERSION == 2
     assert lib.msda_error_string(0) == b"ok"
     assert b"dtype" in lib.msda_error_string(-3)
     assert lib.msda_kernel_family(64, _lib.MSDA_F32, 0) == b"fast"
@@ -39,11 +39,18 @@ def test_abi_version_and_strings(lib):
     assert lib.msda_kernel_family(64, _lib.MSDA_F32, _lib.MSDA_FLAG_FORCE_GENERIC) == b"generic"
     enc = (16, 1500, 8, 64, 4, 1500, 4)
     dec = (64, 1500, 8, 64, 4, 100, 4)
-    assert lib.msda_kernel_choice(*enc, _lib.MSDA_F32, 0) == b"window"
-    assert lib.msda_kernel_choice(*enc, _lib.MSDA_BF16, 0) == b"window"
+    assert lib.msda_kernel_choice(*enc, _lib.MSDA_F32, 0) == b"tile"
+    assert lib.msda_kernel_choice(*enc, _lib.MSDA_BF16, 0) == b"tile"
+    assert lib.msda_kernel_choice(*enc, _lib.MSDA_F32, _lib.MSDA_FLAG_NO_TILE) == b"window"
+    assert lib.msda_forward_workspace_bytes(*enc, _lib.MSDA_F32, _lib.MSDA_FLAG_NO_PLAN) == 16 * 1500 * 4
+    tiles = 16 * 8 * ((1500 + 63) // 64)     # the plan of the split path: 13 KB per tile of 64 queries
+    assert lib.msda_forward_workspace_bytes(*enc, _lib.MSDA_F32, 0) >= 16 * 1500 * 4 + tiles * 12288
+    assert lib.msda_forward_workspace_bytes(*enc, _lib.MSDA_F32, _lib.MSDA_FLAG_NO_TILE) == 0
+    assert lib.msda_backward_workspace_bytes_flags(*enc, _lib.MSDA_F32, 0) == 16 * 1500 * 4
     assert lib.msda_kernel_choice(*enc, _lib.MSDA_F32, _lib.MSDA_FLAG_NO_WINDOW) == b"fast"
     assert lib.msda_kernel_choice(*dec, _lib.MSDA_F32, 0) == b"fast"           # short query list
-    assert lib.msda_kernel_choice(*dec, _lib.MSDA_F32, _lib.MSDA_FLAG_FORCE_WINDOW) == b"window"
+    assert lib.msda_kernel_choice(*dec, _lib.MSDA_F32, _lib.MSDA_FLAG_FORCE_WINDOW) == b"tile"
+    assert lib.msda_forward_workspace_bytes(*dec, _lib.MSDA_F32, 0) == 0
     assert lib.msda_kernel_choice(*enc, _lib.MSDA_F64, 0) == b"generic"
     assert lib.msda_kernel_choice(16, 1500, 8, 64, 4, 1500, 8, _lib.MSDA_F32, 0) == b"fast"   # P != 4
     assert lib.msda_kernel_choice(16, 1500, 8, 64, 4, 1500, 4, 7, 0) == b"invalid"
@@ -109,3 +116,17 @@ def test_product_never_imports_oracle():
                 assert "import oracle" not in text and "from oracle" not in text, f
                 if f.endswith(".py"):
                     assert "F.grid_sample(" not in text, f
+
+
+def test_reference_names_resolve():
+    """models/ops/functions/__init__.py:9 and `import MultiScaleDeformableAttention as MSDA`
+    (ms_deform_attn_func.py:18-21) resolve against this repo; CPU tensors raise."""
+    import torch
+    from mfl_b200.functions import MSDeformAttnFunction, ms_deform_attn_core_pytorch  # noqa: F401
+    import MultiScaleDeformableAttention as MSDA
+    assert callable(MSDA.ms_deform_attn_forward) and callable(MSDA.ms_deform_attn_backward)
+    v = torch.zeros(1, 6, 2, 4)
+    loc = torch.zeros(1, 3, 2, 1, 2, 2)
+    aw = torch.zeros(1, 3, 2, 1, 2)
+    with pytest.raises(RuntimeError, match="Not implemented on the CPU"):
+        ms_deform_attn_core_pytorch(v, [(2, 3)], loc, aw)

@@ -69,15 +69,17 @@ def test_bitwise_reproducible_under_contention():
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["f32", "bf16"])
 def test_window_and_per_tap_families_are_each_reproducible(oracle_c, dtype):
-    """An encoder-like call (row-window kernels, with blocks that fall back) and the same call on
-    the per-tap kernels: both deterministic, both within the oracle tolerance."""
+    """An encoder-like call on the CTA-tile kernels, on the row-window kernels (with blocks that
+    fall back) and on the per-tap kernels: all deterministic, all within the oracle tolerance."""
     T = [96, 48, 24, 12]
     inp = synthetic.make_inputs(2, sum(T), 8, 64, 4, [(1, t) for t in T], dtype, DEV, seed=9, dist="model",
                                 value="normal", enc_ref=True)
     f = {k: (v.float() if v.is_floating_point() else v) for k, v in inp.items()}
     want = oracle_c.backward(*[f[k] for k in ("value", "shapes", "lsi", "loc", "aw")], f["grad_out"], "zeros")
     lib = _lib.load()
-    for fl, fam in ((_lib.MSDA_FLAG_FORCE_WINDOW, "window"), (_lib.MSDA_FLAG_NO_WINDOW, "fast")):
+    for fl, fam in ((_lib.MSDA_FLAG_FORCE_WINDOW, "tile"),
+                    (_lib.MSDA_FLAG_FORCE_WINDOW | _lib.MSDA_FLAG_NO_TILE, "window"),
+                    (_lib.MSDA_FLAG_NO_WINDOW, "fast")):
         assert lib.msda_kernel_choice(2, sum(T), 8, 64, 4, sum(T), 4, 0 if dtype == torch.float32 else 2, fl).decode() == fam
         a = bwd(inp, "zeros", DET | fl)
         b = bwd(inp, "zeros", DET | fl)

@@ -224,3 +224,23 @@ def test_non_default_stream():
         out = MSDeformAttnFunction.apply(*args, 64)
     st.synchronize()
     assert torch.equal(out, ref)
+
+
+def test_core_pytorch_name_runs_border_kernels():
+    """functions.ms_deform_attn_core_pytorch (the name the reference exports,
+    models/ops/functions/__init__.py:9) == the oracle port of the reference function, forward
+    and gradients, on CUDA tensors."""
+    from mfl_b200.functions import ms_deform_attn_core_pytorch
+    from oracle.core_pytorch import ms_deform_attn_core_pytorch as ref_fn
+    shapes_hw = [(6, 4), (3, 2)]
+    inp = synthetic.make_inputs(2, 9, 2, 8, 2, shapes_hw, torch.float32, "cuda", seed=21, dist="spill",
+                                requires_grad=True)
+    out = ms_deform_attn_core_pytorch(inp["value"], shapes_hw, inp["loc"], inp["aw"])
+    out.backward(inp["grad_out"])
+    cpu = {k: v.detach().cpu() for k, v in inp.items()}
+    v, loc, aw = (cpu[k].clone().requires_grad_(True) for k in ("value", "loc", "aw"))
+    want = ref_fn(v, cpu["shapes"], loc, aw, "border")
+    want.backward(cpu["grad_out"])
+    assert float((out.detach().cpu() - want.detach()).abs().max()) <= 1e-5
+    for got, ref in ((inp["value"].grad, v.grad), (inp["aw"].grad, aw.grad)):
+        assert float((got.cpu() - ref).abs().max() / ref.abs().max().clamp_min(1e-30)) <= 1e-4

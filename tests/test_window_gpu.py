@@ -1,4 +1,7 @@
-"""GPU suite for the row-window kernels (csrc/msda_win.cuh) against the C oracle.
+"""GPU suite for the row-window kernels (csrc/msda_win.cuh) and the CTA-tile kernels
+(csrc/msda_tile.cuh: time-sorted query tiles, TMA-filled shared memory) against the C oracle.
+Every case runs through both families (`fam`): "tile" is what the shape class gets by default,
+"window" is the same call with MSDA_FLAG_NO_TILE.
 
 The window path is taken per block of 4 consecutive queries whose packed per-level
 windows fit kWinCap rows; everything else in the same launch runs the per-tap body.
@@ -26,6 +29,12 @@ GRAD_REL_F32 = 1e-4
 BF16_FWD_REL = 2.0 ** -7
 BF16_GRAD_REL = 2e-2
 WIN = _lib.MSDA_FLAG_FORCE_WINDOW
+FAMILY_FLAGS = {"tile": WIN, "window": WIN | _lib.MSDA_FLAG_NO_TILE}
+
+
+@pytest.fixture(params=["tile", "window"])
+def fam(request):
+    return FAMILY_FLAGS[request.param]
 
 
 def rel_err(a, b):
@@ -92,17 +101,17 @@ def make(case, dtype, seed, dist="model"):
 
 @pytest.mark.parametrize("case", CASES, ids=IDS)
 @pytest.mark.parametrize("padding", ["zeros", "border"])
-def test_window_fp32_model_locations(oracle_c, case, padding):
+def test_window_fp32_model_locations(oracle_c, case, padding, fam):
     inp = make(case, torch.float32, seed=11)
-    check_f32(run_cuda(inp, padding, WIN), run_oracle(oracle_c, inp, padding), smooth_mask(inp))
+    check_f32(run_cuda(inp, padding, fam), run_oracle(oracle_c, inp, padding), smooth_mask(inp))
 
 
 @pytest.mark.parametrize("case", CASES[:4], ids=IDS[:4])
 @pytest.mark.parametrize("padding", ["zeros", "border"])
-def test_window_matches_per_tap_kernels(case, padding):
+def test_window_matches_per_tap_kernels(case, padding, fam):
     """Same launch arguments through both kernel families."""
     inp = make(case, torch.float32, seed=12)
-    a = run_cuda(inp, padding, WIN)
+    a = run_cuda(inp, padding, fam)
     b = run_cuda(inp, padding, _lib.MSDA_FLAG_NO_WINDOW)
     assert np.abs(a[0] - b[0]).max() <= 2e-6
     m = smooth_mask(inp)
@@ -111,7 +120,7 @@ def test_window_matches_per_tap_kernels(case, padding):
 
 
 @pytest.mark.parametrize("padding", ["zeros", "border"])
-def test_window_vertical_coordinate_and_edges(oracle_c, padding):
+def test_window_vertical_coordinate_and_edges(oracle_c, padding, fam):
     """(1, W) maps with y != 0.5 (the single row is the low or the high row of the vertical
     pair), x running off both ends, and a NaN location."""
     inp = make(CASES[0], torch.float32, seed=13)
@@ -122,7 +131,7 @@ def test_window_vertical_coordinate_and_edges(oracle_c, padding):
     loc[:, -8:, :, :, :, 0] += 0.05                                                     # off the right end
     loc[0, 17, 1, 2, 3, 0] = float("nan")
     inp["loc"] = loc.contiguous()
-    got = run_cuda(inp, padding, WIN)
+    got = run_cuda(inp, padding, fam)
     assert np.isfinite(got[0]).all()
     ref = dict(inp)
     if padding == "zeros":
@@ -138,21 +147,51 @@ def test_window_vertical_coordinate_and_edges(oracle_c, padding):
         check_f32(got, want, m)
 
 
-def test_window_uniform_locations_fall_back(oracle_c):
-    """Random locations: every block exceeds the window capacity and runs the per-tap body
-    inside the window launch."""
+def test_window_uniform_locations_fall_back(oracle_c, fam):
+    """Random locations: every block / tile exceeds the window capacity and runs the per-tap body
+    inside the window / tile launch."""
     inp = make(CASES[0], torch.float32, seed=14, dist="uniform")
-    check_f32(run_cuda(inp, "zeros", WIN), run_oracle(oracle_c, inp, "zeros"), smooth_mask(inp))
+    check_f32(run_cuda(inp, "zeros", fam), run_oracle(oracle_c, inp, "zeros"), smooth_mask(inp))
 
 
 @pytest.mark.parametrize("case", [CASES[0], CASES[1]], ids=[IDS[0], IDS[1]])
 @pytest.mark.parametrize("padding", ["zeros", "border"])
-def test_window_bf16(oracle_c, case, padding):
+def test_window_bf16(oracle_c, case, padding, fam):
     inp = make(case, torch.bfloat16, seed=15)
-    got, want = run_cuda(inp, padding, WIN), run_oracle(oracle_c, inp, padding)
+    got, want = run_cuda(inp, padding, fam), run_oracle(oracle_c, inp, padding)
     assert rel_err(got[0], want[0]) <= BF16_FWD_REL
     for g_, w_, nm in zip(got[1:], want[1:], ("grad_value", "grad_loc", "grad_aw")):
         assert rel_err(g_, w_) <= BF16_GRAD_REL, nm
+
+
+def test_permuted_queries_tile_bitwise_equal():
+    """The tile kernels take the queries in time order: permuting the query list (the sparse
+    encoders' score-ordered top-k tokens) permutes the output rows and nothing else, bitwise."""
+    inp = make(CASES[0], torch.float32, seed=17)
+    a = [inp[k] for k in ("value", "shapes", "lsi", "loc", "aw")]
+    o0 = MSDA.ms_deform_attn_forward(*a, 64, flags=WIN)
+    g = torch.Generator(device=DEV).manual_seed(3)
+    perm = torch.randperm(inp["loc"].shape[1], device=DEV, generator=g)
+    a[3], a[4] = inp["loc"][:, perm].contiguous(), inp["aw"][:, perm].contiguous()
+    o1 = MSDA.ms_deform_attn_forward(*a, 64, flags=WIN)
+    assert torch.equal(o0[:, perm], o1)
+
+
+def test_tile_2d_maps_and_forward_plan_reuse(oracle_c):
+    """(a) maps with H != 1 inside a tile launch run the 4-tap body; (b) the plan msda_forward_ex
+    leaves behind gives the same backward as a backward that sorts for itself."""
+    inp = synthetic.make_inputs(2, 300, 4, 64, 4, [(4, 8), (2, 4)], torch.float32, DEV, seed=18, dist="uniform")
+    check_f32(run_cuda(inp, "zeros", WIN), run_oracle(oracle_c, inp, "zeros"), smooth_mask(inp))
+    inp = make(CASES[0], torch.float32, seed=19)
+    v, s, l, loc, aw, go = (inp[k] for k in ("value", "shapes", "lsi", "loc", "aw", "grad_out"))
+    out, plan = MSDA.ms_deform_attn_forward(v, s, l, loc, aw, 64, flags=WIN, return_plan=True)
+    assert plan is not None
+    srt = plan[:2 * loc.shape[1]].view(2, -1).sort(1)[0]
+    assert torch.equal(srt, torch.arange(loc.shape[1], device=DEV, dtype=torch.int32).expand(2, -1))
+    g0 = MSDA.ms_deform_attn_backward(v, s, l, loc, aw, go, 64, flags=WIN, plan=plan)
+    g1 = MSDA.ms_deform_attn_backward(v, s, l, loc, aw, go, 64, flags=WIN)
+    assert torch.equal(g0[1], g1[1]) and torch.equal(g0[2], g1[2])
+    assert rel_err(g0[0].cpu().numpy(), g1[0].cpu().numpy()) <= 1e-6
 
 
 def test_window_default_heuristic_and_determinism():

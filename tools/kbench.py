@@ -24,7 +24,7 @@ def main():
     ap.add_argument("--dists", default="model,uniform")
     ap.add_argument("--dtypes", default="f32,bf16")
     ap.add_argument("--iters", type=int, default=50)
-    ap.add_argument("--flags", default="0,4")
+    ap.add_argument("--flags", default="0,32,4", help="0 = default (tile), 32 = no tile (row windows), 4 = per-tap")
     ap.add_argument("--N", type=int, default=0, help="override the workload's batch size")
     ap.add_argument("--ring", type=int, default=4, help="distinct input sets rotated (1 = L2-resident inputs)")
     ap.add_argument("--lib", default="", help="A/B aid: load this build of libmsda_b200.so instead of the in-tree one")
@@ -50,7 +50,7 @@ def main():
                 for fl in [int(x) for x in args.flags.split(",")]:
                     bufs = [bench.OpBuffers(i, "zeros", 0) for i in ring]
                     for b in bufs:
-                        b.flags |= fl
+                        b.set_flags(b.flags | fl)
                     b0 = bufs[0]
                     fb, bb = synthetic.algorithmic_bytes(b0.N, b0.S, b0.Lq, b0.M, b0.D, b0.L, b0.P,
                                                          ring[0]["value"].element_size())

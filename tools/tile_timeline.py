@@ -1,0 +1,40 @@
+#!/usr/bin/env python
+"""Phase timeline of the forward tile kernel from a -DMSDA_TILE_TIMING build (variants/timing.so):
+globaltimer stamps of thread 0 of every CTA.  Dev aid."""
+import ctypes
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from mfl_b200 import _lib  # noqa: E402
+
+_lib.LIB_PATH = os.path.join(ROOT, "variants", "timing.so")
+import bench  # noqa: E402
+from mfl_b200 import synthetic  # noqa: E402
+
+dev = torch.device("cuda", 0)
+ring = [synthetic.make_workload("ENC", torch.float32, dev, seed=1234 + r, dist="model", value="normal") for r in range(4)]
+bufs = [bench.OpBuffers(i, "zeros", 0) for i in ring]
+st = torch.cuda.current_stream().cuda_stream
+for i in range(9):
+    bufs[i % 4].fwd(st)
+torch.cuda.synchronize()
+lib = _lib.load()
+n = 3072
+host = (ctypes.c_ulonglong * (8 * n))()
+lib.msda_debug_tile_times.argtypes = [ctypes.c_void_p, ctypes.c_int]
+assert lib.msda_debug_tile_times(host, 8 * n) == 0
+t = np.array(host, dtype=np.float64).reshape(n, 8)
+t0 = t[:, 0].min()
+names = ["start->setup(perm)", "setup->geometry done", "geometry->barrier", "barrier->plan built(TMA issued)",
+         "plan->V landed", "V->rows done", "rows->stored"]
+d = np.diff(t, axis=1)
+print("kernel span %.1f us, CTA life mean %.2f us" % ((t[:, 7].max() - t0) / 1e3, (t[:, 7] - t[:, 0]).mean() / 1e3))
+for k, nm in enumerate(names):
+    print("  %-34s mean %6.0f ns  p10 %6.0f  p90 %6.0f" % (nm, d[:, k].mean(), np.percentile(d[:, k], 10), np.percentile(d[:, k], 90)))
+start = np.sort(t[:, 0] - t0)
+print("CTA start times (us): first wave until %.1f, median %.1f, last %.1f" % (start[591] / 1e3, np.median(start) / 1e3, start[-1] / 1e3))
