@@ -4,9 +4,11 @@
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
                   [--workload ENC|DEC|CPU] [--dtype f32|bf16] [--dist model|uniform]
 
-A "step" is one pass of the hot path (msda_forward, then zero-fill + msda_backward)
-over one batch of synthetic input of the named workload (default ENC = BASELINE.json
-configs[1]: N=16, S=Lq=1500 tokens, M=8, D=64, L=4, P=4, fp32).
+A "step" is one pass of the hot path (msda_forward_ex, zero-fill of grad_value on a side stream
+under the forward, msda_backward_ex) over one batch of synthetic input of the named workload
+(default ENC = BASELINE.json configs[1]: N=16, S=Lq=1500 tokens, M=8, D=64, L=4, P=4, fp32).
+The timed region of `--steps` steps is repeated `--repeats` times; the line reports the median
+region (`value`, `ms_per_step`) with min / max beside it.
 
   value     queries/s (N*Lq per step, summed over ranks) with inputs resident in HBM,
             kernels launched through the C ABI; CUDA events, max over ranks.
@@ -17,6 +19,13 @@ configs[1]: N=16, S=Lq=1500 tokens, M=8, D=64, L=4, P=4, fp32).
              / its CUDA-event duration averaged over the timed steps.
   cpu_baseline  the oracle port of the reference's pure-PyTorch CPU path
             (oracle/core_pytorch.py, fwd + autograd bwd) on a bounded sample, rank 0, N=1 only.
+  secondary (N=1) the other lines of SURVEY.md 8(d), each with kernel times, roofline fractions and
+            the kernel family: DEC, bf16, uniform locations, a locality sweep (rows of noise on the
+            offsets), permuted query order (default vs row windows vs per-tap), L2-warm inputs, the
+            four calls of a multimodal encoder layer, and the kernel to beat (the reference's own
+            CUDA op from oracle/_ref, test infrastructure, timed after the headline region).
+  train_step  (--train-step, any N) BASELINE.json configs[4]: the 6+6-layer deformable transformer
+            step of tools/train_step.py with the NCCL gradient all-reduce, under this launch.
 
 Multi-GPU (torchrun): batch-sharded, weak scaling (per-GPU batch fixed), no data-path
 collective; barrier + synchronize around the timed region.
@@ -52,7 +61,10 @@ def parse():
     ap.add_argument("--qtile", type=int, default=0, help="tuning: queries-per-tile multiplier (0=auto)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--extra", action="store_true", help="also print per-phase and alt-distribution lines to stderr")
+    ap.add_argument("--repeats", type=int, default=7, help="timed regions of --steps steps; the median is reported")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the secondary records (N=1 only anyway)")
+    ap.add_argument("--train-step", action="store_true", help="add the configs[4] training-step record")
+    ap.add_argument("--flags", type=int, default=0, help="extra MSDA_FLAG_* bits for the GPU arm (A/B aid)")
     return ap.parse_args()
 
 
@@ -97,7 +109,12 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------- CPU legs (oracle port)
-def cpu_leg(workload, steps, warmup, dist):
+def workload_string(workload, N, Lq, S, T, M=8, D=64, L=4, P=4):
+    return "%s: MSDeformAttn fwd+bwd, per-GPU batch %d, Lq=%d, S=%d (T=%s), M=%d, D=%d, L=%d, P=%d" % (
+        workload, N, Lq, S, T, M, D, L, P)
+
+
+def cpu_leg(workload, steps, warmup, dist, padding="zeros"):
     """Times the oracle port of the reference's ms_deform_attn_core_pytorch (fwd + autograd
     bwd, fp32, all host threads) on a bounded sample: CPU_SAMPLE_BATCH batch items of the
     workload per step.  Returns (queries/s, ms_per_step, cores, sample description)."""
@@ -112,7 +129,7 @@ def cpu_leg(workload, steps, warmup, dist):
     Lq = inp["loc"].shape[1]
 
     def step():
-        out = ms_deform_attn_core_pytorch(v, inp["shapes"], loc, aw, "border")
+        out = ms_deform_attn_core_pytorch(v, inp["shapes"], loc, aw, padding)
         out.backward(inp["grad_out"])
         v.grad = loc.grad = aw.grad = None
 
@@ -122,8 +139,8 @@ def cpu_leg(workload, steps, warmup, dist):
     for _ in range(steps):
         step()
     dt = (time.perf_counter() - t0) / steps
-    sample = "%s workload cut to batch %d (Lq=%d), fwd+autograd bwd, fp32, %d threads, %d steps" % (
-        workload, nb, Lq, cores, steps)
+    sample = "%s workload cut to batch %d (Lq=%d), fwd+autograd bwd, fp32, grid_sample padding=%s, %d threads, %d steps" % (
+        workload, nb, Lq, padding, cores, steps)
     return nb * Lq / dt, dt * 1e3, cores, sample
 
 
@@ -131,18 +148,25 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    # at least one untimed step: the first one pays thread-pool start-up and first-touch of ~1 GB
-    steps, warmup = min(args.steps, 20), max(1, min(args.warmup, 3))
-    qps, ms, cores, sample = cpu_leg(args.workload, steps, warmup, args.dist)
+    # every step is a bounded sample (CPU_SAMPLE_BATCH batch items, ~0.4 s at ENC); --steps / --warmup are
+    # honoured up to a cap that keeps the run within minutes
+    steps, warmup = min(args.steps, 50), max(1, min(args.warmup, 10))
+    qps, ms, cores, sample = cpu_leg(args.workload, steps, warmup, args.dist, args.padding)
     from mfl_b200 import synthetic
     w = synthetic.WORKLOADS[args.workload]
+    S = sum(w["T"])
+    Lq = w["Lq"] if w["Lq"] is not None else sum(w.get("Tq", w["T"]))
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": qps, "unit": UNIT, "n_gpus": args.gpus,
         "steps": steps, "warmup": warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "%s: MSDeformAttn fwd+bwd, T=%s, M=8, D=64, L=4, P=4 (CPU sample: batch %d)" % (
-            args.workload, w["T"], min(CPU_SAMPLE_BATCH, w["N"])), "locations": args.dist,
-            "impl_detail": "oracle port of reference ms_deform_attn_core_pytorch (grid_sample border) on host cores"},
+        "config": {"workload": workload_string(args.workload, w["N"], Lq, S, w["T"]), "locations": args.dist,
+                   "padding": args.padding,
+                   "parallelism": "batch-sharded x%d, no data-path collective" % args.gpus,
+                   "l2": "n/a (host memory)",
+                   "impl_detail": "oracle port of the reference's ms_deform_attn_core_pytorch (grid_sample, padding=%s) "
+                                  "on the host cores; each step = a sample of %d batch items" % (
+                                      args.padding, min(CPU_SAMPLE_BATCH, w["N"]))},
         "cpu_baseline": {"value": qps, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": qps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -205,22 +229,48 @@ class OpBuffers:
             self.plan.data_ptr() if self.plan_bytes else None, stream))
 
 
-def time_device(bufs, steps, warmup, dist_sync):
-    """Timed region: `steps` x (fwd, zero-fill, bwd) rotating over the input ring.
-    Returns (total_ms, fwd_ms_avg, zero_ms_avg, bwd_ms_avg)."""
+def time_device(bufs, steps, warmup, dist_sync, overlap_zero=True):
+    """Timed region: `steps` x (fwd, zero-fill of the accumulation target, bwd) rotating over the
+    input ring.  overlap_zero: the zero-fill of step i is enqueued on a side stream when the step
+    starts and joined before the backward -- it runs under the forward kernels, inside the timed
+    step (what MSDeformAttnFunction does, functions/ms_deform_attn_func.py).
+    Returns (total_ms, fwd_ms_avg, zero_ms_avg (0 when overlapped), bwd_ms_avg)."""
     import torch
-    st = torch.cuda.current_stream().cuda_stream
-    for i in range(warmup):
+    main = torch.cuda.current_stream()
+    st = main.cuda_stream
+    side = torch.cuda.Stream()
+    ev_go = [torch.cuda.Event() for _ in range(steps + warmup)]
+    ev_z = [torch.cuda.Event() for _ in range(steps + warmup)]
+
+    def step(i, ev=None):
         b = bufs[i % len(bufs)]
-        b.fwd(st); b.zero(); b.bwd(st)
+        if ev:
+            ev[0].record()
+        if overlap_zero:
+            ev_go[i].record(main)
+            side.wait_event(ev_go[i])           # not before the step has started
+            with torch.cuda.stream(side):
+                b.zero()
+                ev_z[i].record(side)
+        b.fwd(st)
+        if ev:
+            ev[1].record()
+        if overlap_zero:
+            main.wait_event(ev_z[i])
+        else:
+            b.zero()
+        if ev:
+            ev[2].record()
+        b.bwd(st)
+        if ev:
+            ev[3].record()
+
+    for i in range(warmup):
+        step(i)
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(steps)]
     dist_sync()
     for i in range(steps):
-        b = bufs[i % len(bufs)]
-        ev[i][0].record(); b.fwd(st)
-        ev[i][1].record(); b.zero()
-        ev[i][2].record(); b.bwd(st)
-        ev[i][3].record()
+        step(warmup + i, ev[i])
     torch.cuda.synchronize()
     dist_sync()
     total = ev[0][0].elapsed_time(ev[-1][3])
@@ -304,6 +354,100 @@ def time_e2e(host, dev_meta, padding, steps, warmup, dist_sync):
     return e0.elapsed_time(e1), h2d_b, d2h_b
 
 
+def measure(ring, padding, flags, steps, warmup, repeats, dist_sync, hbm_peak, overlap_zero=True):
+    """Kernel times of one workload: `repeats` timed regions of `steps` steps -> medians."""
+    from mfl_b200 import synthetic
+    bufs = [OpBuffers(i, padding, 0) for i in ring]
+    for b in bufs:
+        b.set_flags(b.flags | flags)
+    b0 = bufs[0]
+    esz = ring[0]["value"].element_size()
+    bf, bb = synthetic.algorithmic_bytes(b0.N, b0.S, b0.Lq, b0.M, b0.D, b0.L, b0.P, esz)
+    regs = [time_device(bufs, steps, warmup if r == 0 else 1, dist_sync, overlap_zero) for r in range(repeats)]
+    med = lambda xs: sorted(xs)[len(xs) // 2]
+    step = [r[0] / steps for r in regs]
+    fwd, zero, bwd = (med([r[k] for r in regs]) for k in (1, 2, 3))
+    fam = b0.lib.msda_kernel_choice(b0.N, b0.S, b0.M, b0.D, b0.L, b0.Lq, b0.P, b0.dt, b0.flags).decode()
+    gb = lambda byts, ms: byts / (ms * 1e-3) / 1e9
+    return {"family": fam, "fwd_ms": fwd, "bwd_ms": bwd, "zero_fill_ms": zero, "step_ms": med(step),
+            "step_ms_min": min(step), "step_ms_max": max(step),
+            "fwd_frac": gb(bf, fwd) / hbm_peak, "bwd_frac": gb(bb, bwd) / hbm_peak,
+            "step_frac": gb(bf + bb, med(step)) / hbm_peak, "bytes_fwd": bf, "bytes_bwd": bb,
+            "queries": b0.N * b0.Lq}
+
+
+def time_kernel_to_beat(ring, steps, warmup):
+    """The reference's own CUDA op (oracle/_ref, built from /root/reference by oracle/build_ref.py:
+    test infrastructure) on the same ring of inputs: fwd / bwd ms through its pybind entry points
+    (allocation and zero-fill inside, as the reference does)."""
+    import torch
+    from oracle import ref_cuda
+    if not ref_cuda.available():
+        return None
+    ref = ref_cuda.load()
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(steps)]
+    for i in range(warmup + steps):
+        r = ring[i % len(ring)]
+        a = (r["value"], r["shapes"], r["lsi"], r["loc"], r["aw"])
+        k = i - warmup
+        if k >= 0:
+            ev[k][0].record()
+        ref.ms_deform_attn_forward(*a, 64)
+        if k >= 0:
+            ev[k][1].record()
+        ref.ms_deform_attn_backward(*a, r["grad_out"], 64)
+        if k >= 0:
+            ev[k][2].record()
+    torch.cuda.synchronize()
+    med = lambda xs: sorted(xs)[len(xs) // 2]
+    return {"impl": "reference CUDA op (models/ops/src/cuda) recompiled for sm_100a, oracle/_ref",
+            "fwd_ms": med([e[0].elapsed_time(e[1]) for e in ev]),
+            "bwd_ms": med([e[1].elapsed_time(e[2]) for e in ev])}
+
+
+def secondary_records(args, dev, hbm_peak, dist_sync, ring_enc):
+    """SURVEY.md 8(d) lines beside the headline; every entry is timed like the headline
+    (CUDA events, inputs rotated over distinct sets unless named l2warm)."""
+    import torch
+    from mfl_b200 import _lib, synthetic
+    out = {}
+    steps, warmup, reps = 10, 3, 3
+
+    def ring_of(wl, dtype=torch.float32, n=2, **kw):
+        return [synthetic.make_workload(wl, dtype, dev, seed=4321 + r, value="normal", **kw) for r in range(n)]
+
+    def rec(name, ring, flags=0, **kw):
+        m = measure(ring, args.padding, flags, steps, warmup, reps, dist_sync, hbm_peak, **kw)
+        out[name] = {k: (round(v, 5) if isinstance(v, float) else v) for k, v in m.items()
+                     if k not in ("bytes_fwd", "bytes_bwd", "queries")}
+
+    rec("ENC_f32_l2warm", ring_enc[:1])
+    rec("ENC_f32_no_tile(row windows, round 1 default)", ring_enc, _lib.MSDA_FLAG_NO_TILE)
+    rec("ENC_f32_per_tap", ring_enc, _lib.MSDA_FLAG_NO_WINDOW)
+    rec("ENC_f32_plan_apply_split", ring_enc, _lib.MSDA_FLAG_PLAN)
+    rec("ENC_f32_zero_fill_serial", ring_enc, 0, overlap_zero=False)
+    out["kernel_to_beat"] = time_kernel_to_beat(ring_enc, 5, 2)
+    del ring_enc
+    torch.cuda.empty_cache()
+    for nm, kw in (("ENC_f32_uniform", dict(dist="uniform")),
+                   ("ENC_f32_sigma2", dict(dist="model", sigma=2.0)),
+                   ("ENC_f32_sigma8", dict(dist="model", sigma=8.0)),
+                   ("ENC_f32_sigma32", dict(dist="model", sigma=32.0))):
+        rec(nm, ring_of("ENC", **kw))
+    rp = ring_of("ENC", dist="model", permute=True)
+    rec("ENC_f32_permuted", rp)
+    rec("ENC_f32_permuted_no_tile", rp, _lib.MSDA_FLAG_NO_TILE)
+    rec("ENC_f32_permuted_per_tap", rp, _lib.MSDA_FLAG_NO_WINDOW)
+    del rp
+    rec("ENC_bf16", ring_of("ENC", torch.bfloat16, dist="model"))
+    rec("DEC_f32", ring_of("DEC", dist="model"))
+    rec("DEC_bf16", ring_of("DEC", torch.bfloat16, dist="model"))
+    for wl in ("MM_VV", "MM_AA", "MM_AV", "MM_VA"):
+        rec(wl + "_f32", ring_of(wl, dist="model"))
+    rec("CPU_shape_f32(configs[0] on the GPU)", ring_of("CPU", dist="model"))
+    return out
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -329,30 +473,34 @@ def run_ours(args):
     w = synthetic.WORKLOADS[args.workload]
     ring = [synthetic.make_workload(args.workload, dtype, dev, seed=1234 + 17 * rank + r, dist=args.dist,
                                     value="normal") for r in range(RING)]
-    bufs = [OpBuffers(i, args.padding, args.qtile) for i in ring]
-    b0 = bufs[0]
-    N, S, Lq, M, D, L, P = b0.N, b0.S, b0.Lq, b0.M, b0.D, b0.L, b0.P
-    esz = ring[0]["value"].element_size()
-    bytes_fwd, bytes_bwd = synthetic.algorithmic_bytes(N, S, Lq, M, D, L, P, esz)
     ring_bytes = sum(sum(t.numel() * t.element_size() for t in (i["value"], i["loc"], i["aw"], i["grad_out"]))
                      for i in ring)
+    peaks, peak_src = None, "fallback"
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        peak_src = "measured"
+    except Exception:
+        pass
+    hbm_peak = float(peaks["hbm_gbs"]) if peaks else 6650.0
 
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
         time.sleep(0.3)
     t0 = time.time()
-    total_ms, fwd_ms, zero_ms, bwd_ms = time_device(bufs, args.steps, args.warmup, dist_sync)
+    m = measure(ring, args.padding, args.flags | _flag_qtile(args.qtile), args.steps, args.warmup,
+                max(1, args.repeats), dist_sync, hbm_peak)
     t1 = time.time()
-    clocks = sampler.stop(t0, t1) if rank == 0 else None
 
     from mfl_b200 import sharding
 
     def max_over_ranks(x):
         return sharding.max_over_ranks(x, dev)
 
-    total_ms = max_over_ranks(total_ms)
-    ms_per_step = total_ms / args.steps
+    N, Lq, S = ring[0]["value"].shape[0], ring[0]["loc"].shape[1], ring[0]["value"].shape[1]
+    M, D = ring[0]["value"].shape[2], ring[0]["value"].shape[3]
+    L, P = ring[0]["loc"].shape[3], ring[0]["loc"].shape[4]
+    ms_per_step = max_over_ranks(m["step_ms"])
     value = world * N * Lq / (ms_per_step * 1e-3)
 
     e2e = None
@@ -363,27 +511,24 @@ def run_ours(args):
         e_ms = max_over_ranks(e_ms) / e_steps
         e2e = {"value": world * N * Lq / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": d2h, "ms_per_step": e_ms, "steps": e_steps}
+    clocks = sampler.stop(t0, time.time()) if rank == 0 else None
 
-    peaks, peak_src = None, "fallback"
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        peak_src = "measured"
-    except Exception:
-        pass
-    hbm_peak = float(peaks["hbm_gbs"]) if peaks else 6650.0
-    achieved = bytes_bwd / (bwd_ms * 1e-3) / 1e9
-    fam = b0.lib.msda_kernel_choice(N, S, M, D, L, Lq, P, b0.dt, b0.flags).decode()
-    kname = {"window": "win", "fast": "fast", "generic": "generic"}.get(fam, fam)
-    roofline = {"bound": "hbm", "kernel": "msda_bwd_%s_kernel" % kname, "achieved": achieved, "peak": hbm_peak,
+    gb = lambda byts, ms: byts / (ms * 1e-3) / 1e9
+    kname = {"tile": "tile", "window": "win", "fast": "fast", "generic": "generic"}.get(m["family"], m["family"])
+    roofline = {"bound": "hbm", "kernel": "msda_bwd_%s_kernel" % kname, "achieved": gb(m["bytes_bwd"], m["bwd_ms"]),
+                "peak": hbm_peak,
                 "peak_source": peak_src + " (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s",
-                "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
-                "algorithmic_bytes_per_launch": bytes_bwd, "kernel_ms": bwd_ms,
-                "fwd_kernel": {"achieved": bytes_fwd / (fwd_ms * 1e-3) / 1e9,
-                               "frac": bytes_fwd / (fwd_ms * 1e-3) / 1e9 / hbm_peak, "kernel_ms": fwd_ms,
-                               "algorithmic_bytes_per_launch": bytes_fwd},
-                "zero_fill_ms": zero_ms,
-                "step": {"achieved": (bytes_fwd + bytes_bwd) / (ms_per_step * 1e-3) / 1e9,
-                         "frac": (bytes_fwd + bytes_bwd) / (ms_per_step * 1e-3) / 1e9 / hbm_peak}}
+                "unit": "GB/s", "frac": m["bwd_frac"], "traffic": None,
+                "algorithmic_bytes_per_launch": m["bytes_bwd"], "kernel_ms": m["bwd_ms"],
+                "fwd_kernel": {"name": "msda_sort_cluster_kernel + msda_fwd_%s_kernel" % kname if kname == "tile"
+                               else "msda_fwd_%s_kernel" % kname,
+                               "achieved": gb(m["bytes_fwd"], m["fwd_ms"]), "frac": m["fwd_frac"],
+                               "kernel_ms": m["fwd_ms"], "algorithmic_bytes_per_launch": m["bytes_fwd"]},
+                "zero_fill_ms": m["zero_fill_ms"],
+                "zero_fill": "cudaMemsetAsync of grad_value on a side stream, enqueued at step start, joined "
+                             "before the backward (inside the timed step)",
+                "step": {"achieved": gb(m["bytes_fwd"] + m["bytes_bwd"], ms_per_step),
+                         "frac": gb(m["bytes_fwd"] + m["bytes_bwd"], ms_per_step) / hbm_peak}}
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(traffic_file):
         try:
@@ -391,25 +536,47 @@ def run_ours(args):
         except Exception:
             pass
 
+    secondary = None
+    if rank == 0 and world == 1 and not args.no_secondary and args.workload == "ENC" and args.dtype == "f32":
+        secondary = secondary_records(args, dev, hbm_peak, dist_sync, ring)
+    del ring
+    torch.cuda.empty_cache()
+
+    train = None
+    if args.train_step:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import train_step
+        train = train_step.bench_record(dev, world, rank)
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        qps, ms, cores, sample = cpu_leg(args.workload, 3, 1, args.dist)
+        qps, ms, cores, sample = cpu_leg(args.workload, 3, 1, args.dist, args.padding)
         cpu = {"value": qps, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample, "ms_per_step": ms}
 
     if rank == 0:
+        launches_per_step = {"tile": 3, "window": 2, "fast": 2, "generic": 2}.get(m["family"], 2)
         print(json.dumps({
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
-            "config": {"workload": "%s: MSDeformAttn fwd+bwd, per-GPU batch %d, Lq=%d, S=%d (T=%s), M=%d, D=%d, L=%d, P=%d" % (
-                args.workload, N, Lq, S, w["T"], M, D, L, P),
-                "locations": args.dist, "padding": args.padding, "parallelism": "batch-sharded x%d, no data-path collective" % world,
-                "l2": "inputs rotate over %d distinct sets (%.0f MB) > 126 MB L2" % (RING, ring_bytes / 1e6)},
+            "config": {"workload": workload_string(args.workload, N, Lq, S, w["T"], M, D, L, P),
+                       "locations": args.dist, "padding": args.padding,
+                       "parallelism": "batch-sharded x%d, no data-path collective" % world,
+                       "l2": "inputs rotate over %d distinct sets (%.0f MB) > 126 MB L2" % (RING, ring_bytes / 1e6)},
+            "repeats": {"regions": max(1, args.repeats), "steps_per_region": args.steps,
+                        "ms_per_step_median": m["step_ms"], "ms_per_step_min": m["step_ms_min"],
+                        "ms_per_step_max": m["step_ms_max"]},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
-            "gpu_launches": 2 * args.steps, "clocks": clocks,
+            "gpu_launches": launches_per_step * args.steps * max(1, args.repeats), "clocks": clocks,
+            "secondary": secondary, "train_step": train,
         }))
     if world > 1:
         dist.destroy_process_group()
+
+
+def _flag_qtile(k):
+    from mfl_b200 import _lib
+    return _lib.flag_qtile(k)
 
 
 def main():

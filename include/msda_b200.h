@@ -99,10 +99,13 @@ typedef enum {
 #define MSDA_FLAG_NO_TILE 32u       /* never use the CTA-tile kernels (msda_tile.cuh:
                                       time-sorted query tiles, TMA-filled shared
                                       memory); the row-window kernels run instead */
-#define MSDA_FLAG_NO_PLAN 64u       /* CTA-tile path as ONE kernel per direction (msda_tile.cuh)
-                                      instead of the plan kernel + apply kernels of
-                                      msda_plan.cuh; the workspace then only holds the
-                                      query order */
+#define MSDA_FLAG_PLAN 64u          /* msda_forward_ex: run the CTA-tile path as a PLAN kernel
+                                      (geometry, windows and merged weights of every tile
+                                      -> 13 KB per tile in the workspace) and a persistent
+                                      APPLY kernel (TMA producer warp + consumer warps),
+                                      msda_plan.cuh.  Measured slower than the one-kernel
+                                      form on B200: kept as an
+                                      experiment, off by default */
 /* bits 8..19: queries-per-tile multiplier override for the vectorised kernels
  * (0 = heuristic); a tuning knob, results do not depend on it. */
 #define MSDA_FLAG_QTILE(k) (((unsigned)(k) & 0xfffu) << 8)

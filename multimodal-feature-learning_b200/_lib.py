@@ -21,7 +21,7 @@ MSDA_FLAG_NO_WINDOW = 4
 MSDA_FLAG_FORCE_WINDOW = 8
 MSDA_FLAG_DETERMINISTIC = 16
 MSDA_FLAG_NO_TILE = 32
-MSDA_FLAG_NO_PLAN = 64
+MSDA_FLAG_PLAN = 64
 ABI_VERSION = 2
 
 

@@ -262,6 +262,12 @@ int launch_sort(const void* loc, int* perm, const Dims& d, cudaStream_t st) {
   // heads averaged into the sort key: 2 (one CTA sorts a batch item, and one SM pulls ~50 GB/s:
   // 8 heads of 1500 queries are 30 us of sector fetches, 2 heads give the same order)
   while (hk_shift < 1 && (2 << hk_shift) <= d.M) ++hk_shift;
+  if (d.Lq <= kSortStash) {   // cluster sort: deterministic order, eight SMs per batch item on the keys
+    msda_sort_cluster_kernel<T><<<(unsigned)d.N * kSortCluster, kSortThreads, 0, st>>>((const T*)loc, perm, d,
+                                                                                      hk_shift);
+    const cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
+  }
   msda_sort_kernel<T><<<(unsigned)d.N, kSortThreads, 0, st>>>((const T*)loc, perm, d, hk_shift);
   const cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
@@ -347,6 +353,14 @@ int launch_plan(const int64_t* shapes, const int64_t* lsi, const void* loc, cons
                     (const T*)aw, perm, plan, d, nchunks);
 }
 
+// persistent apply kernels: two CTAs per SM
+inline int apply_grid(long long tiles) {
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const long long g = 2ll * sms;
+  return (int)(tiles < g ? tiles : g);
+}
+
 template <typename T, int NU>
 int launch_fwd_apply(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
                      const void* aw, const char* plan, void* out, const Dims& d, int dtype,
@@ -355,13 +369,14 @@ int launch_fwd_apply(const void* value, const int64_t* shapes, const int64_t* ls
   CUtensorMap map;
   if (!tile_value_map(&map, value, dtype, d)) return MSDA_ERR_NO_TMA;
   auto kern = msda_fwd_apply_kernel<T, NU>;
-  constexpr size_t smem = ApplySmem<T, NU>::kBytes;
+  constexpr size_t smem = ApplySmem<NU * 8 * 16>::kBytes;
   const int rc = tile_smem_attr(kern, smem, attr_done);
   if (rc != MSDA_OK) return rc;
   const int nchunks = (d.Lq + kTileQ - 1) / kTileQ;
-  const unsigned grid = (unsigned)((int64_t)d.N * d.M * nchunks);
-  return launch_pdl(kern, grid, kTileThreads, smem, st, after_plan, map, (const T*)value, shapes, lsi,
-                    (const T*)loc, (const T*)aw, plan, (T*)out, d, nchunks);
+  const long long tiles = (long long)d.N * d.M * nchunks;
+  return launch_pdl(kern, (unsigned)apply_grid(tiles), kApplyThreads, smem, st, after_plan, map,
+                    (const T*)value, shapes, lsi, (const T*)loc, (const T*)aw, plan, (T*)out, d, nchunks,
+                    (int)tiles);
 }
 
 // (dtype, NU, G) -> instantiation.  FN is launch_fwd_fast / launch_bwd_fast.
@@ -565,6 +580,9 @@ const char* msda_kernel_choice(int64_t N, int64_t S, int64_t M, int64_t D, int64
 int msda_debug_tile_times(unsigned long long* host, int n) {
   return (int)cudaMemcpyFromSymbol(host, g_tile_times, (size_t)n * sizeof(unsigned long long));
 }
+int msda_debug_sort_times(unsigned long long* host, int n) {
+  return (int)cudaMemcpyFromSymbol(host, g_sort_times, (size_t)n * sizeof(unsigned long long));
+}
 #endif
 
 int msda_last_cuda_error(void) { return t_last_cuda_error; }
@@ -577,7 +595,7 @@ size_t msda_forward_workspace_bytes(int64_t N, int64_t S, int64_t M, int64_t D, 
   if (check_common(N, S, M, D, L, Lq, P, dtype, MSDA_PAD_ZEROS) != MSDA_OK || N == 0 || Lq == 0) return 0;
   const bool fast = S * M * D < (int64_t(1) << 31) && fast_applies(D, L, dtype, flags);
   if (!fast || !tile_applies(make_dims(N, S, M, D, L, Lq, P, MSDA_PAD_ZEROS), dtype, flags)) return 0;
-  return (flags & MSDA_FLAG_NO_PLAN) ? tile_plan_bytes(N, Lq) : plan_ws_bytes(N, M, Lq);
+  return (flags & MSDA_FLAG_PLAN) ? plan_ws_bytes(N, M, Lq) : tile_plan_bytes(N, Lq);
 }
 
 int msda_forward_ex(const void* value, const int64_t* spatial_shapes, const int64_t* level_start_index,
@@ -602,7 +620,7 @@ int msda_forward_ex(const void* value, const int64_t* spatial_shapes, const int6
     int* perm = (int*)workspace;
     int r = launch_sort_dtype(dtype, sampling_loc, perm, d, st);
     if (r != MSDA_OK) return r;
-    if (!(flags & MSDA_FLAG_NO_PLAN) && workspace_bytes >= plan_ws_bytes(N, M, Lq) &&
+    if ((flags & MSDA_FLAG_PLAN) && workspace_bytes >= plan_ws_bytes(N, M, Lq) &&
         (tile_plan_bytes(N, Lq) % 128) == 0 && (reinterpret_cast<uintptr_t>(workspace) & 127u) == 0) {
       // plan kernel + apply kernel
       char* plan = plan_of(workspace, N, Lq);
@@ -689,7 +707,7 @@ size_t msda_backward_workspace_bytes_flags(int64_t N, int64_t S, int64_t M, int6
                                            int64_t Lq, int64_t P, int dtype, unsigned flags) {
   const size_t main_bytes = ws_main_bytes(N, S, M, D, dtype, flags);
   // + the plan of the CTA-tile kernels (optional: without it the row-window kernels run)
-  const size_t plan = msda_forward_workspace_bytes(N, S, M, D, L, Lq, P, dtype, flags | MSDA_FLAG_NO_PLAN);
+  const size_t plan = msda_forward_workspace_bytes(N, S, M, D, L, Lq, P, dtype, flags & ~MSDA_FLAG_PLAN);
   return plan ? round256(main_bytes) + plan : main_bytes;
 }
 
@@ -750,7 +768,7 @@ int msda_backward_ex(const void* value, const int64_t* spatial_shapes, const int
     // doubles the byte offsets the window kernels keep in 32 bits
     const bool vec8 = fast && ((dtype == MSDA_F32 && (D == 64 || D == 32)) || (dtype == MSDA_BF16 && D == 64));
     const int family = !vec8 ? 0
-                       : perm ? 3
+                       : (perm && Lq <= kSortStash) ? 3   // the order of a longer list is not reproducible
                        : (win_applies(d, dtype, flags) && S * M * D * 8 < (int64_t(1) << 32)) ? 2 : 1;
     if (family == 3 && need_sort) {
       const int r = launch_sort_dtype(dtype, sampling_loc, const_cast<int*>(perm), d, st);

@@ -203,14 +203,25 @@ msda_plan_kernel(const int64_t* __restrict__ shapes, const int64_t* __restrict__
   }
 }
 
-// ------------------------------- forward apply ---------------------------------
-template <typename T, int NU>
+// ------------------------------- apply: common ---------------------------------
+// Persistent CTAs (two per SM), each a pipeline of kApplyStages shared-memory stages:
+//   producer warp (one thread): tile header from the plan -> one mbarrier transaction per stage:
+//       bulk copy of the tile's meta block (header, query list, block descriptors), TMA boxes of
+//       the value rows, bulk copies of the warps' weights;
+//   kTileWarps consumer warps: wait for the stage, run their blocks' row loops out of shared
+//       memory, write their results, release the stage.
+// No CTA barrier in the loop; the value rows of tile i+1 fly in while tile i is computed.
+constexpr int kApplyStages = 2;
+constexpr int kApplyThreads = kTileThreads + 32;
+
+template <int ROW_BYTES>
 struct ApplySmem {
-  static constexpr int kRowBytes = NU * 8 * 16;
-  static constexpr int kValueBytes = kTileCapRows * kRowBytes;
-  static constexpr int kBytes = kValueBytes + kPlanWtBytes;
+  static constexpr int kValueBytes = kTileCapRows * ROW_BYTES;
+  static constexpr int kStageBytes = kValueBytes + kPlanWtBytes + kPlanMetaBytes;
+  static constexpr int kBytes = kApplyStages * kStageBytes;
 };
 static_assert(kTileCapRows <= 255, "tile rows are stored in a byte");
+static_assert(kPlanMetaBytes % 128 == 0 && kPlanWtBytes % 128 == 0, "stage sections stay 128-byte aligned");
 
 // bulk copy global -> shared (1-D), completion on an mbarrier
 __device__ __forceinline__ void tile_bulk_load(void* smem_dst, const void* gsrc, unsigned bytes,
@@ -221,148 +232,220 @@ __device__ __forceinline__ void tile_bulk_load(void* smem_dst, const void* gsrc,
       "l"(gsrc), "r"(bytes), "r"(tile_smem_u32(mbar))
       : "memory");
 }
+__device__ __forceinline__ void tile_mbar_arrive(unsigned long long* mbar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tile_smem_u32(mbar)) : "memory");
+}
 
-// What every apply kernel does first: header -> TMA boxes of the value rows + the warps' weights,
-// all on one mbarrier; per-thread block description.  Returns the tile's mode.
+// L2 prefetch of one value box (no shared memory involved)
+__device__ __forceinline__ void tile_tma_prefetch(const CUtensorMap* map, int col, int row) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(
+                   reinterpret_cast<unsigned long long>(map)),
+               "r"(col), "r"(row)
+               : "memory");
+}
+
+struct ApplyHdr {
+  int4 h0, h1, h2, h3;   // tlo | tbase | total, mode, rtw[0], rtw[1] | rtw[2..]
+};
+__device__ __forceinline__ void apply_load_hdr(const char* plan, int tile, int ntiles, ApplyHdr& h) {
+  if (tile < ntiles) {
+    const char* tp = plan + (size_t)tile * kPlanStride;
+    h.h0 = tile_ld_dep4(tp);
+    h.h1 = tile_ld_dep4(tp + 16);
+    h.h2 = tile_ld_dep4(tp + 32);
+    h.h3 = tile_ld_dep4(tp + 48);
+  }
+}
+// the value boxes of a tile: into the stage (PREFETCH = false) or into L2 only
+template <bool PREFETCH>
+__device__ __forceinline__ void apply_value_boxes(const CUtensorMap* vmap, const ApplyHdr& h, const Dims& d,
+                                                  int nchunks, int tile, char* st, unsigned row_bytes,
+                                                  unsigned long long* mbar) {
+  const int total = h.h2.x;
+  const int m = tile % d.M, b = tile / d.M / nchunks;
+  const int tlo[4] = {h.h0.x, h.h0.y, h.h0.z, h.h0.w}, tbase[4] = {h.h1.x, h.h1.y, h.h1.z, h.h1.w};
+#pragma unroll
+  for (int l = 0; l < kWinMaxL; ++l) {
+    const int nb = ((l + 1 < kWinMaxL ? tbase[l + 1] : total) - tbase[l]) / kTileBoxRows;
+    for (int k = 0; k < nb; ++k) {
+      if (PREFETCH)
+        tile_tma_prefetch(vmap, m * d.D, b * d.S + tlo[l] + k * kTileBoxRows);
+      else
+        tile_tma_load(st + (size_t)(tbase[l] + k * kTileBoxRows) * row_bytes, vmap, m * d.D,
+                      b * d.S + tlo[l] + k * kTileBoxRows, mbar);
+    }
+  }
+}
+
+// The producer: fills stage after stage.  Called by ONE thread.  Headers are read two tiles
+// ahead and the value rows of the next tile are pulled into L2 while the current one is loaded,
+// so that the load into a stage that has just been released is an L2 hit.
+__device__ __forceinline__ void apply_producer(const CUtensorMap* vmap, const char* plan, const Dims& d,
+                                               int nchunks, int ntiles, char* stages, int stage_bytes,
+                                               int value_bytes, unsigned row_bytes,
+                                               unsigned long long* full, unsigned long long* empty) {
+  ApplyHdr cur, nxt;
+  apply_load_hdr(plan, blockIdx.x, ntiles, cur);
+  apply_load_hdr(plan, blockIdx.x + gridDim.x, ntiles, nxt);
+  int it = 0;
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+    const int s = it % kApplyStages, use = it / kApplyStages;
+    const int tile_n = tile + gridDim.x;
+    if (tile_n < ntiles && nxt.h2.y == kPlanModeTile && nxt.h2.x > 0)
+      apply_value_boxes<true>(vmap, nxt, d, nchunks, tile_n, nullptr, row_bytes, nullptr);
+    if (use > 0) tile_mbar_wait(&empty[s], (use - 1) & 1);
+    const char* tp = plan + (size_t)tile * kPlanStride;
+    char* st = stages + s * stage_bytes;
+    const int total = cur.h2.x, mode = cur.h2.y;
+    const int rtw[6] = {cur.h2.z, cur.h2.w, cur.h3.x, cur.h3.y, cur.h3.z, cur.h3.w};
+    unsigned bytes = kPlanMetaBytes;
+    const bool rows = mode == kPlanModeTile && total > 0;
+    if (rows) {
+      bytes += (unsigned)total * row_bytes;
+#pragma unroll
+      for (int w = 0; w < kTileWarps; ++w) bytes += (unsigned)rtw[w] * 64u;
+    }
+    tile_mbar_expect_tx(&full[s], bytes);
+    tile_bulk_load(st + value_bytes + kPlanWtBytes, tp, kPlanMetaBytes, &full[s]);
+    if (rows) {
+      apply_value_boxes<false>(vmap, cur, d, nchunks, tile, st, row_bytes, &full[s]);
+#pragma unroll
+      for (int w = 0; w < kTileWarps; ++w)
+        if (rtw[w] > 0)
+          tile_bulk_load(st + value_bytes + w * kPlanWarpWtBytes, tp + kPlanMetaBytes + w * kPlanWarpWtBytes,
+                         (unsigned)rtw[w] * 64u, &full[s]);
+    }
+    cur = nxt;
+    apply_load_hdr(plan, tile_n + gridDim.x, ntiles, nxt);
+  }
+}
+
+// per-thread block description, read from the stage's meta block
 struct ApplyBlk {
   int blo[kWinMaxL], brows[kWinMaxL], wmax[kWinMaxL], wrows[kWinMaxL], trow[kWinMaxL], bpoff[kWinMaxL];
   int rt;
 };
-__device__ __forceinline__ int apply_setup(const CUtensorMap* vmap, const char* tp, const Dims& d, int b,
-                                           int m, char* vtile, char* s_wt, unsigned row_bytes,
-                                           unsigned long long* mbar, int* s_q, ApplyBlk& ab,
-                                           bool& have_rows) {
-  const int tid = threadIdx.x, g = tid >> 3, warp = tid >> 5;
-  if (tid == 0) tile_mbar_init(mbar, 1);
-  tile_grid_wait();
-  const int4 h0 = tile_ld_dep4(tp);          // tlo
-  const int4 h1 = tile_ld_dep4(tp + 16);     // tbase
-  const int4 h2 = tile_ld_dep4(tp + 32);     // total, mode, rtw[0], rtw[1]
-  const int4 h3 = tile_ld_dep4(tp + 48);     // rtw[2..]
-  const int total = h2.x, mode = h2.y;
-  if (tid < kTileQ) s_q[tid] = tile_ld_dep(reinterpret_cast<const int*>(tp + kPlanQOff) + tid);
-  have_rows = total > 0;
-  if (mode == kPlanModeTile) {
-    const int rtw[6] = {h2.z, h2.w, h3.x, h3.y, h3.z, h3.w};
-    if (tid == 0 && total > 0) {
-      unsigned bytes = (unsigned)total * row_bytes;
+__device__ __forceinline__ void apply_block(const char* meta, int g, int warp, ApplyBlk& ab) {
+  const int4 b0 = *reinterpret_cast<const int4*>(meta + kPlanBlkOff + g * kPlanBlkBytes);
+  const uint4 b1 = *reinterpret_cast<const uint4*>(meta + kPlanBlkOff + g * kPlanBlkBytes + 16);
+  const int blo[4] = {b0.x, b0.y, b0.z, b0.w};
+  int off = 0;
 #pragma unroll
-      for (int w = 0; w < kTileWarps; ++w) bytes += (unsigned)rtw[w] * 64u;
-      tile_mbar_expect_tx(mbar, bytes);
-      const int tlo[4] = {h0.x, h0.y, h0.z, h0.w}, tbase[4] = {h1.x, h1.y, h1.z, h1.w};
-#pragma unroll
-      for (int l = 0; l < kWinMaxL; ++l) {
-        const int nb = ((l + 1 < kWinMaxL ? tbase[l + 1] : total) - tbase[l]) / kTileBoxRows;
-        for (int k = 0; k < nb; ++k)
-          tile_tma_load(vtile + (size_t)(tbase[l] + k * kTileBoxRows) * row_bytes, vmap, m * d.D,
-                        b * d.S + tlo[l] + k * kTileBoxRows, mbar);
-      }
-#pragma unroll
-      for (int w = 0; w < kTileWarps; ++w)
-        if (rtw[w] > 0)
-          tile_bulk_load(s_wt + w * kPlanWarpWtBytes, tp + kPlanMetaBytes + w * kPlanWarpWtBytes,
-                         (unsigned)rtw[w] * 64u, mbar);
-    }
-    const int4 b0 = tile_ld_dep4(tp + kPlanBlkOff + g * kPlanBlkBytes);
-    const int4 b1s = tile_ld_dep4(tp + kPlanBlkOff + g * kPlanBlkBytes + 16);
-    const uint4 b1 = make_uint4((unsigned)b1s.x, (unsigned)b1s.y, (unsigned)b1s.z, (unsigned)b1s.w);
-    const int blo[4] = {b0.x, b0.y, b0.z, b0.w};
-    int off = 0;
-#pragma unroll
-    for (int l = 0; l < kWinMaxL; ++l) {
-      ab.blo[l] = blo[l];
-      ab.brows[l] = (b1.x >> (8 * l)) & 255;
-      ab.wmax[l] = (b1.y >> (8 * l)) & 255;
-      ab.wrows[l] = (b1.z >> (8 * l)) & 255;
-      ab.trow[l] = (b1.w >> (8 * l)) & 255;
-      ab.bpoff[l] = off;
-      off += ab.wrows[l];
-    }
-    ab.rt = rtw[warp];
+  for (int l = 0; l < kWinMaxL; ++l) {
+    ab.blo[l] = blo[l];
+    ab.brows[l] = (b1.x >> (8 * l)) & 255;
+    ab.wmax[l] = (b1.y >> (8 * l)) & 255;
+    ab.wrows[l] = (b1.z >> (8 * l)) & 255;
+    ab.trow[l] = (b1.w >> (8 * l)) & 255;
+    ab.bpoff[l] = off;
+    off += ab.wrows[l];
   }
-  __syncthreads();   // mbarrier initialised, s_q in place
-  return mode;
+  ab.rt = reinterpret_cast<const int*>(meta)[10 + warp];
 }
 
+// ------------------------------- forward apply ---------------------------------
 template <typename T, int NU>
-__global__ void __launch_bounds__(kTileThreads, 4)
+__global__ void __launch_bounds__(kApplyThreads, 2)
 msda_fwd_apply_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restrict__ value,
                       const int64_t* __restrict__ shapes, const int64_t* __restrict__ lsi,
                       const T* __restrict__ loc, const T* __restrict__ aw,
-                      const char* __restrict__ plan, T* __restrict__ out, Dims d, int nchunks) {
+                      const char* __restrict__ plan, T* __restrict__ out, Dims d, int nchunks,
+                      int ntiles) {
   using U = Unit<T>;
   using Raw = typename U::Raw;
-  using SM = ApplySmem<T, NU>;
   constexpr int G = 8;
   constexpr int E = U::E;
-  constexpr int RB = SM::kRowBytes;
+  constexpr int RB = NU * G * 16;
+  using SM = ApplySmem<RB>;
   __shared__ int s_lvl[3 * kWinMaxL];
-  __shared__ int s_q[kTileQ];
-  __shared__ __align__(8) unsigned long long s_mbar;
+  __shared__ __align__(8) unsigned long long s_full[kApplyStages], s_empty[kApplyStages];
   extern __shared__ __align__(128) char s_raw[];
-  char* vtile = s_raw;
-  char* s_wt = s_raw + SM::kValueBytes;
   const int tid = threadIdx.x, g = tid >> 3, j = tid & 7, warp = tid >> 5;
-  const int m = blockIdx.x % d.M;
-  const int b = blockIdx.x / d.M / nchunks;
-  const char* tp = plan + (size_t)blockIdx.x * kPlanStride;
-  ApplyBlk ab;
-  bool have_rows;
-  const int mode = apply_setup(&vmap, tp, d, b, m, vtile, s_wt, RB, &s_mbar, s_q, ab, have_rows);
-  if (mode != kPlanModeTile) {
-    win_stage_levels(shapes, lsi, d.L, s_lvl);
-    if (mode == kPlanModeTap4) tile_fallback_fwd<T, NU, 4>(value, loc, aw, out, d, b, m, s_lvl, s_raw, s_q);
-    else tile_fallback_fwd<T, NU, 2>(value, loc, aw, out, d, b, m, s_lvl, s_raw, s_q);
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < kApplyStages; ++s) {
+      tile_mbar_init(&s_full[s], 1);
+      tile_mbar_init(&s_empty[s], kTileWarps);
+    }
+  }
+  win_stage_levels(shapes, lsi, d.L, s_lvl);   // also the barrier behind the mbarrier inits
+  tile_grid_wait();
+  if (warp == kTileWarps) {
+    if ((tid & 31) == 0)
+      apply_producer(&vmap, plan, d, nchunks, ntiles, s_raw, SM::kStageBytes, SM::kValueBytes, RB, s_full,
+                     s_empty);
     return;
   }
-  float2 acc[kWinQ][NU][E / 2];
+  int it = 0;
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+    const int s = it % kApplyStages, use = it / kApplyStages;
+    char* vtile = s_raw + s * SM::kStageBytes;
+    char* s_wt = vtile + SM::kValueBytes;
+    const char* meta = s_wt + kPlanWtBytes;
+    const int* s_q = reinterpret_cast<const int*>(meta + kPlanQOff);
+    const int m = tile % d.M, b = tile / d.M / nchunks;
+    tile_mbar_wait(&s_full[s], use & 1);
+    const int mode = reinterpret_cast<const int*>(meta)[9];
+    if (mode != kPlanModeTile) {
+      if (mode == kPlanModeTap4) tile_fallback_fwd<T, NU, 4>(value, loc, aw, out, d, b, m, s_lvl, s_wt, s_q);
+      else tile_fallback_fwd<T, NU, 2>(value, loc, aw, out, d, b, m, s_lvl, s_wt, s_q);
+    } else {
+      ApplyBlk ab;
+      apply_block(meta, g, warp, ab);
+      float2 acc[kWinQ][NU][E / 2];
 #pragma unroll
-  for (int q = 0; q < kWinQ; ++q)
+      for (int q = 0; q < kWinQ; ++q)
 #pragma unroll
-    for (int uu = 0; uu < NU; ++uu)
+        for (int uu = 0; uu < NU; ++uu)
 #pragma unroll
-      for (int c = 0; c < E / 2; ++c) acc[q][uu][c] = make_float2(0.f, 0.f);
-  if (have_rows) tile_mbar_wait(&s_mbar, 0);
-  const float4* Wt = reinterpret_cast<const float4*>(s_wt + warp * kPlanWarpWtBytes) + (g & 3) * ab.rt;
+          for (int c = 0; c < E / 2; ++c) acc[q][uu][c] = make_float2(0.f, 0.f);
+      const float4* Wt = reinterpret_cast<const float4*>(s_wt + warp * kPlanWarpWtBytes) + (g & 3) * ab.rt;
 #pragma unroll
-  for (int l = 0; l < kWinMaxL; ++l) {
-    const char* vr = vtile + ab.trow[l] * RB + j * 16;
-    const float4* wl = Wt + ab.bpoff[l];
-    const int n = ab.wmax[l], nb = ab.brows[l];
+      for (int l = 0; l < kWinMaxL; ++l) {
+        const char* vr = vtile + ab.trow[l] * RB + j * 16;
+        const float4* wl = Wt + ab.bpoff[l];
+        const int n = ab.wmax[l], nb = ab.brows[l];
 #pragma unroll 2
-    for (int i = 0; i < n; ++i) {
-      const float4 wv = wl[i];
-      const float wq[kWinQ] = {wv.x, wv.y, wv.z, wv.w};
+        for (int i = 0; i < n; ++i) {
+          const float4 wv = wl[i];
+          const float wq[kWinQ] = {wv.x, wv.y, wv.z, wv.w};
 #pragma unroll
-      for (int uu = 0; uu < NU; ++uu) {
-        Raw raw[U::RW];
-        tile_lds<U>(vr + uu * (G * 16), raw);
-        float v[E];
-        U::unpack_raw(raw, v);
+          for (int uu = 0; uu < NU; ++uu) {
+            Raw raw[U::RW];
+            tile_lds<U>(vr + uu * (G * 16), raw);
+            float v[E];
+            U::unpack_raw(raw, v);
 #pragma unroll
-        for (int q = 0; q < kWinQ; ++q) {
-          const float2 w2 = make_float2(wq[q], wq[q]);
+            for (int q = 0; q < kWinQ; ++q) {
+              const float2 w2 = make_float2(wq[q], wq[q]);
 #pragma unroll
-          for (int c = 0; c < E / 2; ++c)
-            acc[q][uu][c] = __ffma2_rn(w2, make_float2(v[2 * c], v[2 * c + 1]), acc[q][uu][c]);
+              for (int c = 0; c < E / 2; ++c)
+                acc[q][uu][c] = __ffma2_rn(w2, make_float2(v[2 * c], v[2 * c + 1]), acc[q][uu][c]);
+            }
+          }
+          if (i + 1 < nb) vr += RB;
         }
       }
-      if (i + 1 < nb) vr += RB;
-    }
-  }
 #pragma unroll
-  for (int q = 0; q < kWinQ; ++q) {
-    const int qq = s_q[g * kWinQ + q];
-    if (qq >= 0) {
-      T* og = out + (((size_t)b * d.Lq + qq) * d.M + m) * d.D + j * E;
+      for (int q = 0; q < kWinQ; ++q) {
+        const int qq = s_q[g * kWinQ + q];
+        if (qq >= 0) {
+          T* og = out + (((size_t)b * d.Lq + qq) * d.M + m) * d.D + j * E;
 #pragma unroll
-      for (int uu = 0; uu < NU; ++uu) {
-        float o[E];
+          for (int uu = 0; uu < NU; ++uu) {
+            float o[E];
 #pragma unroll
-        for (int c = 0; c < E / 2; ++c) { o[2 * c] = acc[q][uu][c].x; o[2 * c + 1] = acc[q][uu][c].y; }
-        U::st_stream(og + uu * (G * E), o);
+            for (int c = 0; c < E / 2; ++c) { o[2 * c] = acc[q][uu][c].x; o[2 * c + 1] = acc[q][uu][c].y; }
+            U::st_stream(og + uu * (G * E), o);
+          }
+        }
       }
     }
+    // this warp is done with the stage (the per-tap body used it as scratch through the generic
+    // proxy: order that before the producer's next asynchronous copies)
+    if (mode != kPlanModeTile) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncwarp();
+    if ((tid & 31) == 0) tile_mbar_arrive(&s_empty[s]);
   }
 }
 

@@ -28,6 +28,7 @@
 // through 0 * inf; MSDA_FLAG_NO_WINDOW selects the per-tap kernels, which never read a row
 // they do not tap.
 #pragma once
+#include <cooperative_groups.h>
 #include <cuda.h>   // CUtensorMap (the type only; the encoder is resolved at run time)
 #include <type_traits>
 
@@ -40,10 +41,10 @@ namespace msda {
 #define MSDA_TILE_WARPS 4
 #endif
 #ifndef MSDA_TILE_CAP
-#define MSDA_TILE_CAP 160
+#define MSDA_TILE_CAP 152
 #endif
 #ifndef MSDA_TILE_BLK
-#define MSDA_TILE_BLK 48
+#define MSDA_TILE_BLK 56
 #endif
 #ifndef MSDA_TILE_FWD_CTAS
 #define MSDA_TILE_FWD_CTAS 4
@@ -72,8 +73,17 @@ __device__ __forceinline__ void tile_stamp(int k) {
     g_tile_times[blockIdx.x * 8 + k] = t;
   }
 }
+__device__ unsigned long long g_sort_times[8 * 64];
+__device__ __forceinline__ void sort_stamp(int k) {
+  if (threadIdx.x == 0 && blockIdx.x < 64) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    g_sort_times[blockIdx.x * 8 + k] = t;
+  }
+}
 #else
 __device__ __forceinline__ void tile_stamp(int) {}
+__device__ __forceinline__ void sort_stamp(int) {}
 #endif
 
 // ---- query order ---------------------------------------------------------------
@@ -99,20 +109,22 @@ template <> struct SortKey<__nv_bfloat16> {
 // a bin, the forward is bitwise independent of the permutation).  P == 4.
 // HK lanes share a query (one head each, the first HK = min(M, 2) heads), so all loads of a pass are in flight together; the bin of a query is kept in shared
 // memory between the two passes when Lq allows it.
-constexpr int kSortStash = 8192;
+constexpr int kSortStash = 4096;   // static shared memory stays below 48 KB
 
 template <typename T>
 __global__ void __launch_bounds__(kSortThreads)
 msda_sort_kernel(const T* __restrict__ loc, int* __restrict__ perm, Dims d, int hk_shift) {
   __shared__ int s_hist[kSortBins];
   __shared__ int s_warp[32];
-  __shared__ unsigned short s_bin[kSortStash];
+  __shared__ unsigned s_bin[kSortStash];   // (bin << 16) | rank inside the bin
   // let the dependent (tile) kernel's CTAs be scheduled right away: they wait for this grid's
   // completion (griddepcontrol.wait) before they read the permutation
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int b = blockIdx.x, tid = threadIdx.x;
+  sort_stamp(0);
   for (int i = tid; i < kSortBins; i += kSortThreads) s_hist[i] = 0;
   __syncthreads();
+  sort_stamp(1);
   const int HK = 1 << hk_shift;
   const size_t hstride = (size_t)d.L * d.P * 2;
   const T* lb = loc + (size_t)b * d.Lq * d.M * hstride;
@@ -127,15 +139,30 @@ msda_sort_kernel(const T* __restrict__ loc, int* __restrict__ perm, Dims d, int 
     // NaN -> bin 0 (fmaxf drops it), +-inf clamp
     return __float2int_rd(fminf(fmaxf(s * scale, 0.f), (float)(kSortBins - 1)));
   };
-#pragma unroll 4
-  for (int item = tid; item < items_up; item += kSortThreads) {
-    const int bin = bin_of(item);
-    if (item < items && (item & (HK - 1)) == 0) {
-      atomicAdd(&s_hist[bin], 1);
-      if (stash) s_bin[item >> hk_shift] = (unsigned short)bin;
+  // 4 items per thread and round: all loads of a round are issued before the first is used
+  for (int base = tid; base < items_up; base += 4 * kSortThreads) {
+    float ks[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int item = base + u * kSortThreads;
+      ks[u] = item < items ? SortKey<T>::sum4(lb + ((size_t)(item >> hk_shift) * d.M + (item & (HK - 1))) * hstride)
+                           : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int item = base + u * kSortThreads;
+      if (item - tid >= items_up) break;               // warp-uniform: the shuffles stay converged
+      float sk = ks[u];
+      for (int o = 1; o < HK; o <<= 1) sk += __shfl_xor_sync(0xffffffffu, sk, o);
+      const int bin = __float2int_rd(fminf(fmaxf(sk * scale, 0.f), (float)(kSortBins - 1)));
+      if (item < items && (item & (HK - 1)) == 0) {
+        const int slot = atomicAdd(&s_hist[bin], 1);
+        if (stash) s_bin[item >> hk_shift] = ((unsigned)bin << 16) | (unsigned)slot;
+      }
     }
   }
   __syncthreads();
+  sort_stamp(2);
   // exclusive scan of the histogram: 4 bins per thread, shuffle scan per warp, then over warps
   constexpr int PER = kSortBins / kSortThreads;
   int v[PER], sum = 0;
@@ -163,9 +190,10 @@ msda_sort_kernel(const T* __restrict__ loc, int* __restrict__ perm, Dims d, int 
 #pragma unroll
   for (int k = 0; k < PER; ++k) { s_hist[tid * PER + k] = run; run += v[k]; }
   __syncthreads();
+  sort_stamp(3);
   int* pb = perm + (size_t)b * d.Lq;
-  if (stash) {
-    for (int q = tid; q < d.Lq; q += kSortThreads) pb[atomicAdd(&s_hist[s_bin[q]], 1)] = q;
+  if (stash) {   // position = start of the bin + the rank the first pass drew: no second atomic pass
+    for (int q = tid; q < d.Lq; q += kSortThreads) pb[s_hist[s_bin[q] >> 16] + (int)(s_bin[q] & 0xffffu)] = q;
   } else {
 #pragma unroll 4
     for (int item = tid; item < items_up; item += kSortThreads) {
@@ -173,6 +201,117 @@ msda_sort_kernel(const T* __restrict__ loc, int* __restrict__ perm, Dims d, int 
       if (item < items && (item & (HK - 1)) == 0) pb[atomicAdd(&s_hist[bin], 1)] = item >> hk_shift;
     }
   }
+  __syncthreads();
+  sort_stamp(4);
+}
+
+// The same for Lq <= kSortStash, faster and DETERMINISTIC (ties in index order): a cluster of
+// kSortCluster CTAs per batch item.  All of them read keys (the loads are one 32-byte sector per
+// (query, head), fully divergent: one SM's L1 serves ~1 sector per clock, eight SMs eight), and
+// drop w = (key16 << 16 | query) into the shared memory of the cluster's first CTA through DSMEM.
+// That CTA counting-sorts the words on their top kSortBits bits and then ranks every word inside
+// its bin (the words are unique), so the result does not depend on the order the atomics ran in.
+constexpr int kSortCluster = 8;
+constexpr int kSortBits = 11;
+constexpr int kSortBins2 = 1 << kSortBits;
+
+template <typename T>
+__global__ void __cluster_dims__(kSortCluster, 1, 1) __launch_bounds__(kSortThreads)
+msda_sort_cluster_kernel(const T* __restrict__ loc, int* __restrict__ perm, Dims d, int hk_shift) {
+  namespace cg = cooperative_groups;
+  __shared__ unsigned s_key[kSortStash];     // w per query, later the sorted words
+  __shared__ unsigned s_tmp[kSortStash];     // (slot << 16 | bin) per query, later bin-ordered words
+  __shared__ int s_hist[kSortBins2 + 1];
+  __shared__ int s_warp[32];
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  cg::cluster_group cluster = cg::this_cluster();
+  const int rank = (int)cluster.block_rank();
+  const int b = blockIdx.x / kSortCluster, tid = threadIdx.x;
+  sort_stamp(0);
+  const int HK = 1 << hk_shift;
+  const size_t hstride = (size_t)d.L * d.P * 2;
+  const T* lb = loc + (size_t)b * d.Lq * d.M * hstride;
+  const float scale = 65536.f / (float)(4 * HK);
+  unsigned* key0 = cluster.map_shared_rank(s_key, 0);
+  const int per = (d.Lq + kSortCluster - 1) / kSortCluster;
+  const int q0 = rank * per, nq = max(min(d.Lq - q0, per), 0);
+  const int items = nq << hk_shift;
+  const int items_up = (items + 31) & ~31;
+  for (int item = tid; item < items_up; item += kSortThreads) {
+    const int q = q0 + (item >> hk_shift), hd = item & (HK - 1);
+    float sk = item < items ? SortKey<T>::sum4(lb + ((size_t)q * d.M + hd) * hstride) : 0.f;
+    for (int o = 1; o < HK; o <<= 1) sk += __shfl_xor_sync(0xffffffffu, sk, o);
+    // NaN -> 0 (fmaxf drops it), +-inf clamp
+    const unsigned kb = (unsigned)__float2int_rd(fminf(fmaxf(sk * scale, 0.f), 65535.f));
+    if (item < items && hd == 0) key0[q] = (kb << 16) | (unsigned)q;
+  }
+  if (rank == 0)
+    for (int i = tid; i <= kSortBins2; i += kSortThreads) s_hist[i] = 0;
+  cluster.sync();
+  sort_stamp(1);
+  if (rank != 0) return;
+  // counts (order-independent) and a provisional slot per query
+  for (int q = tid; q < d.Lq; q += kSortThreads) {
+    const int bin = (int)(s_key[q] >> (32 - kSortBits));
+    s_tmp[q] = ((unsigned)atomicAdd(&s_hist[bin], 1) << 16) | (unsigned)bin;
+  }
+  __syncthreads();
+  // exclusive scan of the counts: kSortBins2 / kSortThreads bins per thread
+  constexpr int PER = kSortBins2 / kSortThreads;
+  int v[PER], sum = 0;
+#pragma unroll
+  for (int k = 0; k < PER; ++k) { v[k] = s_hist[tid * PER + k]; sum += v[k]; }
+  int inc = sum;
+#pragma unroll
+  for (int s = 1; s < 32; s <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, inc, s);
+    if ((tid & 31) >= s) inc += t;
+  }
+  if ((tid & 31) == 31) s_warp[tid >> 5] = inc;
+  __syncthreads();
+  if (tid < 32) {
+    int w = s_warp[tid], wi = w;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, wi, s);
+      if (tid >= s) wi += t;
+    }
+    s_warp[tid] = wi - w;
+  }
+  __syncthreads();
+  int run = s_warp[tid >> 5] + inc - sum;
+#pragma unroll
+  for (int k = 0; k < PER; ++k) { s_hist[tid * PER + k] = run; run += v[k]; }
+  if (tid == kSortThreads - 1) s_hist[kSortBins2] = run;
+  sort_stamp(2);
+  // words into bin order (any order inside a bin), registers in between: s_tmp changes meaning
+  unsigned wq[kSortStash / kSortThreads], pq[kSortStash / kSortThreads];
+#pragma unroll
+  for (int u = 0; u < kSortStash / kSortThreads; ++u) {
+    const int q = tid + u * kSortThreads;
+    if (q < d.Lq) { wq[u] = s_key[q]; pq[u] = s_tmp[q]; }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int u = 0; u < kSortStash / kSortThreads; ++u) {
+    const int q = tid + u * kSortThreads;
+    if (q < d.Lq) s_tmp[s_hist[pq[u] & 0xffffu] + (int)(pq[u] >> 16)] = wq[u];
+  }
+  __syncthreads();
+  // rank inside the bin: the words are unique, so this fixes the order
+  for (int p = tid; p < d.Lq; p += kSortThreads) {
+    const unsigned w = s_tmp[p];
+    const int bin = (int)(w >> (32 - kSortBits));
+    const int lo = s_hist[bin], hi = s_hist[bin + 1];
+    int r = 0;
+    for (int x = lo; x < hi; ++x) r += s_tmp[x] < w;
+    s_key[lo + r] = w;
+  }
+  __syncthreads();
+  sort_stamp(3);
+  int* pb = perm + (size_t)b * d.Lq;
+  for (int i = tid; i < d.Lq; i += kSortThreads) pb[i] = (int)(s_key[i] & 0xffffu);
+  sort_stamp(4);
 }
 
 // Loads of data the PRECEDING kernel of a programmatic dependent launch produced (the query order,

@@ -47,7 +47,8 @@ def encoder_reference_points(T, device):
 
 
 def make_inputs(N, Lq, M, D, P, shapes_hw, dtype=torch.float32, device="cuda", seed=1234,
-                dist="uniform", value="small", enc_ref=False, requires_grad=False, query_T=None):
+                dist="uniform", value="small", enc_ref=False, requires_grad=False, query_T=None,
+                sigma=0.5, permute=False):
     """dist: 'uniform'  loc ~ U[0,1)^2 (models/ops/test.py:34)
              'model'    loc_x = ref + (bias[m,p] + 0.5*N(0,1)) / W_l   (a freshly initialised module)
              'interior' every tap inside the map (zeros == border)
@@ -56,6 +57,10 @@ def make_inputs(N, Lq, M, D, P, shapes_hw, dtype=torch.float32, device="cuda", s
        enc_ref: the queries are the tokens of a multi-level sequence (of the value's own
        levels, or of `query_T` when the queries come from the other modality) and carry the
        encoder's reference points.
+       sigma: rows of Gaussian noise on the 'model' offsets (0.5 = a freshly initialised module;
+       larger values probe how much learned offset spread the windowed kernels take).
+       permute: shuffle the query list per batch item (the sparse encoders hand the op
+       score-ordered top-k tokens: models/sparse/unimodal_sparse_deformable_transformer.py:218).
        For maps with H == 1 the y coordinate is the constant 0.5 the module stacks on."""
     gen = torch.Generator(device=device).manual_seed(seed)
     shapes, lsi, S = level_tensors(shapes_hw, device)
@@ -73,7 +78,7 @@ def make_inputs(N, Lq, M, D, P, shapes_hw, dtype=torch.float32, device="cuda", s
     Wl = shapes[:, 1].float()[None, None, None, :, None]
     Hl = shapes[:, 0].float()[None, None, None, :, None]
     if dist == "model":
-        off = head_bias(M, P, device)[None, None, :, None, :] + 0.5 * torch.randn(N, Lq, M, L, P, **f32)
+        off = head_bias(M, P, device)[None, None, :, None, :] + sigma * torch.randn(N, Lq, M, L, P, **f32)
         x = ref[:, :, None, None, None] + off / Wl
         y = torch.rand(N, Lq, M, L, P, **f32)
     else:
@@ -91,6 +96,10 @@ def make_inputs(N, Lq, M, D, P, shapes_hw, dtype=torch.float32, device="cuda", s
     loc = torch.stack((x, y), -1)
     aw = torch.softmax(torch.randn(N, Lq, M, L * P, **f32), -1).view(N, Lq, M, L, P)
     gout = torch.randn(N, Lq, M * D, **f32)
+    if permute:
+        idx = torch.stack([torch.randperm(Lq, device=device, generator=gen) for _ in range(N)])
+        loc = torch.gather(loc, 1, idx[:, :, None, None, None, None].expand_as(loc))
+        aw = torch.gather(aw, 1, idx[:, :, None, None, None].expand_as(aw))
     out = dict(value=val.to(dtype), shapes=shapes, lsi=lsi, loc=loc.to(dtype).contiguous(),
                aw=aw.to(dtype).contiguous(), grad_out=gout.to(dtype))
     if requires_grad:
@@ -100,12 +109,12 @@ def make_inputs(N, Lq, M, D, P, shapes_hw, dtype=torch.float32, device="cuda", s
 
 
 def make_workload(name, dtype=torch.float32, device="cuda", seed=1234, dist="model", value="normal",
-                  N=None):
+                  N=None, sigma=0.5, permute=False):
     w = WORKLOADS[name]
     T = w["T"]
     Lq = w["Lq"] if w["Lq"] is not None else sum(w.get("Tq", T))
     return make_inputs(N or w["N"], Lq, w["M"], w["D"], w["P"], [(1, t) for t in T], dtype, device,
-                       seed, dist, value, enc_ref=w["enc"], query_T=w.get("Tq"))
+                       seed, dist, value, enc_ref=w["enc"], query_T=w.get("Tq"), sigma=sigma, permute=permute)
 
 
 def algorithmic_bytes(N, S, Lq, M, D, L, P, elem_bytes):

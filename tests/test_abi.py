@@ -42,9 +42,9 @@ def test_abi_version_and_strings(lib):
     assert lib.msda_kernel_choice(*enc, _lib.MSDA_F32, 0) == b"tile"
     assert lib.msda_kernel_choice(*enc, _lib.MSDA_BF16, 0) == b"tile"
     assert lib.msda_kernel_choice(*enc, _lib.MSDA_F32, _lib.MSDA_FLAG_NO_TILE) == b"window"
-    assert lib.msda_forward_workspace_bytes(*enc, _lib.MSDA_F32, _lib.MSDA_FLAG_NO_PLAN) == 16 * 1500 * 4
+    assert lib.msda_forward_workspace_bytes(*enc, _lib.MSDA_F32, 0) == 16 * 1500 * 4
     tiles = 16 * 8 * ((1500 + 63) // 64)     # the plan of the split path: 13 KB per tile of 64 queries
-    assert lib.msda_forward_workspace_bytes(*enc, _lib.MSDA_F32, 0) >= 16 * 1500 * 4 + tiles * 12288
+    assert lib.msda_forward_workspace_bytes(*enc, _lib.MSDA_F32, _lib.MSDA_FLAG_PLAN) >= 16 * 1500 * 4 + tiles * 12288
     assert lib.msda_forward_workspace_bytes(*enc, _lib.MSDA_F32, _lib.MSDA_FLAG_NO_TILE) == 0
     assert lib.msda_backward_workspace_bytes_flags(*enc, _lib.MSDA_F32, 0) == 16 * 1500 * 4
     assert lib.msda_kernel_choice(*enc, _lib.MSDA_F32, _lib.MSDA_FLAG_NO_WINDOW) == b"fast"

@@ -1,7 +1,8 @@
 """GPU suite for the row-window kernels (csrc/msda_win.cuh) and the CTA-tile kernels
 (csrc/msda_tile.cuh: time-sorted query tiles, TMA-filled shared memory) against the C oracle.
-Every case runs through both families (`fam`): "tile" is what the shape class gets by default,
-"window" is the same call with MSDA_FLAG_NO_TILE.
+Every case runs through the families (`fam`): "tile" is what the shape class gets by default,
+"window" is the same call with MSDA_FLAG_NO_TILE, "plan" the forward as plan kernel + persistent
+apply kernel (MSDA_FLAG_PLAN, csrc/msda_plan.cuh; the backward of that family is the tile kernel).
 
 The window path is taken per block of 4 consecutive queries whose packed per-level
 windows fit kWinCap rows; everything else in the same launch runs the per-tap body.
@@ -29,10 +30,10 @@ GRAD_REL_F32 = 1e-4
 BF16_FWD_REL = 2.0 ** -7
 BF16_GRAD_REL = 2e-2
 WIN = _lib.MSDA_FLAG_FORCE_WINDOW
-FAMILY_FLAGS = {"tile": WIN, "window": WIN | _lib.MSDA_FLAG_NO_TILE}
+FAMILY_FLAGS = {"tile": WIN, "window": WIN | _lib.MSDA_FLAG_NO_TILE, "plan": WIN | _lib.MSDA_FLAG_PLAN}
 
 
-@pytest.fixture(params=["tile", "window"])
+@pytest.fixture(params=["tile", "window", "plan"])
 def fam(request):
     return FAMILY_FLAGS[request.param]
 

@@ -38,3 +38,10 @@ for k, nm in enumerate(names):
     print("  %-34s mean %6.0f ns  p10 %6.0f  p90 %6.0f" % (nm, d[:, k].mean(), np.percentile(d[:, k], 10), np.percentile(d[:, k], 90)))
 start = np.sort(t[:, 0] - t0)
 print("CTA start times (us): first wave until %.1f, median %.1f, last %.1f" % (start[591] / 1e3, np.median(start) / 1e3, start[-1] / 1e3))
+
+hs = (ctypes.c_ulonglong * (8 * 16))()
+lib.msda_debug_sort_times.argtypes = [ctypes.c_void_p, ctypes.c_int]
+assert lib.msda_debug_sort_times(hs, 8 * 16) == 0
+ts = np.array(hs, dtype=np.float64).reshape(16, 8)[:, :5]
+print("sort kernel phases (ns), mean over 16 CTAs: zero %s | keys+hist %s | scan %s | scatter %s ; first start -> last end %.1f us; sort end -> first tile CTA start %.1f us" % (
+    *[("%.0f" % x) for x in np.diff(ts, axis=1).mean(0)], (ts[:, 4].max() - ts[:, 0].min()) / 1e3, (t[:, 0].min() - ts[:, 4].max()) / 1e3))
