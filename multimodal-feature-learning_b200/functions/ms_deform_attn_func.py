@@ -70,6 +70,8 @@ class _MSDeformAttnBase(Function):
         gv = None
         if getattr(ctx, "msda_gv", None) is not None:
             gv, ev = ctx.msda_gv
+            ctx.msda_gv = None          # single use: a second backward over the same graph (gradcheck,
+                                        # retain_graph) allocates and clears its own buffer
             torch.cuda.current_stream(value.device).wait_event(ev)
             flags |= _lib.MSDA_FLAG_SKIP_ZERO_FILL      # (ignored by the deterministic variant)
         grad_value, grad_loc, grad_aw = MSDA.ms_deform_attn_backward(

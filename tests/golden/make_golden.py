@@ -199,3 +199,25 @@ if __name__ == "__main__":
     if not os.path.isdir(REF):
         sys.exit("needs %s (build container only)" % REF)
     main()
+
+
+def make_transformer_keys():
+    """State-dict keys and shapes of the reference's DeformableTransformer at the configs[4] size
+    (models/deformable/unimodal_deformable_transformer.py:13-60) -> ref_transformer_keys.json;
+    tools/train_step.py's model must accept them key for key."""
+    import importlib
+    import json
+    import types
+    stub = types.ModuleType("models")
+    stub.__path__ = [os.path.join(REF, "models")]
+    sys.modules["models"] = stub
+    udt = importlib.import_module("models.deformable.unimodal_deformable_transformer")
+    m = udt.DeformableTransformer(d_model=512, num_head=8, num_encoder_layers=6, num_decoder_layers=6,
+                                  dim_feedforward=2048, dropout=0.1, activation="relu", return_intermediate_dec=True,
+                                  num_feature_levels=4, dec_n_points=4, enc_n_points=4)
+    with open(os.path.join(HERE, "ref_transformer_keys.json"), "w") as f:
+        json.dump({k: list(v.shape) for k, v in m.state_dict().items()}, f, indent=0)
+
+
+if os.environ.get("MSDA_GOLDEN_TRANSFORMER_KEYS"):
+    make_transformer_keys()

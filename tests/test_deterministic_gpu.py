@@ -117,3 +117,18 @@ def test_scale_follows_the_gradient_magnitude(oracle_c, scale):
     zero = dict(inp)
     zero["grad_out"] = torch.zeros_like(inp["grad_out"])
     assert float(bwd(zero, "zeros", DET)[0].abs().max()) == 0.0
+
+
+def test_deterministic_edge_cases():
+    """(a) a non-finite grad_output under the deterministic flag surfaces as NaN in grad_value
+    instead of finite garbage; (b) no value rows at all (S == 0) with the flag set does not touch
+    the (absent) workspace."""
+    inp = synthetic.make_inputs(2, 37, 4, 64, 4, [(1, 20), (1, 10)], torch.float32, DEV, seed=11, dist="uniform",
+                                value="normal")
+    inp["grad_out"][1, 3, 5] = float("inf")
+    gv, gl, ga = bwd(inp, "zeros", DET)
+    assert torch.isnan(gv).all()
+    inp0 = synthetic.make_inputs(2, 5, 2, 64, 4, [(1, 0), (1, 0)], torch.float32, DEV, seed=12, dist="uniform")
+    assert inp0["value"].shape[1] == 0
+    gv, gl, ga = bwd(inp0, "zeros", DET)
+    assert gv.numel() == 0 and float(gl.abs().max()) == 0.0 and float(ga.abs().max()) == 0.0

@@ -220,3 +220,59 @@ def test_faster_than_reference_cuda_op(workload):
         with open(os.path.join(out_dir, "ref_cuda_timing_%s.json" % workload), "w") as f:
             json.dump(t, f)
     assert t["ours_fwd_us"] < t["ref_fwd_us"] and t["ours_bwd_us"] < t["ref_bwd_us"], t
+
+
+@pytest.mark.skipif(not ref_cuda.available(), reason="oracle/_ref (reference CUDA op) not built")
+@pytest.mark.parametrize("case", ["permuted", "top30_by_score", "sigma2", "sigma8"])
+def test_fullsize_query_orders_vs_reference_cuda_op(case):
+    """Non-monotone long query lists, the sparse encoders' input
+    (models/sparse/unimodal_sparse_deformable_transformer.py:218, 425-431: torch.topk indices are in
+    score order), and offsets with more spread than a fresh module: same results as the reference's
+    op, whichever kernel family the tiles end up in; and the three families agree."""
+    from mfl_b200 import _lib
+    ref = ref_cuda.load()
+    kw = dict(permute=True) if case in ("permuted", "top30_by_score") else dict(sigma=float(case[5:]))
+    inp = synthetic.make_workload("ENC", torch.float32, DEV, seed=61, dist="model", value="small", **kw)
+    if case == "top30_by_score":      # a score-ordered 30 % subset of the (shuffled) tokens
+        k = int(0.3 * inp["loc"].shape[1])
+        inp["loc"], inp["aw"] = inp["loc"][:, :k].contiguous(), inp["aw"][:, :k].contiguous()
+        inp["grad_out"] = inp["grad_out"][:, :k].contiguous()
+    a = [inp[k] for k in ("value", "shapes", "lsi", "loc", "aw")]
+    want_out = ref.ms_deform_attn_forward(*a, 64)
+    want_g = ref.ms_deform_attn_backward(*a, inp["grad_out"], 64)
+    ok = _smooth_points(inp)
+    for flags in (0, _lib.MSDA_FLAG_NO_TILE, _lib.MSDA_FLAG_NO_WINDOW):
+        got_out = MSDA.ms_deform_attn_forward(*a, 64, flags=flags)
+        got_g = MSDA.ms_deform_attn_backward(*a, inp["grad_out"], 64, flags=flags)
+        assert float((got_out - want_out).abs().max()) <= 1e-5, flags
+        assert rel(got_g[0], want_g[0]) <= 1e-4 and rel(got_g[2], want_g[2]) <= 1e-4, flags
+        assert rel(got_g[1] * ok, want_g[1] * ok) <= 1e-4, flags
+
+
+def test_non_finite_value_rows():
+    """A non-finite value row: the reference (and the per-tap kernels, MSDA_FLAG_NO_WINDOW) only
+    poison the queries that tap it.  The windowed kernels (tile / row window) multiply every row of
+    a 4-query block's window by all four queries' weights, so up to three time-neighbours of a
+    tapping query see 0 * inf = NaN as well -- the documented deviation:
+    never FEWER NaN outputs than the reference, and none outside blocks that tap the row."""
+    from mfl_b200 import _lib
+    from oracle.core_pytorch import ms_deform_attn_core_pytorch as ref_fn
+    T = [128, 64, 32, 16]
+    inp = synthetic.make_inputs(1, sum(T), 2, 64, 4, [(1, t) for t in T], torch.float32, DEV, seed=71,
+                                dist="model", value="small", enc_ref=True)
+    inp["value"][0, 40, 1, :] = float("inf")
+    a = [inp[k] for k in ("value", "shapes", "lsi", "loc", "aw")]
+    want = ref_fn(inp["value"], inp["shapes"], inp["loc"], inp["aw"], "zeros")
+    bad_ref = ~torch.isfinite(want).view(1, -1, 2, 64).all(-1)            # [1, Lq, M]
+    assert bad_ref.any() and not bad_ref[..., 0].any()
+    out_tap = MSDA.ms_deform_attn_forward(*a, 64, flags=_lib.MSDA_FLAG_NO_WINDOW | _lib.MSDA_FLAG_FORCE_WINDOW)
+    bad_tap = ~torch.isfinite(out_tap).view(1, -1, 2, 64).all(-1)
+    assert torch.equal(bad_tap, bad_ref)                                   # per-tap kernels == reference
+    for flags in (_lib.MSDA_FLAG_FORCE_WINDOW, _lib.MSDA_FLAG_FORCE_WINDOW | _lib.MSDA_FLAG_NO_TILE):
+        out = MSDA.ms_deform_attn_forward(*a, 64, flags=flags)
+        bad = ~torch.isfinite(out).view(1, -1, 2, 64).all(-1)
+        assert (bad | ~bad_ref).all()                                      # a superset of the reference's
+        assert not bad[..., 0].any()                                       # other heads untouched
+        assert int(bad.sum()) <= 4 * int(bad_ref.sum())                    # at most the 4-query blocks
+        fin = ~bad
+        assert float((out.view(1, -1, 2, 64)[fin] - want.view(1, -1, 2, 64)[fin]).abs().max()) <= 1e-5

@@ -80,3 +80,17 @@ def test_outputs_stay_inside_their_buffers(case, dtype):
             for name, g in (("out", out), ("grad_value", gv), ("grad_loc", gl), ("grad_aw", ga)):
                 assert g.fully_written(), (name, padding, fl)
                 assert bool(torch.isfinite(g.t.float()).all()), (name, padding, fl)
+
+
+def test_bf16_backward_without_queries_zeroes_grad_value():
+    """Lq == 0 with bf16: grad_value is not the accumulation image, it must still come back as zeros
+    (ADVICE round 1)."""
+    import torch
+    from mfl_b200 import MultiScaleDeformableAttention as MSDA
+    from mfl_b200 import synthetic
+    inp = synthetic.make_inputs(2, 0, 2, 64, 4, [(1, 20), (1, 10)], torch.bfloat16, "cuda", seed=3)
+    gv = torch.full_like(inp["value"], 7.0)
+    out = MSDA.ms_deform_attn_backward(inp["value"], inp["shapes"], inp["lsi"], inp["loc"], inp["aw"],
+                                       inp["grad_out"], 64, grad_value=gv)
+    torch.cuda.synchronize()
+    assert float(out[0].abs().max()) == 0.0 and out[1].numel() == 0 and out[2].numel() == 0

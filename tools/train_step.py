@@ -80,15 +80,54 @@ class DecoderLayer(nn.Module):
         return self.norm3(tgt + self.linear2(F.relu(self.linear1(tgt))))
 
 
+class _Stack(nn.Module):
+    """`encoder.layers.N...` / `decoder.layers.N...`: the reference's state-dict paths."""
+
+    def __init__(self, layers):
+        super().__init__()
+        self.layers = nn.ModuleList(layers)
+
+    def __iter__(self):
+        return iter(self.layers)
+
+
+class DeformableTransformer(nn.Module):
+    """Same parameters, names and shapes as the reference's DeformableTransformer
+    (models/deformable/unimodal_deformable_transformer.py:13-60): its state dict loads into this
+    one key for key (tests/test_train_step_keys.py, fixture tests/golden/ref_transformer_keys.json)."""
+
+    def __init__(self, C=512, ffn=2048, M=8, L=4, P=4, layers=6):
+        super().__init__()
+        self.encoder = _Stack(EncoderLayer(C, ffn, M, L, P) for _ in range(layers))
+        self.decoder = _Stack(DecoderLayer(C, ffn, M, L, P) for _ in range(layers))
+        self.level_embed = nn.Parameter(torch.randn(L, C))
+        self.reference_points = nn.Linear(C, 1)
+
+
 class DeformableEncoderDecoder(nn.Module):
+    """The transformer plus the event-query embedding the DVC model owns in the reference."""
+
     def __init__(self, C=512, ffn=2048, M=8, L=4, P=4, layers=6, queries=100):
         super().__init__()
-        self.encoder = nn.ModuleList(EncoderLayer(C, ffn, M, L, P) for _ in range(layers))
-        self.decoder = nn.ModuleList(DecoderLayer(C, ffn, M, L, P) for _ in range(layers))
-        self.level_embed = nn.Parameter(torch.randn(L, C))
+        self.transformer = DeformableTransformer(C, ffn, M, L, P, layers)
         self.query_embed = nn.Embedding(queries, 2 * C)
-        self.reference_points = nn.Linear(C, 1)
         self.L = L
+
+    @property
+    def encoder(self):
+        return self.transformer.encoder
+
+    @property
+    def decoder(self):
+        return self.transformer.decoder
+
+    @property
+    def level_embed(self):
+        return self.transformer.level_embed
+
+    @property
+    def reference_points(self):
+        return self.transformer.reference_points
 
     def forward(self, src, pos, enc_ref, T, lsi):
         N = src.shape[0]
@@ -129,6 +168,87 @@ def op_share(step_fn):
     except Exception as exc:  # noqa: BLE001
         print("profiler unavailable: %r" % (exc,), file=sys.stderr)
         return None, None, None, None
+
+
+def bench_record(dev, world, rank, steps=10, warmup=3, batch=16, layers=6):
+    """The step under bench.py's launch (python bench.py --train-step, any N; the process group is
+    bench.py's): eager, one flat NCCL all-reduce (avg) of all gradients per step.  Returns the
+    sub-record of the bench line: samples/s over all ranks (device-timed, max over ranks), the
+    all-reduce alone (ms and bus bandwidth 2(N-1)/N * bytes / time) and the op's share."""
+    torch.backends.cuda.matmul.allow_tf32 = True
+    torch.backends.cudnn.allow_tf32 = True
+    w = synthetic.WORKLOADS["ENC"]
+    T_list, C = w["T"], w["M"] * w["D"]
+    torch.manual_seed(1234)
+    model = DeformableEncoderDecoder(C, 2048, w["M"], len(T_list), w["P"], layers, 100).to(dev)
+    n_params = sum(p.numel() for p in model.parameters())
+    flat = torch.zeros(n_params, device=dev)
+    o = 0
+    for p_ in model.parameters():
+        p_.grad = flat[o:o + p_.numel()].view_as(p_)
+        o += p_.numel()
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-4, weight_decay=1e-4, fused=True)
+    gen = torch.Generator(device=dev).manual_seed(99 + rank)
+    S = sum(T_list)
+    src = torch.randn(batch, S, C, device=dev, generator=gen)
+    pos = torch.randn(batch, S, C, device=dev, generator=gen) * 0.1
+    T = torch.tensor(T_list, dtype=torch.long, device=dev)
+    lsi = torch.cat((T.new_zeros(1), T.cumsum(0)[:-1]))
+    enc_ref = synthetic.encoder_reference_points(T_list, dev)[None, :, None, None].expand(
+        batch, -1, len(T_list), 1).contiguous()
+
+    def step():
+        flat.zero_()
+        loss = model(src, pos, enc_ref, T, lsi).float().pow(2).mean()
+        loss.backward()
+        if world > 1:
+            dist.all_reduce(flat, op=dist.ReduceOp.AVG)
+        torch.nn.utils.clip_grad_norm_(model.parameters(), 0.1, foreach=True)
+        opt.step()
+        return loss
+
+    step()
+    for mod in model.modules():
+        if isinstance(mod, MSDeformAttn):
+            mod.check_input_lengths = False
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        loss = step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    ar_ms = None
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        dist.barrier()
+        a0.record()
+        for _ in range(10):
+            dist.all_reduce(flat, op=dist.ReduceOp.AVG)
+        a1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([a0.elapsed_time(a1) / 10], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ar_ms = float(t)
+    ms_step = float(ms) / steps
+    share = op_share(step) if rank == 0 else (step(), None, None, None)[1:]
+    rec = {"metric": "configs[4] training step (6+6-layer deformable transformer, 39.4 M parameters + query "
+                     "embedding), eager, flat NCCL gradient all-reduce", "samples_per_s": batch * world / ms_step * 1e3,
+           "ms_per_step": ms_step, "per_gpu_batch": batch, "n_gpus": world, "steps": steps, "params": n_params,
+           "allreduce_bytes": n_params * 4, "allreduce_ms": ar_ms,
+           "allreduce_busbw_GBps": (2.0 * (world - 1) / world * n_params * 4 / (ar_ms * 1e-3) / 1e9) if ar_ms else None,
+           "collective": "ncclAllReduce (avg) of one flat fp32 buffer over NVLink 5 / NVSwitch" if world > 1 else None,
+           "loss": float(loss.detach())}
+    if rank == 0 and share and share[0] is not None:
+        rec.update(op_share_of_gpu_time=share[0], op_us_per_step=share[1], gpu_us_per_step=share[2],
+                   op_launches_per_step=share[3])
+    return rec
 
 
 def main():
@@ -290,15 +410,16 @@ def main():
             "op_share_of_gpu_time": share[0], "op_us_per_step": share[1], "gpu_us_per_step": share[2],
             "op_launches_per_step": share[3],
         }), flush=True)
-    if world > 1 and args.cuda_graph:
-        # tearing down a communicator whose collectives live in a captured graph can block:
-        # everything is measured and printed, leave without the teardown
-        torch.cuda.synchronize()
-        sys.stdout.flush()
-        sys.stderr.flush()
-        os._exit(0)
     if world > 1:
+        # a captured graph holds references into the communicator: drop the graph (and everything
+        # captured with it) before the process group goes away, then tear down in order
+        torch.cuda.synchronize()
+        if args.cuda_graph:
+            del step
+            graph.reset()
+            del graph
         dist.barrier()
+        torch.cuda.synchronize()
         dist.destroy_process_group()
 
 
