@@ -265,6 +265,25 @@ int msda_dam_scatter(const void* loc, const void* aw, const int64_t* level_sizes
 int msda_encoder_reference_points(const int64_t* level_sizes, const float* valid_ratios,
                                   float* out, int64_t N, int64_t S, int64_t L, void* stream);
 
+/*
+ * Token gather / scatter of the sparse encoders (SURVEY.md section 8(f) row 3;
+ * models/sparse/unimodal_sparse_deformable_transformer.py:425-431 torch.gather over an index
+ * repeated along the channels, :443-448 one `output[i].scatter(...)` per batch item in a Python
+ * loop).  Rows of `row_bytes` bytes (C * element size), any element type.
+ *   x, base, out_scatter [B, S, row]   idx [B, K] int64 (device)   src, out_gather [B, K, row]
+ *   nums [B] int64 (device) or NULL: only the first nums[b] indices of item b count
+ *   msda_token_gather : out[b,k] = x[b, idx[b,k]]   (k >= nums[b] or an index outside [0,S): zeros)
+ *   msda_token_scatter: out[b,s] = src[b,k] where idx[b,k] == s for a counted k (indices of one item
+ *                       are distinct, as torch.topk's are), else base[b,s]; zero_hit_rows != 0 writes
+ *                       zeros instead of src rows (the gradient w.r.t. base; src may be NULL).
+ *                       `inverse`: caller's scratch of B*S int32 (filled here).  out may not alias base.
+ */
+int msda_token_gather(const void* x, const int64_t* idx, const int64_t* nums, void* out,
+                      int64_t B, int64_t S, int64_t K, int64_t row_bytes, void* stream);
+int msda_token_scatter(const void* base, const int64_t* idx, const int64_t* nums, const void* src,
+                       void* out, int* inverse, int64_t B, int64_t S, int64_t K, int64_t row_bytes,
+                       int zero_hit_rows, void* stream);
+
 /* Last CUDA runtime error code seen by the calling thread inside this library
  * (cudaError_t as int) and its string. */
 int msda_last_cuda_error(void);

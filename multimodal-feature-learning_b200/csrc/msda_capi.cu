@@ -13,6 +13,7 @@
 #include "msda_frontend.cuh"
 #include "msda_generic.cuh"
 #include "msda_plan.cuh"
+#include "msda_sparse.cuh"
 #include "msda_tile.cuh"
 #include "msda_win.cuh"
 
@@ -971,6 +972,54 @@ int msda_dam_scatter(const void* loc, const void* aw, const int64_t* level_sizes
   else
     msda_dam_scatter_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(
         (const __nv_bfloat16*)loc, (const __nv_bfloat16*)aw, level_sizes, level_start, out, d);
+  e = cudaGetLastError();
+  return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
+}
+
+
+int msda_token_gather(const void* x, const int64_t* idx, const int64_t* nums, void* out, int64_t B,
+                      int64_t S, int64_t K, int64_t row_bytes, void* stream) {
+  if (B < 0 || S < 0 || K < 0 || row_bytes <= 0) return MSDA_ERR_BAD_SHAPE;
+  if (B * K >= (int64_t(1) << 31) || B * S >= (int64_t(1) << 31) || row_bytes >= (int64_t(1) << 30))
+    return MSDA_ERR_TOO_LARGE;
+  if (B == 0 || K == 0) return MSDA_OK;
+  if (!idx || !out || (S > 0 && !x)) return MSDA_ERR_NULL_POINTER;
+  const unsigned grid = (unsigned)((B * K + 7) / 8);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (row_bytes % 16 == 0 && aligned16(x) && aligned16(out))
+    msda_token_gather_kernel<16><<<grid, 256, 0, st>>>((const char*)x, idx, nums, (char*)out, (int)B, (int)S,
+                                                       (int)K, (int)row_bytes);
+  else
+    msda_token_gather_kernel<1><<<grid, 256, 0, st>>>((const char*)x, idx, nums, (char*)out, (int)B, (int)S,
+                                                      (int)K, (int)row_bytes);
+  const cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
+}
+
+int msda_token_scatter(const void* base, const int64_t* idx, const int64_t* nums, const void* src, void* out,
+                       int* inverse, int64_t B, int64_t S, int64_t K, int64_t row_bytes, int zero_hit_rows,
+                       void* stream) {
+  if (B < 0 || S < 0 || K < 0 || row_bytes <= 0) return MSDA_ERR_BAD_SHAPE;
+  if (B * K >= (int64_t(1) << 31) || B * S >= (int64_t(1) << 31) || row_bytes >= (int64_t(1) << 30))
+    return MSDA_ERR_TOO_LARGE;
+  if (B == 0 || S == 0) return MSDA_OK;
+  if (!base || !out || !inverse || (K > 0 && (!idx || (!src && !zero_hit_rows)))) return MSDA_ERR_NULL_POINTER;
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e = cudaMemsetAsync(inverse, 0xff, (size_t)(B * S) * sizeof(int), st);   // -1: keep the base row
+  if (e != cudaSuccess) return cuda_fail(e);
+  if (K > 0)
+    msda_token_inverse_kernel<<<(unsigned)((B * K + 255) / 256), 256, 0, st>>>(idx, nums, inverse, (int)B, (int)S,
+                                                                               (int)K);
+  const unsigned grid = (unsigned)((B * S + 7) / 8);
+  const bool vec = row_bytes % 16 == 0 && aligned16(base) && aligned16(out) && (zero_hit_rows || aligned16(src));
+#define MSDA_SCATTER(V_, Z_)                                                                               \
+  msda_token_scatter_kernel<V_, Z_><<<grid, 256, 0, st>>>((const char*)base, inverse, (const char*)src,  \
+                                                          (char*)out, (int)B, (int)S, (int)K, (int)row_bytes)
+  if (vec && zero_hit_rows) MSDA_SCATTER(16, true);
+  else if (vec) MSDA_SCATTER(16, false);
+  else if (zero_hit_rows) MSDA_SCATTER(1, true);
+  else MSDA_SCATTER(1, false);
+#undef MSDA_SCATTER
   e = cudaGetLastError();
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
 }

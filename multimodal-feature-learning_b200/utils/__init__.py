@@ -2,5 +2,7 @@
 # encoders' get_reference_points
 from .dam import attn_map_to_flat_grid, compute_corr, idx_to_flat_grid
 from .reference_points import get_reference_points
+from .sparse_tokens import gather_tokens, scatter_tokens
 
-__all__ = ["attn_map_to_flat_grid", "compute_corr", "idx_to_flat_grid", "get_reference_points"]
+__all__ = ["attn_map_to_flat_grid", "compute_corr", "idx_to_flat_grid", "get_reference_points",
+           "gather_tokens", "scatter_tokens"]
