@@ -68,6 +68,8 @@ typedef enum {
   MSDA_ERR_WORKSPACE = -6,      /* workspace missing or too small */
   MSDA_ERR_CUDA = -7,           /* CUDA runtime error (see msda_last_cuda_error) */
   MSDA_ERR_MISALIGNED = -8,     /* a data pointer is not 16-byte aligned */
+  MSDA_ERR_UNSUPPORTED = -10,   /* msda_module_*: the call is outside the fused path (nothing was
+                                   enqueued); use msda_frontend_* + msda_forward_ex / msda_backward_ex */
   MSDA_ERR_NO_TMA = -9          /* internal: the TMA descriptor could not be encoded; the
                                    entry points fall back to the row-window kernels and
                                    never return it */
@@ -236,6 +238,37 @@ int msda_frontend_backward(const void* offsets, const void* aw, const void* ref,
                            void* grad_ref,
                            int64_t N, int64_t Lq, int64_t M, int64_t L, int64_t P,
                            int ref_dim, int dtype, void* stream);
+
+/*
+ * The module's front-end INSIDE the op (second step): for the
+ * shape class of the CTA-tile kernels (temporal maps (1, T_l), P = 4, L <= 4, D = 64 (f32, bf16) or
+ * 32 (f32), Lq >= 256) the tile kernels take what MSDeformAttn.forward holds BEFORE
+ * models/ops/modules/ms_deform_attn.py:98-117 -- offsets [N,Lq,M,L,P], logits [N,Lq,M,L*P],
+ * ref [N,Lq,L,ref_dim] -- and do the softmax, x = ref + off / T_l (ref_dim 1) or
+ * ref0 + off / P * ref1 * 0.5 (ref_dim 2) and y = 0.5 in their prologue; sampling_locations and
+ * attention_weights are never written to memory (37 MB at the encoder shape, and two kernels per
+ * module call).  The backward writes grad_offsets, grad_logits and (fp32, summed over heads and
+ * points, zero-filled inside; may be NULL) grad_ref directly.  `workspace` of the forward:
+ * msda_forward_workspace_bytes(..., flags) bytes, which is the `plan` the backward needs;
+ * `workspace` of the backward: msda_backward_workspace_bytes (bf16 image) or NULL for f32.
+ * msda_module_supported() != 0 <=> the pair accepts the shape; otherwise they return
+ * MSDA_ERR_UNSUPPORTED without enqueueing anything.  spatial_shapes must hold H_l = 1.
+ */
+int msda_module_supported(int64_t N, int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq,
+                          int64_t P, int ref_dim, int dtype, unsigned flags);
+int msda_module_forward(const void* value, const int64_t* spatial_shapes,
+                        const int64_t* level_start_index, const void* offsets, const void* logits,
+                        const void* ref, void* output,
+                        int64_t N, int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq, int64_t P,
+                        int ref_dim, int dtype, int padding, unsigned flags,
+                        void* workspace, size_t workspace_bytes, void* stream);
+int msda_module_backward(const void* value, const int64_t* spatial_shapes,
+                         const int64_t* level_start_index, const void* offsets, const void* logits,
+                         const void* ref, const void* grad_output, void* grad_value,
+                         void* grad_offsets, void* grad_logits, float* grad_ref,
+                         int64_t N, int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq, int64_t P,
+                         int ref_dim, int dtype, int padding, unsigned flags,
+                         void* workspace, size_t workspace_bytes, const void* plan, void* stream);
 
 /*
  * Decoder attention map (utils/dam.py:20-73 attn_map_to_flat_grid; consumer

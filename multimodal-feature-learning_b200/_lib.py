@@ -43,6 +43,9 @@ EXPORTED_SYMBOLS = (
     "msda_backward_workspace_bytes_flags",
     "msda_backward",
     "msda_backward_ex",
+    "msda_module_supported",
+    "msda_module_forward",
+    "msda_module_backward",
     "msda_frontend_forward",
     "msda_frontend_backward",
     "msda_dam_scatter",
@@ -97,6 +100,13 @@ def _declare(lib):
     lib.msda_backward.argtypes = (
         [vp] * 9 + [i64] * 7 + [c.c_int, c.c_int, u32, vp, c.c_size_t, vp]
     )
+    lib.msda_module_supported.restype = c.c_int
+    lib.msda_module_supported.argtypes = [i64] * 7 + [c.c_int, c.c_int, u32]
+    lib.msda_module_forward.restype = c.c_int
+    lib.msda_module_forward.argtypes = ([vp] * 7 + [i64] * 7 + [c.c_int, c.c_int, c.c_int, u32, vp, c.c_size_t, vp])
+    lib.msda_module_backward.restype = c.c_int
+    lib.msda_module_backward.argtypes = ([vp] * 11 + [i64] * 7 + [c.c_int, c.c_int, c.c_int, u32, vp, c.c_size_t,
+                                                                 vp, vp])
     lib.msda_frontend_forward.restype = c.c_int
     lib.msda_frontend_forward.argtypes = [vp] * 6 + [i64] * 5 + [c.c_int, c.c_int, vp]
     lib.msda_frontend_backward.restype = c.c_int

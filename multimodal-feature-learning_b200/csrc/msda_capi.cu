@@ -258,20 +258,24 @@ int tile_smem_attr(K kern, size_t smem, std::atomic<unsigned long long>& done) {
 }
 
 template <typename T>
-int launch_sort(const void* loc, int* perm, const Dims& d, cudaStream_t st) {
+int launch_sort(const SortSrc<T>& src, int* perm, const Dims& d, cudaStream_t st) {
   int hk_shift = 0;
-  // heads averaged into the sort key: 2 (one CTA sorts a batch item, and one SM pulls ~50 GB/s:
-  // 8 heads of 1500 queries are 30 us of sector fetches, 2 heads give the same order)
+  // heads averaged into the sort key: 2 (a key costs one fully divergent 32-byte sector per head)
   while (hk_shift < 1 && (2 << hk_shift) <= d.M) ++hk_shift;
-  if (d.Lq <= kSortStash) {   // cluster sort: deterministic order, eight SMs per batch item on the keys
-    msda_sort_cluster_kernel<T><<<(unsigned)d.N * kSortCluster, kSortThreads, 0, st>>>((const T*)loc, perm, d,
-                                                                                      hk_shift);
-    const cudaError_t e = cudaGetLastError();
-    return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
-  }
-  msda_sort_kernel<T><<<(unsigned)d.N, kSortThreads, 0, st>>>((const T*)loc, perm, d, hk_shift);
+  if (d.Lq <= kSortStash)   // cluster sort: deterministic order, eight SMs per batch item on the keys
+    msda_sort_cluster_kernel<T><<<(unsigned)d.N * kSortCluster, kSortThreads, 0, st>>>(src, perm, d, hk_shift);
+  else
+    msda_sort_kernel<T><<<(unsigned)d.N, kSortThreads, 0, st>>>(src, perm, d, hk_shift);
   const cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
+}
+int launch_sort_dtype(int dtype, const void* loc, int* perm, const Dims& d, cudaStream_t st) {
+  if (dtype == MSDA_BF16) {
+    const SortSrc<__nv_bfloat16> src = {(const __nv_bfloat16*)loc, nullptr, nullptr, nullptr, 0};
+    return launch_sort<__nv_bfloat16>(src, perm, d, st);
+  }
+  const SortSrc<float> src = {(const float*)loc, nullptr, nullptr, nullptr, 0};
+  return launch_sort<float>(src, perm, d, st);
 }
 
 // Launch a tile kernel as a programmatic dependent of the kernel before it in the stream (the
@@ -293,36 +297,34 @@ int launch_pdl(void (*kern)(KArgs...), unsigned grid, unsigned block, size_t sme
   const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
 }
-int launch_sort_dtype(int dtype, const void* loc, int* perm, const Dims& d, cudaStream_t st) {
-  return dtype == MSDA_BF16 ? launch_sort<__nv_bfloat16>(loc, perm, d, st) : launch_sort<float>(loc, perm, d, st);
-}
 
-template <typename T, int NU>
+template <typename T, int NU, bool FUSED = false>
 int launch_fwd_tile(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
                     const void* aw, const int* perm, void* out, const Dims& d, int dtype,
-                    cudaStream_t st, bool after_sort) {
+                    cudaStream_t st, bool after_sort, TileFront<T> front = TileFront<T>()) {
   static std::atomic<unsigned long long> attr_done{0};
   CUtensorMap map;
   if (!tile_value_map(&map, value, dtype, d)) return MSDA_ERR_NO_TMA;
-  auto kern = msda_fwd_tile_kernel<T, NU>;
+  auto kern = msda_fwd_tile_kernel<T, NU, FUSED>;
   constexpr size_t smem = TileSmem<T, NU>::kBytes;
   const int rc = tile_smem_attr(kern, smem, attr_done);
   if (rc != MSDA_OK) return rc;
   const int nchunks = (d.Lq + kTileQ - 1) / kTileQ;
   const unsigned grid = (unsigned)((int64_t)d.N * d.M * nchunks);
   return launch_pdl(kern, grid, kTileThreads, smem, st, after_sort, map, (const T*)value, shapes, lsi,
-                    (const T*)loc, (const T*)aw, perm, (T*)out, d, nchunks);
+                    (const T*)loc, (const T*)aw, perm, (T*)out, d, nchunks, front);
 }
 
-template <typename T, int NU, typename GV = float, typename U = Unit<T>>
+template <typename T, int NU, typename GV = float, typename U = Unit<T>, bool FUSED = false>
 int launch_bwd_tile(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
                     const void* aw, const void* gout, const int* perm, GV* gvalue, void* gloc,
                     void* gaw, const Dims& d, int dtype, cudaStream_t st,
-                    const DetHeader* det = nullptr, bool after_sort = false) {
+                    const DetHeader* det = nullptr, bool after_sort = false,
+                    TileFront<T> front = TileFront<T>()) {
   static std::atomic<unsigned long long> attr_done{0};
   CUtensorMap map;
   if (!tile_value_map(&map, value, dtype, d)) return MSDA_ERR_NO_TMA;
-  auto kern = msda_bwd_tile_kernel<T, NU, GV, U>;
+  auto kern = msda_bwd_tile_kernel<T, NU, GV, U, FUSED>;
   constexpr size_t smem = (size_t)kTileCapRows * NU * 8 * U::BYTES + (size_t)kTileBlocks * kTileBlkRows * 16 + 128;
   const int rc = tile_smem_attr(kern, smem, attr_done);
   if (rc != MSDA_OK) return rc;
@@ -330,7 +332,7 @@ int launch_bwd_tile(const void* value, const int64_t* shapes, const int64_t* lsi
   const unsigned grid = (unsigned)((int64_t)d.N * d.M * nchunks);
   return launch_pdl(kern, grid, kTileThreads, smem, st, after_sort, map, (const T*)value, shapes, lsi,
                     (const T*)loc, (const T*)aw, (const T*)gout, perm, gvalue, (T*)gloc, (T*)gaw, d,
-                    nchunks, det);
+                    nchunks, det, front);
 }
 
 // ---- plan / apply split (msda_plan.cuh) ---------------------------------------------
@@ -558,6 +560,7 @@ const char* msda_error_string(int status) {
     case MSDA_ERR_WORKSPACE: return "workspace missing or smaller than msda_backward_workspace_bytes()";
     case MSDA_ERR_CUDA: return "CUDA runtime error (see msda_last_cuda_error_string)";
     case MSDA_ERR_MISALIGNED: return "data pointer not aligned to its element size";
+    case MSDA_ERR_UNSUPPORTED: return "shape / dtype / flags outside the fused module path (use msda_frontend_* + msda_forward/backward)";
     case MSDA_ERR_NO_TMA: return "TMA tensor map could not be encoded (driver entry point missing or rejected)";
     default: return "unknown msda status";
   }
@@ -976,6 +979,134 @@ int msda_dam_scatter(const void* loc, const void* aw, const int64_t* level_sizes
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
 }
 
+
+}  // extern "C"
+
+// ---- fused module entry points (second step) -----------
+namespace {
+template <typename T>
+TileFront<T> make_front(const void* off, const void* logits, const void* ref, void* g_off, void* g_logits,
+                        float* g_ref, int ref_dim) {
+  TileFront<T> f;
+  f.off = (const T*)off; f.logits = (const T*)logits; f.ref = (const T*)ref;
+  f.g_off = (T*)g_off; f.g_logits = (T*)g_logits; f.g_ref = g_ref; f.ref_dim = ref_dim;
+  return f;
+}
+inline bool module_supported(const Dims& d, int64_t S, int64_t M, int64_t D, int64_t L, int dtype, int ref_dim,
+                             unsigned flags) {
+  if (ref_dim != 1 && ref_dim != 2) return false;
+  if (flags & (MSDA_FLAG_DETERMINISTIC | MSDA_FLAG_NO_TILE | MSDA_FLAG_NO_WINDOW | MSDA_FLAG_FORCE_GENERIC |
+               MSDA_FLAG_PLAN))
+    return false;
+  if (dtype != MSDA_F32 && dtype != MSDA_BF16) return false;
+  if (!(S * M * D < (int64_t(1) << 31)) || !fast_applies(D, L, dtype, flags)) return false;
+  return tile_applies(d, dtype, flags) && tile_encoder() != nullptr;
+}
+}  // namespace
+
+extern "C" {
+
+int msda_module_supported(int64_t N, int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq, int64_t P,
+                          int ref_dim, int dtype, unsigned flags) {
+  if (check_common(N, S, M, D, L, Lq, P, dtype, MSDA_PAD_ZEROS) != MSDA_OK || N == 0 || Lq == 0) return 0;
+  return module_supported(make_dims(N, S, M, D, L, Lq, P, MSDA_PAD_ZEROS), S, M, D, L, dtype, ref_dim, flags) ? 1 : 0;
+}
+
+int msda_module_forward(const void* value, const int64_t* spatial_shapes, const int64_t* level_start_index,
+                        const void* offsets, const void* logits, const void* ref, void* output, int64_t N,
+                        int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq, int64_t P, int ref_dim,
+                        int dtype, int padding, unsigned flags, void* workspace, size_t workspace_bytes,
+                        void* stream) {
+  const int rc = check_common(N, S, M, D, L, Lq, P, dtype, padding);
+  if (rc != MSDA_OK) return rc;
+  if (N == 0 || Lq == 0) return MSDA_OK;
+  if (!value || !spatial_shapes || !level_start_index || !offsets || !logits || !ref || !output)
+    return MSDA_ERR_NULL_POINTER;
+  Dims d = make_dims(N, S, M, D, L, Lq, P, padding);
+  if (!module_supported(d, S, M, D, L, dtype, ref_dim, flags) || !workspace || !aligned16(workspace) ||
+      workspace_bytes < tile_plan_bytes(N, Lq) || !aligned16(value) || !aligned16(output) || !aligned16(offsets) ||
+      !aligned16(logits))
+    return MSDA_ERR_UNSUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+  int* perm = (int*)workspace;
+  int r;
+  if (dtype == MSDA_BF16) {
+    const SortSrc<__nv_bfloat16> src = {nullptr, (const __nv_bfloat16*)offsets, (const __nv_bfloat16*)ref,
+                                        spatial_shapes, ref_dim};
+    if ((r = launch_sort<__nv_bfloat16>(src, perm, d, st)) != MSDA_OK) return r;
+    r = launch_fwd_tile<__nv_bfloat16, 1, true>(value, spatial_shapes, level_start_index, nullptr, nullptr, perm,
+                                                output, d, dtype, st, true,
+                                                make_front<__nv_bfloat16>(offsets, logits, ref, nullptr, nullptr,
+                                                                          nullptr, ref_dim));
+  } else {
+    const SortSrc<float> src = {nullptr, (const float*)offsets, (const float*)ref, spatial_shapes, ref_dim};
+    if ((r = launch_sort<float>(src, perm, d, st)) != MSDA_OK) return r;
+    const TileFront<float> f = make_front<float>(offsets, logits, ref, nullptr, nullptr, nullptr, ref_dim);
+    r = D == 64 ? launch_fwd_tile<float, 2, true>(value, spatial_shapes, level_start_index, nullptr, nullptr, perm,
+                                                  output, d, dtype, st, true, f)
+                : launch_fwd_tile<float, 1, true>(value, spatial_shapes, level_start_index, nullptr, nullptr, perm,
+                                                  output, d, dtype, st, true, f);
+  }
+  return r == MSDA_ERR_NO_TMA ? MSDA_ERR_UNSUPPORTED : r;
+}
+
+int msda_module_backward(const void* value, const int64_t* spatial_shapes, const int64_t* level_start_index,
+                         const void* offsets, const void* logits, const void* ref, const void* grad_output,
+                         void* grad_value, void* grad_offsets, void* grad_logits, float* grad_ref, int64_t N,
+                         int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq, int64_t P, int ref_dim,
+                         int dtype, int padding, unsigned flags, void* workspace, size_t workspace_bytes,
+                         const void* plan, void* stream) {
+  const int rc = check_common(N, S, M, D, L, Lq, P, dtype, padding);
+  if (rc != MSDA_OK) return rc;
+  if (N == 0 || Lq == 0) return MSDA_ERR_UNSUPPORTED;   // nothing fused about an empty call: use msda_backward
+  if (!value || !spatial_shapes || !level_start_index || !offsets || !logits || !ref || !grad_output ||
+      !grad_value || !grad_offsets || !grad_logits || !plan)
+    return MSDA_ERR_NULL_POINTER;
+  Dims d = make_dims(N, S, M, D, L, Lq, P, padding);
+  const size_t ws_need = ws_main_bytes(N, S, M, D, dtype, flags);
+  if (!module_supported(d, S, M, D, L, dtype, ref_dim, flags) || !aligned16(plan) || !aligned16(value) ||
+      !aligned16(grad_output) || !aligned16(grad_value) || !aligned16(offsets) || !aligned16(logits) ||
+      !aligned16(grad_offsets) || !aligned16(grad_logits))
+    return MSDA_ERR_UNSUPPORTED;
+  if (ws_need > 0 && (!workspace || workspace_bytes < ws_need)) return MSDA_ERR_WORKSPACE;
+  if (ws_need > 0 && !aligned16(workspace)) return MSDA_ERR_MISALIGNED;
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t esz = dtype == MSDA_F32 ? 4 : 2;
+  const size_t nvalue = (size_t)N * S * M * D;
+  void* acc = ws_need ? workspace : grad_value;
+  cudaError_t e = cudaSuccess;
+  if (!(flags & MSDA_FLAG_SKIP_ZERO_FILL)) e = cudaMemsetAsync(acc, 0, ws_need ? ws_need : nvalue * esz, st);
+  if (e == cudaSuccess && grad_ref)
+    e = cudaMemsetAsync(grad_ref, 0, (size_t)N * Lq * L * ref_dim * sizeof(float), st);
+  if (e != cudaSuccess) return cuda_fail(e);
+  const int* perm = (const int*)plan;
+  int r;
+  if (dtype == MSDA_BF16) {
+    r = launch_bwd_tile<__nv_bfloat16, 2, float, UnitBf16x4, true>(
+        value, spatial_shapes, level_start_index, nullptr, nullptr, grad_output, perm, (float*)acc, nullptr,
+        nullptr, d, dtype, st, nullptr, false,
+        make_front<__nv_bfloat16>(offsets, logits, ref, grad_offsets, grad_logits, grad_ref, ref_dim));
+  } else {
+    const TileFront<float> f = make_front<float>(offsets, logits, ref, grad_offsets, grad_logits, grad_ref, ref_dim);
+    r = D == 64 ? launch_bwd_tile<float, 2, float, Unit<float>, true>(
+                      value, spatial_shapes, level_start_index, nullptr, nullptr, grad_output, perm, (float*)acc,
+                      nullptr, nullptr, d, dtype, st, nullptr, false, f)
+                : launch_bwd_tile<float, 1, float, Unit<float>, true>(
+                      value, spatial_shapes, level_start_index, nullptr, nullptr, grad_output, perm, (float*)acc,
+                      nullptr, nullptr, d, dtype, st, nullptr, false, f);
+  }
+  if (r == MSDA_ERR_NO_TMA) return MSDA_ERR_UNSUPPORTED;
+  if (r != MSDA_OK) return r;
+  if (dtype == MSDA_BF16) {
+    const size_t n8 = nvalue / 8;
+    size_t blocks = (n8 + 255) / 256;
+    if (blocks > 148u * 16u) blocks = 148u * 16u;
+    msda_round_bf16_kernel<<<(unsigned)blocks, 256, 0, st>>>((const float*)acc, (__nv_bfloat16*)grad_value, n8);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e);
+  }
+  return MSDA_OK;
+}
 
 int msda_token_gather(const void* x, const int64_t* idx, const int64_t* nums, void* out, int64_t B,
                       int64_t S, int64_t K, int64_t row_bytes, void* stream) {

@@ -294,12 +294,17 @@ template <typename T, int NT, bool BWD>
 __device__ __forceinline__ void owner_point(const T* __restrict__ loc_g, const T* __restrict__ aw_g,
                                             int pt, int LP, int P, int MD, bool border,
                                             const int* s_lvl, TapMeta<NT>& tm, float (&cw)[NT],
-                                            float (&cx)[NT], float (&cy)[NT]) {
+                                            float (&cx)[NT], float (&cy)[NT],
+                                            const float* lpts = nullptr) {
 #pragma unroll
   for (int k = 0; k < NT; ++k) { tm.off[k] = -1; tm.w[k] = 0.f; cw[k] = cx[k] = cy[k] = 0.f; }
   if (pt >= LP) return;
   float lx, ly, a;
-  LocLoad<T>::ld(loc_g + 2 * pt, aw_g + pt, lx, ly, a);
+  if (lpts) {   // (x, y, weight) of the query's points as floats, e.g. in shared memory (fused front-end)
+    lx = lpts[3 * pt]; ly = lpts[3 * pt + 1]; a = lpts[3 * pt + 2];
+  } else {
+    LocLoad<T>::ld(loc_g + 2 * pt, aw_g + pt, lx, ly, a);
+  }
   const int l = pt / P;
   PointGeom<float> g;
   point_geom<float>(lx, ly, s_lvl[3 * l], s_lvl[3 * l + 1], s_lvl[3 * l + 2], border, g);
@@ -328,7 +333,7 @@ __device__ __forceinline__ void fwd_body(const T* __restrict__ value, const T* _
                                          const T* __restrict__ aw, T* __restrict__ out,
                                          const Dims& d, int b, int m, int q_first, int q_end,
                                          int q_step, const int* s_lvl, TapMeta<NT>* s_meta,
-                                         const int* qlist = nullptr) {
+                                         const int* qlist = nullptr, const float* lpts = nullptr) {
   // the group handles queries q_first, q_first + q_step, ... < q_end of (b, m) -- or, with a
   // query list (the time-sorted tiles of msda_tile.cuh), the queries qlist[q_first], ...,
   // negative entries skipped; s_meta = G entries private to the group
@@ -357,7 +362,7 @@ __device__ __forceinline__ void fwd_body(const T* __restrict__ value, const T* _
         TapMeta<NT> tm;
         float cw[NT], cx[NT], cy[NT];
         owner_point<T, NT, false>(loc_g, aw_g, base + j, LP, d.P, MD, d.border != 0, s_lvl, tm, cw,
-                                  cx, cy);
+                                  cx, cy, lpts ? lpts + (size_t)qq * LP * 3 : nullptr);
         s_meta[j] = tm;
       }
       __syncwarp(mask);
@@ -430,7 +435,8 @@ __device__ __forceinline__ void bwd_body(const T* __restrict__ value, const T* _
                                          T* __restrict__ gaw, const Dims& d, int b, int m,
                                          int q_first, int q_end, int q_step, const int* s_lvl,
                                          TapMeta<NT>* s_meta, float gv_scale = 1.f,
-                                         const int* qlist = nullptr) {
+                                         const int* qlist = nullptr, const float* lpts = nullptr,
+                                         float* lgrad = nullptr) {
   constexpr int E = U::E;
   const int lane = threadIdx.x & 31;
   const int j = threadIdx.x % G;
@@ -456,7 +462,8 @@ __device__ __forceinline__ void bwd_body(const T* __restrict__ value, const T* _
       float cw[NT], cx[NT], cy[NT];
       {
         TapMeta<NT> tm;
-        owner_point<T, NT, true>(loc_g, aw_g, pt, LP, d.P, MD, d.border != 0, s_lvl, tm, cw, cx, cy);
+        owner_point<T, NT, true>(loc_g, aw_g, pt, LP, d.P, MD, d.border != 0, s_lvl, tm, cw, cx, cy,
+                                 lpts ? lpts + (size_t)qq * LP * 3 : nullptr);
         s_meta[j] = tm;
       }
       __syncwarp(mask);
@@ -491,7 +498,14 @@ __device__ __forceinline__ void bwd_body(const T* __restrict__ value, const T* _
         gx = fmaf(cx[k], r, gx);
         gy = fmaf(cy[k], r, gy);
       }
-      if (pt < LP) LocLoad<T>::st(gloc + (grp * LP + pt) * 2, gaw + grp * LP + pt, gx, gy, ga);
+      if (pt < LP) {
+        if (lgrad) {   // (d/dx, d/dy, d/d weight) per point as floats, for a fused epilogue
+          float* gq = lgrad + ((size_t)qq * LP + pt) * 3;
+          gq[0] = gx; gq[1] = gy; gq[2] = ga;
+        } else {
+          LocLoad<T>::st(gloc + (grp * LP + pt) * 2, gaw + grp * LP + pt, gx, gy, ga);
+        }
+      }
       __syncwarp(mask);
     }
   }

@@ -104,6 +104,29 @@ template <> struct SortKey<__nv_bfloat16> {
   }
 };
 
+// Where the sort key comes from: the op's sampling locations, or -- fused module front-end -- the raw
+// offsets and reference points (x = ref + off * sc, sc = 1 / T_0 or ref1 * 0.5 / P).
+template <typename T>
+struct SortSrc {
+  const T* loc;
+  const T* off;
+  const T* ref;
+  const int64_t* shapes;
+  int ref_dim;
+};
+template <typename T>
+__device__ __forceinline__ float sort_key_sum4(const SortSrc<T>& s, const Dims& d, int b, int q, int hd) {
+  if (s.off == nullptr)
+    return SortKey<T>::sum4(s.loc + (((size_t)b * d.Lq + q) * d.M + hd) * (size_t)(d.L * d.P * 2));
+  const T* op = s.off + (((size_t)b * d.Lq + q) * d.M + hd) * (size_t)(d.L * d.P);
+  const T* rp = s.ref + ((size_t)b * d.Lq + q) * (size_t)(d.L * s.ref_dim);
+  float o = 0.f;
+#pragma unroll
+  for (int p = 0; p < 4; ++p) o += (float)to_acc<T>(op[p]);
+  const float sc = s.ref_dim == 1 ? 1.f / (float)s.shapes[1] : (float)to_acc<T>(rp[1]) * (0.5f / 4.f);
+  return 4.f * (float)to_acc<T>(rp[0]) + o * sc;
+}
+
 // One CTA per batch item: counting sort of its Lq queries by time bin.  perm[b][i] = index of
 // the i-th query in time order (ties in arbitrary order: no result depends on the order inside
 // a bin, the forward is bitwise independent of the permutation).  P == 4.
@@ -113,7 +136,7 @@ constexpr int kSortStash = 4096;   // static shared memory stays below 48 KB
 
 template <typename T>
 __global__ void __launch_bounds__(kSortThreads)
-msda_sort_kernel(const T* __restrict__ loc, int* __restrict__ perm, Dims d, int hk_shift) {
+msda_sort_kernel(SortSrc<T> src, int* __restrict__ perm, Dims d, int hk_shift) {
   __shared__ int s_hist[kSortBins];
   __shared__ int s_warp[32];
   __shared__ unsigned s_bin[kSortStash];   // (bin << 16) | rank inside the bin
@@ -126,15 +149,13 @@ msda_sort_kernel(const T* __restrict__ loc, int* __restrict__ perm, Dims d, int 
   __syncthreads();
   sort_stamp(1);
   const int HK = 1 << hk_shift;
-  const size_t hstride = (size_t)d.L * d.P * 2;
-  const T* lb = loc + (size_t)b * d.Lq * d.M * hstride;
   const float scale = (float)kSortBins / (float)(4 * HK);
   const bool stash = d.Lq <= kSortStash;
   const int items = d.Lq << hk_shift;
   const int items_up = (items + kSortThreads - 1) / kSortThreads * kSortThreads;
   auto bin_of = [&](int item) -> int {   // all lanes of a warp call it together
     const int q = item >> hk_shift, hd = item & (HK - 1);
-    float s = item < items ? SortKey<T>::sum4(lb + ((size_t)q * d.M + hd) * hstride) : 0.f;
+    float s = item < items ? sort_key_sum4<T>(src, d, b, q, hd) : 0.f;
     for (int o = 1; o < HK; o <<= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
     // NaN -> bin 0 (fmaxf drops it), +-inf clamp
     return __float2int_rd(fminf(fmaxf(s * scale, 0.f), (float)(kSortBins - 1)));
@@ -145,8 +166,7 @@ msda_sort_kernel(const T* __restrict__ loc, int* __restrict__ perm, Dims d, int 
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const int item = base + u * kSortThreads;
-      ks[u] = item < items ? SortKey<T>::sum4(lb + ((size_t)(item >> hk_shift) * d.M + (item & (HK - 1))) * hstride)
-                           : 0.f;
+      ks[u] = item < items ? sort_key_sum4<T>(src, d, b, item >> hk_shift, item & (HK - 1)) : 0.f;
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
@@ -217,7 +237,7 @@ constexpr int kSortBins2 = 1 << kSortBits;
 
 template <typename T>
 __global__ void __cluster_dims__(kSortCluster, 1, 1) __launch_bounds__(kSortThreads)
-msda_sort_cluster_kernel(const T* __restrict__ loc, int* __restrict__ perm, Dims d, int hk_shift) {
+msda_sort_cluster_kernel(SortSrc<T> src, int* __restrict__ perm, Dims d, int hk_shift) {
   namespace cg = cooperative_groups;
   __shared__ unsigned s_key[kSortStash];     // w per query, later the sorted words
   __shared__ unsigned s_tmp[kSortStash];     // (slot << 16 | bin) per query, later bin-ordered words
@@ -229,8 +249,6 @@ msda_sort_cluster_kernel(const T* __restrict__ loc, int* __restrict__ perm, Dims
   const int b = blockIdx.x / kSortCluster, tid = threadIdx.x;
   sort_stamp(0);
   const int HK = 1 << hk_shift;
-  const size_t hstride = (size_t)d.L * d.P * 2;
-  const T* lb = loc + (size_t)b * d.Lq * d.M * hstride;
   const float scale = 65536.f / (float)(4 * HK);
   unsigned* key0 = cluster.map_shared_rank(s_key, 0);
   const int per = (d.Lq + kSortCluster - 1) / kSortCluster;
@@ -239,7 +257,7 @@ msda_sort_cluster_kernel(const T* __restrict__ loc, int* __restrict__ perm, Dims
   const int items_up = (items + 31) & ~31;
   for (int item = tid; item < items_up; item += kSortThreads) {
     const int q = q0 + (item >> hk_shift), hd = item & (HK - 1);
-    float sk = item < items ? SortKey<T>::sum4(lb + ((size_t)q * d.M + hd) * hstride) : 0.f;
+    float sk = item < items ? sort_key_sum4<T>(src, d, b, q, hd) : 0.f;
     for (int o = 1; o < HK; o <<= 1) sk += __shfl_xor_sync(0xffffffffu, sk, o);
     // NaN -> 0 (fmaxf drops it), +-inf clamp
     const unsigned kb = (unsigned)__float2int_rd(fminf(fmaxf(sk * scale, 0.f), 65535.f));
@@ -385,6 +403,99 @@ __device__ __forceinline__ void tile_lds(const char* p, typename U::Raw (&buf)[U
   }
 }
 
+// ---- fused module front-end (second step) ----------
+// With a TileFront the tile kernels take what MSDeformAttn.forward has BEFORE
+// models/ops/modules/ms_deform_attn.py:98-117 -- raw sampling offsets, attention logits and
+// reference points -- and do the softmax over L*P, x = ref + off / T_l (or the (centre, length)
+// form) and y = 0.5 in their prologue: sampling_locations and attention_weights never exist in
+// HBM.  The backward's epilogue turns (d/dx, d/d aw) straight into grad_offsets, grad_logits
+// (softmax backward) and grad_ref (fp32 atomics over heads and points).
+template <typename T>
+struct TileFront {
+  const T* off;        // [N, Lq, M, L, P]   (nullptr: not fused, the kernels read loc / aw)
+  const T* logits;     // [N, Lq, M, L*P]
+  const T* ref;        // [N, Lq, L, ref_dim]
+  T* g_off;            // backward outputs
+  T* g_logits;
+  float* g_ref;        // [N, Lq, L, ref_dim] fp32, zeroed by the host side (nullptr: not wanted)
+  int ref_dim;
+};
+
+template <typename T> struct Front4;       // 4 consecutive elements <-> 4 floats
+template <> struct Front4<float> {
+  static __device__ __forceinline__ void ld(const float* p, float (&v)[4]) {
+    const float4 t = __ldg(reinterpret_cast<const float4*>(p));
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  }
+  static __device__ __forceinline__ void st(float* p, const float (&v)[4]) {
+    __stcs(reinterpret_cast<float4*>(p), make_float4(v[0], v[1], v[2], v[3]));
+  }
+};
+template <> struct Front4<__nv_bfloat16> {
+  static __device__ __forceinline__ void ld(const __nv_bfloat16* p, float (&v)[4]) {
+    const uint2 t = __ldg(reinterpret_cast<const uint2*>(p));
+    v[0] = __uint_as_float(t.x << 16); v[1] = __uint_as_float(t.x & 0xffff0000u);
+    v[2] = __uint_as_float(t.y << 16); v[3] = __uint_as_float(t.y & 0xffff0000u);
+  }
+  static __device__ __forceinline__ void st(__nv_bfloat16* p, const float (&v)[4]) {
+    const __nv_bfloat162 a = __floats2bfloat162_rn(v[0], v[1]), b = __floats2bfloat162_rn(v[2], v[3]);
+    uint2 t;
+    t.x = *reinterpret_cast<const uint32_t*>(&a);
+    t.y = *reinterpret_cast<const uint32_t*>(&b);
+    __stcs(reinterpret_cast<uint2*>(p), t);
+  }
+};
+
+// The 2 x 4 points of lane (qi, h) -- levels h and h + 2 of its query -- from the raw module
+// tensors.  All 32 lanes call it together (the softmax sum crosses to lane ^ 4, which holds the
+// query's other two levels).  off[][] are returned for the (centre, length) backward; sc[] is
+// d x / d off per level.
+template <typename T>
+__device__ __forceinline__ void tile_front_points(const TileFront<T>& f, const Dims& d, size_t grp, size_t bq,
+                                                  int h, const int* s_lvl, float (&x)[2][4], float (&y)[2][4],
+                                                  float (&a)[2][4], float (&off)[2][4], float (&sc)[2]) {
+  constexpr unsigned FULL = 0xffffffffu;
+  float lg[2][4], r0[2];
+  float mx = -INFINITY;
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int l = h + 2 * i;
+    const bool on = l < d.L;
+    const int ls = on ? l : 0;
+    Front4<T>::ld(f.off + (grp * d.L + ls) * kWinP, off[i]);
+    Front4<T>::ld(f.logits + (grp * d.L + ls) * kWinP, lg[i]);
+    const T* rp = f.ref + (bq * d.L + ls) * f.ref_dim;
+    r0[i] = (float)to_acc<T>(rp[0]);
+    const float tl = (float)s_lvl[3 * ls + 1];
+    sc[i] = f.ref_dim == 1 ? 1.f / tl : (float)to_acc<T>(rp[f.ref_dim - 1]) * (0.5f / (float)kWinP);
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      if (!on) lg[i][p] = -INFINITY;
+      mx = fmaxf(mx, lg[i][p]);
+      // the module's own arithmetic (ms_deform_attn.py:102-108): ref + off / T_l, or
+      // ref0 + off / P * ref1 * 0.5
+      x[i][p] = f.ref_dim == 1 ? r0[i] + off[i][p] / tl
+                               : r0[i] + off[i][p] / (float)kWinP * (float)to_acc<T>(rp[f.ref_dim - 1]) * 0.5f;
+      y[i][p] = 0.5f;
+    }
+  }
+  mx = fmaxf(mx, __shfl_xor_sync(FULL, mx, 4));
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      a[i][p] = expf(lg[i][p] - mx);     // exp(-inf) = 0 for the levels that do not exist
+      sum += a[i][p];
+    }
+  sum += __shfl_xor_sync(FULL, sum, 4);
+  const float inv = 1.f / sum;
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int p = 0; p < 4; ++p) a[i][p] *= inv;
+}
+
 // ---- the tile's plan ------------------------------------------------------------
 // Everything a thread knows after the prologue.  Block = the 8 lanes that share g = tid / 8;
 // lane (qi = j & 3, h = j >> 2) owns the points of query qi at levels h and h + 2.
@@ -407,12 +518,13 @@ struct TilePlan {
 // PAIR: row loops run over pairs of rows (backward): every level of a plan is padded to an even
 // row count.
 // On return (plan.ok) the block's weights are in Wt, the value boxes are in flight on mbar.
-template <typename T, bool PAIR, bool ISSUE = true>
+template <typename T, bool PAIR, bool ISSUE = true, bool FUSED = false>
 __device__ __forceinline__ void tile_prologue(const CUtensorMap* vmap, const T* __restrict__ loc,
                                               const T* __restrict__ aw, const Dims& d, int b, int m,
                                               int q, const int* s_lvl, int* s_win, char* vtile,
                                               unsigned row_bytes, float4* Wt,
-                                              unsigned long long* mbar, TilePlan& pl) {
+                                              unsigned long long* mbar, TilePlan& pl,
+                                              const TileFront<T>* front = nullptr) {
   constexpr unsigned FULL = 0xffffffffu;
   const int tid = threadIdx.x, j = tid & 7, qi = j & 3, h = j >> 2;
   const int gbase = (tid & 31) & ~7;
@@ -423,13 +535,23 @@ __device__ __forceinline__ void tile_prologue(const CUtensorMap* vmap, const T* 
   int r0[2][4];
   float w0[2][4], w1[2][4];
   int lo[2], hi[2];
+  float fx[2][4], fy[2][4], fa[2][4];
+  if (FUSED) {
+    float foff[2][4], fsc[2];
+    tile_front_points<T>(*front, d, grp, (size_t)b * d.Lq + (have_q ? q : 0), h, s_lvl, fx, fy, fa, foff, fsc);
+  }
 #pragma unroll
   for (int i = 0; i < 2; ++i) {
     const int l = h + 2 * i;
     const bool active = have_q && l < d.L;
     const int ls = l < d.L ? l : 0;
     float x[4], y[4], a[4];
-    WinPts<T>::ld(loc + (grp * LP + ls * kWinP) * 2, aw + grp * LP + ls * kWinP, x, y, a);
+    if (FUSED) {
+#pragma unroll
+      for (int p = 0; p < 4; ++p) { x[p] = fx[i][p]; y[p] = fy[i][p]; a[p] = fa[i][p]; }
+    } else {
+      WinPts<T>::ld(loc + (grp * LP + ls * kWinP) * 2, aw + grp * LP + ls * kWinP, x, y, a);
+    }
     const int W = s_lvl[3 * ls + 1], start = s_lvl[3 * ls + 2];
     lo[i] = kTileBig; hi[i] = -kTileBig;
 #pragma unroll
@@ -562,19 +684,82 @@ __device__ __forceinline__ bool tile_setup(const int64_t* __restrict__ shapes,
 template <typename T, int NU, int NT>
 __device__ __noinline__ void tile_fallback_fwd(const T* value, const T* loc, const T* aw, T* out, Dims d,
                                                int b, int m, const int* s_lvl, char* scratch,
-                                               const int* s_q) {
+                                               const int* s_q, const float* lpts = nullptr) {
   const int g = threadIdx.x >> 3;
   fwd_body<T, NU, 8, NT>(value, loc, aw, out, d, b, m, g, kTileQ, kTileBlocks, s_lvl,
-                         reinterpret_cast<TapMeta<NT>*>(scratch) + g * 8, s_q);
+                         reinterpret_cast<TapMeta<NT>*>(scratch) + g * 8, s_q, lpts);
 }
 template <typename T, int NU, int NT, typename GV, typename U>
 __device__ __noinline__ void tile_fallback_bwd(const T* value, const T* loc, const T* aw, const T* gout,
                                                GV* gvalue, T* gloc, T* gaw, Dims d, int b, int m,
                                                const int* s_lvl, char* scratch, float gv_scale,
-                                               const int* s_q) {
+                                               const int* s_q, const float* lpts = nullptr,
+                                               float* lgrad = nullptr) {
   const int g = threadIdx.x >> 3;
   bwd_body<T, NU, 8, NT, GV, U>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, g, kTileQ, kTileBlocks,
-                                s_lvl, reinterpret_cast<TapMeta<NT>*>(scratch) + g * 8, gv_scale, s_q);
+                                s_lvl, reinterpret_cast<TapMeta<NT>*>(scratch) + g * 8, gv_scale, s_q, lpts,
+                                lgrad);
+}
+
+// Fused front-end, tile without a plan: the thread's points (x, y, weight) as floats into shared
+// memory [kTileQ][L*4][3], where the per-tap body finds them.  All threads; ends with a barrier.
+template <typename T>
+__device__ __forceinline__ void tile_front_stash(const TileFront<T>& f, const Dims& d, int b, int m, int q,
+                                                 const int* s_lvl, float* lp) {
+  const int tid = threadIdx.x, g = tid >> 3, j = tid & 7, qi = j & 3, h = j >> 2;
+  const int qq = q >= 0 ? q : 0;
+  float x[2][4], y[2][4], a[2][4], off[2][4], sc[2];
+  tile_front_points<T>(f, d, ((size_t)b * d.Lq + qq) * d.M + m, (size_t)b * d.Lq + qq, h, s_lvl, x, y, a, off, sc);
+  const int LP = d.L * kWinP;
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int l = h + 2 * i;
+    if (l < d.L) {
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        float* o = lp + ((size_t)(g * kWinQ + qi) * LP + l * kWinP + p) * 3;
+        o[0] = x[i][p]; o[1] = y[i][p]; o[2] = a[i][p];
+      }
+    }
+  }
+  __syncthreads();
+}
+
+// Fused front-end, backward epilogue: (d/dx, d/d weight) of the thread's 2 x 4 points ->
+// grad_offsets, grad_logits (softmax backward over the query's L*4 points: this lane's 8 and lane
+// ^ 4's), grad_ref (fp32 atomics: summed over points here, over heads in memory).  All 32 lanes.
+template <typename T>
+__device__ __forceinline__ void tile_front_backward(const TileFront<T>& f, const Dims& d, int b, int m, int q,
+                                                    int h, const float (&a)[2][4], const float (&off)[2][4],
+                                                    const float (&sc)[2], const float (&gx)[2][4],
+                                                    const float (&ga)[2][4]) {
+  float dot = 0.f;
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int p = 0; p < 4; ++p) dot = fmaf(a[i][p], ga[i][p], dot);
+  dot += __shfl_xor_sync(0xffffffffu, dot, 4);
+  if (q < 0) return;
+  const size_t grp = ((size_t)b * d.Lq + q) * d.M + m, bq = (size_t)b * d.Lq + q;
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int l = h + 2 * i;
+    if (l >= d.L) continue;
+    float go[4], gl[4], gr0 = 0.f, gr1 = 0.f;
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      go[p] = gx[i][p] * sc[i];
+      gl[p] = a[i][p] * (ga[i][p] - dot);
+      gr0 += gx[i][p];
+      gr1 = fmaf(gx[i][p], off[i][p], gr1);
+    }
+    Front4<T>::st(f.g_off + (grp * d.L + l) * kWinP, go);
+    Front4<T>::st(f.g_logits + (grp * d.L + l) * kWinP, gl);
+    if (f.g_ref) {
+      atomicAdd(f.g_ref + (bq * d.L + l) * f.ref_dim, gr0);
+      if (f.ref_dim == 2) atomicAdd(f.g_ref + (bq * d.L + l) * 2 + 1, gr1 * (0.5f / (float)kWinP));
+    }
+  }
 }
 
 template <typename T, int NU>
@@ -586,12 +771,13 @@ struct TileSmem {
 };
 
 // ------------------------------- forward ------------------------------------
-template <typename T, int NU>
+template <typename T, int NU, bool FUSED = false>
 __global__ void __launch_bounds__(kTileThreads, MSDA_TILE_FWD_CTAS)
 msda_fwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restrict__ value,
                      const int64_t* __restrict__ shapes, const int64_t* __restrict__ lsi,
                      const T* __restrict__ loc, const T* __restrict__ aw,
-                     const int* __restrict__ perm, T* __restrict__ out, Dims d, int nchunks) {
+                     const int* __restrict__ perm, T* __restrict__ out, Dims d, int nchunks,
+                     TileFront<T> front) {
   using U = Unit<T>;
   using Raw = typename U::Raw;
   using SM = TileSmem<T, NU>;
@@ -614,15 +800,22 @@ msda_fwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
   const bool one_d = tile_setup(shapes, lsi, perm, d, b, chunk, s_lvl, s_win, s_q, &s_mbar);
   tile_stamp(1);
   if (!one_d) {
+    if (FUSED) __trap();   // the module's maps are (1, T_l): precondition of the fused entry points
     tile_fallback_fwd<T, NU, 4>(value, loc, aw, out, d, b, m, s_lvl, s_plan, s_q);
     return;
   }
   float4* Wt = reinterpret_cast<float4*>(s_plan) + g * kTileBlkRows;
   TilePlan pl;
-  tile_prologue<T, false>(&vmap, loc, aw, d, b, m, s_q[g * kWinQ + (j & 3)], s_lvl, s_win, vtile, RB, Wt,
-                          &s_mbar, pl);
+  tile_prologue<T, false, true, FUSED>(&vmap, loc, aw, d, b, m, s_q[g * kWinQ + (j & 3)], s_lvl, s_win, vtile,
+                                       RB, Wt, &s_mbar, pl, &front);
   if (!pl.ok) {
-    tile_fallback_fwd<T, NU, 2>(value, loc, aw, out, d, b, m, s_lvl, s_plan, s_q);
+    if (FUSED) {
+      float* lp = reinterpret_cast<float*>(vtile);
+      tile_front_stash<T>(front, d, b, m, s_q[g * kWinQ + (j & 3)], s_lvl, lp);
+      tile_fallback_fwd<T, NU, 2>(value, loc, aw, out, d, b, m, s_lvl, s_plan + SM::kPlanBytes - 4096, s_q, lp);
+    } else {
+      tile_fallback_fwd<T, NU, 2>(value, loc, aw, out, d, b, m, s_lvl, s_plan, s_q);
+    }
     return;
   }
   tile_stamp(4);
@@ -687,14 +880,14 @@ msda_fwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
 // unit and lane of a block, 4.7 rows per query in time order); the dots <grad_out, value row>
 // are transpose-reduced over the 8 lanes for two rows at a time and stored over the weights;
 // the epilogue reads the points again (L2) and forms grad_attn_weight / grad_sampling_loc.
-template <typename T, int NU, typename GV = float, typename U = Unit<T>>
+template <typename T, int NU, typename GV = float, typename U = Unit<T>, bool FUSED = false>
 __global__ void __launch_bounds__(kTileThreads, MSDA_TILE_BWD_CTAS)
 msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restrict__ value,
                      const int64_t* __restrict__ shapes, const int64_t* __restrict__ lsi,
                      const T* __restrict__ loc, const T* __restrict__ aw,
                      const T* __restrict__ gout, const int* __restrict__ perm,
                      GV* __restrict__ gvalue, T* __restrict__ gloc, T* __restrict__ gaw, Dims d,
-                     int nchunks, const DetHeader* __restrict__ det) {
+                     int nchunks, const DetHeader* __restrict__ det, TileFront<T> front) {
   const float gv_scale = det ? (float)det->scale : 1.f;
   using Raw = typename U::Raw;
   constexpr int G = 8;
@@ -715,6 +908,7 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
   const int chunk = t2 % nchunks, b = t2 / nchunks;
   const bool one_d = tile_setup(shapes, lsi, perm, d, b, chunk, s_lvl, s_win, s_q, &s_mbar);
   if (!one_d) {
+    if (FUSED) __trap();
     tile_fallback_bwd<T, NU, 4, GV, U>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, s_lvl, s_plan,
                                        gv_scale, s_q);
     return;
@@ -742,10 +936,37 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
   float4* Wt = reinterpret_cast<float4*>(s_plan) + g * kTileBlkRows;
   float* Gs = reinterpret_cast<float*>(Wt);   // the dots G[t][qi] overwrite Wt[t][qi] pair by pair
   TilePlan pl;
-  tile_prologue<T, true>(&vmap, loc, aw, d, b, m, my_q, s_lvl, s_win, vtile, RB, Wt, &s_mbar, pl);
+  tile_prologue<T, true, true, FUSED>(&vmap, loc, aw, d, b, m, my_q, s_lvl, s_win, vtile, RB, Wt, &s_mbar, pl,
+                                      &front);
   if (!pl.ok) {
-    tile_fallback_bwd<T, NU, 2, GV, U>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, s_lvl, s_plan,
-                                       gv_scale, s_q);
+    if (FUSED) {
+      // points to shared memory, per-tap body with its per-point gradients to shared memory, then
+      // the fused epilogue on those
+      const int LPf = d.L * kWinP;
+      float* lp = reinterpret_cast<float*>(vtile);
+      float* lg = lp + kTileQ * LPf * 3;
+      tile_front_stash<T>(front, d, b, m, my_q, s_lvl, lp);
+      tile_fallback_bwd<T, NU, 2, GV, U>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, s_lvl,
+                                         s_plan + kTileBlocks * kTileBlkRows * 16 - 4096, gv_scale, s_q, lp, lg);
+      __syncthreads();
+      float x[2][4], y[2][4], a[2][4], off[2][4], sc[2], gxx[2][4], gaa[2][4];
+      const int qs = my_q >= 0 ? my_q : 0;
+      tile_front_points<T>(front, d, ((size_t)b * d.Lq + qs) * d.M + m, (size_t)b * d.Lq + qs, h, s_lvl, x, y, a,
+                           off, sc);
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+          const int l = h + 2 * i;
+          const float* gq = lg + ((size_t)(g * kWinQ + qi) * LPf + (l < d.L ? l : 0) * kWinP + p) * 3;
+          gxx[i][p] = (l < d.L && my_q >= 0) ? gq[0] : 0.f;
+          gaa[i][p] = (l < d.L && my_q >= 0) ? gq[2] : 0.f;
+        }
+      tile_front_backward<T>(front, d, b, m, my_q, h, a, off, sc, gxx, gaa);
+    } else {
+      tile_fallback_bwd<T, NU, 2, GV, U>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, s_lvl, s_plan,
+                                         gv_scale, s_q);
+    }
     return;
   }
   float2 go[kWinQ][NU][E / 2];
@@ -822,13 +1043,21 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
   const bool have_q = my_q >= 0;
   const int LP = d.L * kWinP;
   const size_t grp_me = ((size_t)b * d.Lq + (have_q ? my_q : 0)) * d.M + m;
+  float fx[2][4], fy[2][4], fa[2][4], foff[2][4], fsc[2], fgx[2][4], fga[2][4];
+  if (FUSED)
+    tile_front_points<T>(front, d, grp_me, (size_t)b * d.Lq + (have_q ? my_q : 0), h, s_lvl, fx, fy, fa, foff, fsc);
 #pragma unroll
   for (int i = 0; i < 2; ++i) {
     const int l = h + 2 * i;
     const bool active = have_q && l < d.L;
     const int ls = l < d.L ? l : 0;
     float x[4], y[4], a[4];
-    WinPts<T>::ld_stream(loc + (grp_me * LP + ls * kWinP) * 2, aw + grp_me * LP + ls * kWinP, x, y, a);
+    if (FUSED) {
+#pragma unroll
+      for (int p = 0; p < 4; ++p) { x[p] = fx[i][p]; y[p] = fy[i][p]; a[p] = fa[i][p]; }
+    } else {
+      WinPts<T>::ld_stream(loc + (grp_me * LP + ls * kWinP) * 2, aw + grp_me * LP + ls * kWinP, x, y, a);
+    }
     const int W = s_lvl[3 * ls + 1], start = s_lvl[3 * ls + 2];
     const int tb = i == 0 ? (h ? pl.bpoff[1] - pl.blo[1] : pl.bpoff[0] - pl.blo[0])
                           : (h ? pl.bpoff[3] - pl.blo[3] : pl.bpoff[2] - pl.blo[2]);
@@ -846,10 +1075,12 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
       ga[p] = fmaf(c.k0, g0, c.k1 * g1);
       gx[p] = c.fx * (g1 - g0);
       gy[p] = fmaf(c.cy0, g0, c.cy1 * g1);
+      if (FUSED) { fgx[i][p] = gx[p]; fga[i][p] = ga[p]; }
     }
-    if (active)
+    if (!FUSED && active)
       WinPts<T>::st(gloc + (grp_me * LP + l * kWinP) * 2, gaw + grp_me * LP + l * kWinP, gx, gy, ga);
   }
+  if (FUSED) tile_front_backward<T>(front, d, b, m, my_q, h, fa, foff, fsc, fgx, fga);
 }
 
 }  // namespace msda

@@ -19,6 +19,7 @@ import torch.nn.functional as F
 from torch import nn
 from torch.nn.init import constant_, xavier_uniform_
 
+from ..functions import module_func
 from ..functions.frontend import msdeform_frontend
 from ..functions.ms_deform_attn_func import ms_deform_attn
 
@@ -57,6 +58,9 @@ class MSDeformAttn(nn.Module):
         # softmax + sampling locations in one kernel (functions/frontend.py); False = the
         # reference's chain of torch kernels (ms_deform_attn.py:98-117), same results
         self.fused_frontend = True
+        # ... and, where the call qualifies (functions/module_func.py: encoder-class shapes), that
+        # arithmetic inside the op's tile kernels: no sampling_locations / attention_weights in memory
+        self.fused_op = True
         self._len_cache = {}
         self._hw_cache = None   # (weakref to input_spatial_shapes, its version, the [L, 2] (1, T_l) tensor)
 
@@ -65,6 +69,13 @@ class MSDeformAttn(nn.Module):
         self.value_proj = nn.Linear(d_model, d_model)
         self.output_proj = nn.Linear(d_model, d_model)
         self._reset_parameters()
+
+    def __getstate__(self):
+        # the caches hold a weakref / per-process verdicts: not part of a pickled module
+        st = self.__dict__.copy()
+        st["_hw_cache"] = None
+        st["_len_cache"] = {}
+        return st
 
     def _reset_parameters(self):
         # ms_deform_attn.py:62-77: offsets start on a ring of head directions,
@@ -100,14 +111,16 @@ class MSDeformAttn(nn.Module):
         return hw
 
     def _check_lengths(self, input_spatial_shapes, Len_in):
-        # ms_deform_attn.py:93 syncs the device every call; cache the verdict
-        # per (tensor storage, version) so steady-state calls stay async.
-        key = (input_spatial_shapes.data_ptr(), input_spatial_shapes._version, Len_in)
-        if key not in self._len_cache:
-            if len(self._len_cache) > 64:
-                self._len_cache.clear()
-            self._len_cache[key] = int(input_spatial_shapes.sum()) == Len_in
-        assert self._len_cache[key], "sum of input_spatial_shapes must equal the flattened input length"
+        # ms_deform_attn.py:93 syncs the device every call; cache the verdict per tensor OBJECT
+        # (weak reference: a recycled address is a different tensor) and version, so steady-state
+        # calls stay async.
+        c = self._len_cache.get("last")
+        if not (c is not None and c[0]() is input_spatial_shapes and c[1] == input_spatial_shapes._version
+                and c[2] == Len_in):
+            c = (weakref.ref(input_spatial_shapes), input_spatial_shapes._version, Len_in,
+                 int(input_spatial_shapes.sum()) == Len_in)
+            self._len_cache["last"] = c
+        assert c[3], "sum of input_spatial_shapes must equal the flattened input length"
 
     def forward(self, query, reference_points, input_flatten, input_spatial_shapes,
                 input_level_start_index, input_padding_mask=None, is_sparse=False):
@@ -138,6 +151,13 @@ class MSDeformAttn(nn.Module):
         if reference_points.shape[-1] not in (1, 2):
             raise ValueError("Last dim of reference_points must be 1 or 2, but get {} instead.".format(
                 reference_points.shape[-1]))
+        if (self.fused_frontend and self.fused_op and not is_sparse
+                and module_func.supported(value, sampling_offsets, reference_points)):
+            # softmax + sampling locations inside the tile kernels: no loc / aw in memory
+            output = module_func.msdeform_module(value, self._shapes_hw(input_spatial_shapes),
+                                                 input_level_start_index, sampling_offsets, logits,
+                                                 reference_points, self.padding_mode)
+            return self.output_proj(output)
         if self.fused_frontend:
             loc_xy, attention_weights = msdeform_frontend(sampling_offsets, logits, reference_points,
                                                           input_spatial_shapes)
