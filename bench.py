@@ -405,6 +405,73 @@ def time_kernel_to_beat(ring, steps, warmup):
             "bwd_ms": med([e[1].elapsed_time(e[2]) for e in ev])}
 
 
+def time_module_call(dev, steps, warmup, reps):
+    """what sits between the module's Linear layers and its output projection
+    (ms_deform_attn.py:98-122) at the ENC shape, through the C ABI: (a) front-end kernel + op forward,
+    op backward + front-end backward (loc / aw through HBM); (b) msda_module_forward / backward
+    (softmax and locations inside the tile kernels).  ms per forward + backward, CUDA events, median."""
+    import torch
+    from mfl_b200 import _lib, synthetic
+    lib = _lib.load()
+    w = synthetic.WORKLOADS["ENC"]
+    N, M, D, P, T = w["N"], w["M"], w["D"], w["P"], w["T"]
+    L, S = len(T), sum(T)
+    Lq = S
+    sets = []
+    for r in range(2):
+        g = torch.Generator(device=dev).manual_seed(777 + r)
+        f = dict(device=dev, generator=g)
+        ref = synthetic.encoder_reference_points(T, dev)[None, :, None, None].expand(N, -1, L, 1).contiguous()
+        off = synthetic.head_bias(M, P, dev)[None, None, :, None, :] + 0.5 * torch.randn(N, Lq, M, L, P, **f)
+        sets.append(dict(value=torch.randn(N, S, M, D, **f), off=off.contiguous(), logits=torch.randn(N, Lq, M, L * P, **f),
+                         ref=ref, gout=torch.randn(N, Lq, M * D, **f)))
+    Tt = torch.tensor(T, device=dev)
+    shapes = torch.stack((torch.ones_like(Tt), Tt), -1).contiguous()
+    lsi = torch.cat((Tt.new_zeros(1), Tt.cumsum(0)[:-1]))
+    e = lambda *sh: torch.empty(*sh, device=dev)
+    loc, aw, out = e(N, Lq, M, L, P, 2), e(N, Lq, M, L, P), e(N, Lq, M * D)
+    gv, gloc, gaw = e(N, S, M, D), e(N, Lq, M, L, P, 2), e(N, Lq, M, L, P)
+    goff, glog, gref = e(N, Lq, M, L, P), e(N, Lq, M, L * P), e(N, Lq, L, 1)
+    dims = (N, S, M, D, L, Lq, P)
+    nb = lib.msda_forward_workspace_bytes(*dims, 0, 0)
+    plan = torch.empty(max(nb // 4, 1), dtype=torch.int32, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    ck = _lib.check
+    p = lambda t: t.data_ptr()
+
+    def two_kernel(c):
+        ck(lib.msda_frontend_forward(p(c["off"]), p(c["logits"]), p(c["ref"]), p(Tt), p(loc), p(aw), N, Lq, M, L, P, 1, 0, st))
+        ck(lib.msda_forward_ex(p(c["value"]), p(shapes), p(lsi), p(loc), p(aw), p(out), *dims, 0, 0, 0, p(plan), nb, st))
+        ck(lib.msda_backward_ex(p(c["value"]), p(shapes), p(lsi), p(loc), p(aw), p(c["gout"]), p(gv), p(gloc), p(gaw),
+                                *dims, 0, 0, 0, None, 0, p(plan), st))
+        ck(lib.msda_frontend_backward(p(c["off"]), p(aw), p(c["ref"]), p(Tt), p(gloc), p(gaw), p(goff), p(glog), p(gref),
+                                      N, Lq, M, L, P, 1, 0, st))
+
+    def fused(c):
+        ck(lib.msda_module_forward(p(c["value"]), p(shapes), p(lsi), p(c["off"]), p(c["logits"]), p(c["ref"]), p(out),
+                                   *dims, 1, 0, 0, 0, p(plan), nb, st))
+        ck(lib.msda_module_backward(p(c["value"]), p(shapes), p(lsi), p(c["off"]), p(c["logits"]), p(c["ref"]),
+                                    p(c["gout"]), p(gv), p(goff), p(glog), p(gref), *dims, 1, 0, 0, 0, None, 0, p(plan), st))
+
+    res = {}
+    for name, fn in (("two_kernel_path_ms", two_kernel), ("fused_module_op_ms", fused)):
+        ts = []
+        for r in range(reps):
+            for i in range(warmup):
+                fn(sets[i % 2])
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for i in range(steps):
+                fn(sets[i % 2])
+            e1.record()
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1) / steps)
+        res[name] = round(sorted(ts)[len(ts) // 2], 5)
+    res["note"] = ("ENC f32, forward + backward of the module's core (front-end + op), zero-fill of grad_value "
+                   "inside the backward (not overlapped), C ABI calls")
+    return res
+
+
 def secondary_records(args, dev, hbm_peak, dist_sync, ring_enc):
     """SURVEY.md 8(d) lines beside the headline; every entry is timed like the headline
     (CUDA events, inputs rotated over distinct sets unless named l2warm)."""
@@ -445,6 +512,8 @@ def secondary_records(args, dev, hbm_peak, dist_sync, ring_enc):
     for wl in ("MM_VV", "MM_AA", "MM_AV", "MM_VA"):
         rec(wl + "_f32", ring_of(wl, dist="model"))
     rec("CPU_shape_f32(configs[0] on the GPU)", ring_of("CPU", dist="model"))
+    torch.cuda.empty_cache()
+    out["ENC_f32_module_call"] = time_module_call(dev, steps, warmup, reps)
     return out
 
 

@@ -109,27 +109,32 @@ def make_case(name, seed, N, M, D, Lq, P, shapes_hw, dtype, loc_range=(0.0, 1.0)
     print(name, {k: tuple(v.shape) for k, v in rec.items() if k.startswith(("value", "loc"))})
 
 
-def make_module_case(name, seed, rd, with_mask):
+def make_module_case(name, seed, rd, with_mask, encoder=False):
     """The reference's live MSDeformAttn (attention.py:394-511) run on CPU: parameters, inputs,
-    output, the (loc, aw) it returns with is_sparse=True and the gradients of sum(out * g)."""
+    output, the (loc, aw) it returns with is_sparse=True and the gradients of sum(out * g).
+    encoder=True: an encoder-class call (one 64-channel head, 270 tokens attending to themselves
+    with the encoder's reference points) -- the shape class of the fused module op."""
     torch.manual_seed(seed)
-    C, L, M, P = 64, 4, 4, 4
-    T = torch.tensor([24, 12, 6, 3], dtype=torch.long)
+    C, L, M, P = (64, 4, 1, 4) if encoder else (64, 4, 4, 4)
+    T = torch.tensor([144, 72, 36, 18] if encoder else [24, 12, 6, 3], dtype=torch.long)
     lsi = torch.cat((T.new_zeros(1), T.cumsum(0)[:-1]))
-    N, Lq, S = 2, 17, int(T.sum())
+    N, Lq, S = (1, int(T.sum()), int(T.sum())) if encoder else (2, 17, int(T.sum()))
     mod = ref_live.MSDeformAttn(C, L, M, P)
     with torch.no_grad():
         mod.sampling_offsets.weight.normal_(0, 0.05)     # otherwise the offsets do not depend on the query
     q = torch.randn(N, Lq, C, requires_grad=True)
     src = torch.randn(N, S, C, requires_grad=True)
-    ref = torch.rand(N, Lq, L, rd)
+    if encoder:
+        ref = torch.cat([(torch.arange(int(t)) + 0.5) / int(t) for t in T])[None, :, None, None].expand(N, -1, L, 1).clone()
+    else:
+        ref = torch.rand(N, Lq, L, rd)
     if rd == 2:
         ref[..., 1] = ref[..., 1] * 0.5 + 0.05
     ref.requires_grad_(True)
     mask = None
     if with_mask:
         mask = torch.zeros(N, S, dtype=torch.bool)
-        mask[1, -9:] = True
+        mask[N - 1, -9:] = True
     out, loc, aw = mod(q, ref, src, T, lsi, mask, is_sparse=True)
     g = torch.randn_like(out)
     (out * g).sum().backward()
@@ -179,6 +184,7 @@ def main():
     make_refpoints_case("refpoints_f32", 61)
     make_module_case("module_live_ref1_f32", 41, 1, True)
     make_module_case("module_live_ref2_f32", 42, 2, False)
+    make_module_case("module_live_enc_f32", 43, 1, True, encoder=True)
     make_dam_case("dam_f32", 51)
     # models/ops/test.py:17-44 (the only shapes/seeds the reference's tests fix)
     make_case("testpy_tiny_f64", 3, 1, 2, 2, 2, 2, [(6, 4), (3, 2)], torch.float64)
