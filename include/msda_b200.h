@@ -299,6 +299,23 @@ int msda_encoder_reference_points(const int64_t* level_sizes, const float* valid
                                   float* out, int64_t N, int64_t S, int64_t L, void* stream);
 
 /*
+ * prepare_encoder_inputs (models/deformable/unimodal_deformable_transformer.py:90-134 and its copies
+ * in the multimodal and sparse transformers; SURVEY.md section 8(f) row 4, second half): the per-level
+ * transposes, the level-embedding add, the three concatenations and the valid ratios in two launches.
+ *   srcs[l], pos_embeds[l]  [B, C, T_l]  (HOST arrays of L device pointers)    masks[l] [B, T_l] bool
+ *   level_sizes_host [L] int64 in HOST memory (the T_l are tensor shapes: no device round trip)
+ *   level_embed [L, C]
+ *   -> src_flatten, lvl_pos_embed_flatten [B, S, C] (pos + level_embed[l]), mask_flatten [B, S] bool,
+ *      valid_ratios [B, L] float32 = (tokens of the level that are not padding) / T_l
+ */
+int msda_prepare_encoder_inputs(const void* const* srcs, const void* const* pos_embeds,
+                                const unsigned char* const* masks, const int64_t* level_sizes_host,
+                                const void* level_embed, void* src_flatten,
+                                void* lvl_pos_embed_flatten, unsigned char* mask_flatten,
+                                float* valid_ratios, int64_t B, int64_t C, int64_t L, int dtype,
+                                void* stream);
+
+/*
  * Token gather / scatter of the sparse encoders (SURVEY.md section 8(f) row 3;
  * models/sparse/unimodal_sparse_deformable_transformer.py:425-431 torch.gather over an index
  * repeated along the channels, :443-448 one `output[i].scatter(...)` per batch item in a Python

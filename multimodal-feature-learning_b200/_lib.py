@@ -50,6 +50,7 @@ EXPORTED_SYMBOLS = (
     "msda_frontend_backward",
     "msda_dam_scatter",
     "msda_encoder_reference_points",
+    "msda_prepare_encoder_inputs",
     "msda_token_gather",
     "msda_token_scatter",
     "msda_last_cuda_error",
@@ -113,6 +114,8 @@ def _declare(lib):
     lib.msda_frontend_backward.argtypes = [vp] * 9 + [i64] * 5 + [c.c_int, c.c_int, vp]
     lib.msda_encoder_reference_points.restype = c.c_int
     lib.msda_encoder_reference_points.argtypes = [vp] * 3 + [i64] * 3 + [vp]
+    lib.msda_prepare_encoder_inputs.restype = c.c_int
+    lib.msda_prepare_encoder_inputs.argtypes = [vp] * 9 + [i64] * 3 + [c.c_int, vp]
     lib.msda_token_gather.restype = c.c_int
     lib.msda_token_gather.argtypes = [vp] * 4 + [i64] * 4 + [vp]
     lib.msda_token_scatter.restype = c.c_int

@@ -13,6 +13,7 @@
 #include "msda_frontend.cuh"
 #include "msda_generic.cuh"
 #include "msda_plan.cuh"
+#include "msda_prepare.cuh"
 #include "msda_sparse.cuh"
 #include "msda_tile.cuh"
 #include "msda_win.cuh"
@@ -1155,6 +1156,46 @@ int msda_token_scatter(const void* base, const int64_t* idx, const int64_t* nums
   return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
 }
 
+
+int msda_prepare_encoder_inputs(const void* const* srcs, const void* const* pos_embeds,
+                                const unsigned char* const* masks, const int64_t* level_sizes_host,
+                                const void* level_embed, void* src_flatten, void* lvl_pos_embed_flatten,
+                                unsigned char* mask_flatten, float* valid_ratios, int64_t B, int64_t C,
+                                int64_t L, int dtype, void* stream) {
+  if (B < 0 || C <= 0 || L <= 0 || L > kPrepMaxL) return MSDA_ERR_BAD_SHAPE;
+  if (dtype != MSDA_F32 && dtype != MSDA_F64 && dtype != MSDA_BF16) return MSDA_ERR_BAD_DTYPE;
+  if (!srcs || !pos_embeds || !masks || !level_sizes_host) return MSDA_ERR_NULL_POINTER;
+  PrepLevels lv;
+  lv.L = (int)L;
+  int64_t S = 0;
+  int tiles = 0;
+  for (int l = 0; l < (int)L; ++l) {
+    const int64_t Tl = level_sizes_host[l];
+    if (Tl < 0 || S + Tl >= (int64_t(1) << 31)) return MSDA_ERR_TOO_LARGE;
+    if (Tl > 0 && B > 0 && (!srcs[l] || !pos_embeds[l] || !masks[l])) return MSDA_ERR_NULL_POINTER;
+    lv.src[l] = srcs[l]; lv.pos[l] = pos_embeds[l]; lv.mask[l] = masks[l];
+    lv.T[l] = (int)Tl; lv.start[l] = (int)S; lv.tile0[l] = tiles;
+    S += Tl;
+    tiles += (int)((Tl + 31) / 32);
+  }
+  lv.tile0[L] = tiles;
+  if (B == 0 || S == 0) return MSDA_OK;
+  if (!level_embed || !src_flatten || !lvl_pos_embed_flatten || !mask_flatten || !valid_ratios)
+    return MSDA_ERR_NULL_POINTER;
+  if (B > 65535 || (C + 31) / 32 > 65535) return MSDA_ERR_TOO_LARGE;
+  cudaStream_t st = (cudaStream_t)stream;
+  const dim3 grid((unsigned)tiles, (unsigned)((C + 31) / 32), (unsigned)B);
+#define MSDA_PREP(T_)                                                                                   \
+  msda_prepare_encoder_kernel<T_><<<grid, 256, 0, st>>>(lv, (const T_*)level_embed, (T_*)src_flatten, \
+                                                        (T_*)lvl_pos_embed_flatten, mask_flatten, (int)B, (int)C, (int)S)
+  if (dtype == MSDA_F32) MSDA_PREP(float);
+  else if (dtype == MSDA_F64) MSDA_PREP(double);
+  else MSDA_PREP(__nv_bfloat16);
+#undef MSDA_PREP
+  msda_valid_ratio_kernel<<<dim3((unsigned)L, (unsigned)B), 32, 0, st>>>(lv, valid_ratios, (int)B);
+  const cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? MSDA_OK : cuda_fail(e);
+}
 
 int msda_encoder_reference_points(const int64_t* level_sizes, const float* valid_ratios, float* out,
                                   int64_t N, int64_t S, int64_t L, void* stream) {
