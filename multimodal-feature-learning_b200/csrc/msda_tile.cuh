@@ -679,6 +679,35 @@ __device__ __forceinline__ bool tile_setup(const int64_t* __restrict__ shapes,
   return win_stage_levels(shapes, lsi, d.L, s_lvl);   // one barrier
 }
 
+// L2 prefetch of the points of the tile that will run ~2 waves later (tile index + kTileAhead): its
+// CTA then finds its query list and its sampling points (or raw offsets / logits) in L2 instead of
+// HBM -- the two dependent HBM round trips at the head of every tile CTA's life.
+// Threads 64..127 of the CTA, after the grid-dependency wait (the permutation is final).
+#ifndef MSDA_TILE_AHEAD
+#define MSDA_TILE_AHEAD 1184
+#endif
+template <typename T>
+__device__ __forceinline__ void tile_prefetch_ahead(const int* __restrict__ perm, const T* loc, const T* aw,
+                                                    const TileFront<T>* front, const Dims& d, int nchunks) {
+  if (MSDA_TILE_AHEAD <= 0) return;
+  const int t = (int)threadIdx.x - 64;
+  if (t < 0 || t >= kTileQ) return;
+  const long long ft = (long long)blockIdx.x + MSDA_TILE_AHEAD;
+  if (ft >= (long long)gridDim.x) return;
+  const int fm = (int)(ft % d.M);
+  const long long f2 = ft / d.M;
+  const int fchunk = (int)(f2 % nchunks), fb = (int)(f2 / nchunks);
+  const int pos = fchunk * kTileQ + t;
+  if (pos >= d.Lq) return;
+  const int q = perm[(size_t)fb * d.Lq + pos];
+  const size_t grp = ((size_t)fb * d.Lq + q) * d.M + fm;
+  const int LP = d.L * kWinP;
+  const T* p0 = front && front->off ? front->off + grp * LP : loc + grp * LP * 2;
+  const T* p1 = front && front->off ? front->logits + grp * LP : aw + grp * LP;
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p0));
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p1));
+}
+
 // The per-tap bodies as out-of-line functions: they are the rare path and must not shape the
 // register allocation of the tile path.
 template <typename T, int NU, int NT>
@@ -767,7 +796,10 @@ struct TileSmem {
   static constexpr int kRowBytes = NU * 8 * 16;                        // D * sizeof(T)
   static constexpr int kValueBytes = kTileCapRows * kRowBytes;
   static constexpr int kPlanBytes = kTileBlocks * kTileBlkRows * 16;
-  static constexpr int kBytes = kValueBytes + kPlanBytes + 128;         // + alignment slack
+#ifndef MSDA_TILE_SMEM_PAD
+#define MSDA_TILE_SMEM_PAD 0      // experiment knob: extra bytes per CTA, to cap the CTAs per SM
+#endif
+  static constexpr int kBytes = kValueBytes + kPlanBytes + 128 + MSDA_TILE_SMEM_PAD;
 };
 
 // ------------------------------- forward ------------------------------------
@@ -799,6 +831,7 @@ msda_fwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
   tile_stamp(0);
   const bool one_d = tile_setup(shapes, lsi, perm, d, b, chunk, s_lvl, s_win, s_q, &s_mbar);
   tile_stamp(1);
+  tile_prefetch_ahead<T>(perm, loc, aw, FUSED ? &front : nullptr, d, nchunks);
   if (!one_d) {
     if (FUSED) __trap();   // the module's maps are (1, T_l): precondition of the fused entry points
     tile_fallback_fwd<T, NU, 4>(value, loc, aw, out, d, b, m, s_lvl, s_plan, s_q);
@@ -907,6 +940,7 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
   const int t2 = blockIdx.x / d.M;
   const int chunk = t2 % nchunks, b = t2 / nchunks;
   const bool one_d = tile_setup(shapes, lsi, perm, d, b, chunk, s_lvl, s_win, s_q, &s_mbar);
+  tile_prefetch_ahead<T>(perm, loc, aw, FUSED ? &front : nullptr, d, nchunks);
   if (!one_d) {
     if (FUSED) __trap();
     tile_fallback_bwd<T, NU, 4, GV, U>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, s_lvl, s_plan,
