@@ -21,6 +21,7 @@ def test_train_step_runs(extra):
     line = [l for l in res.stdout.splitlines() if l.startswith("{")][-1]
     rec = json.loads(line)
     assert rec["n_gpus"] == 1 and rec["value"] > 0 and rec["loss"] == rec["loss"]      # finite, not NaN
-    # 1 encoder + 1 decoder layer: 2 op forwards + 2 backwards (+ as many front-end launches when fused),
-    # + the query-order pre-pass of the encoder's forward (its backward reuses the plan)
-    assert rec["op_launches_per_step"] == (5 if "--torch-frontend" in extra else 9)
+    # 1 encoder + 1 decoder layer.  Default: the encoder layer runs the fused module op (query-order
+    # pre-pass + forward, backward reusing the plan: 3 launches), the decoder layer the front-end kernel +
+    # op, both ways (4).  --torch-frontend: 2 op forwards + 2 backwards + the encoder's pre-pass.
+    assert rec["op_launches_per_step"] == (5 if "--torch-frontend" in extra else 7)
