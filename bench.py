@@ -448,9 +448,9 @@ def time_module_call(dev, steps, warmup, reps):
                                       N, Lq, M, L, P, 1, 0, st))
 
     def fused(c):
-        ck(lib.msda_module_forward(p(c["value"]), p(shapes), p(lsi), p(c["off"]), p(c["logits"]), p(c["ref"]), p(out),
+        ck(lib.msda_module_forward(p(c["value"]), p(shapes), p(lsi), p(c["off"]), p(c["logits"]), p(c["ref"]), None, p(out),
                                    *dims, 1, 0, 0, 0, p(plan), nb, st))
-        ck(lib.msda_module_backward(p(c["value"]), p(shapes), p(lsi), p(c["off"]), p(c["logits"]), p(c["ref"]),
+        ck(lib.msda_module_backward(p(c["value"]), p(shapes), p(lsi), p(c["off"]), p(c["logits"]), p(c["ref"]), None,
                                     p(c["gout"]), p(gv), p(goff), p(glog), p(gref), *dims, 1, 0, 0, 0, None, 0, p(plan), st))
 
     res = {}

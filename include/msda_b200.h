@@ -251,6 +251,9 @@ int msda_frontend_backward(const void* offsets, const void* aw, const void* ref,
  * points, zero-filled inside; may be NULL) grad_ref directly.  `workspace` of the forward:
  * msda_forward_workspace_bytes(..., flags) bytes, which is the `plan` the backward needs;
  * `workspace` of the backward: msda_backward_workspace_bytes (bf16 image) or NULL for f32.
+ * padding_mask [N, S] bool (true = padding; may be NULL): value.masked_fill(mask, 0) of
+ * ms_deform_attn.py:96-97 without the pass over value -- masked rows are zeroed in the shared-memory
+ * tile as they land, and receive no gradient.
  * msda_module_supported() != 0 <=> the pair accepts the shape; otherwise they return
  * MSDA_ERR_UNSUPPORTED without enqueueing anything.  spatial_shapes must hold H_l = 1.
  */
@@ -258,13 +261,14 @@ int msda_module_supported(int64_t N, int64_t S, int64_t M, int64_t D, int64_t L,
                           int64_t P, int ref_dim, int dtype, unsigned flags);
 int msda_module_forward(const void* value, const int64_t* spatial_shapes,
                         const int64_t* level_start_index, const void* offsets, const void* logits,
-                        const void* ref, void* output,
+                        const void* ref, const unsigned char* padding_mask, void* output,
                         int64_t N, int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq, int64_t P,
                         int ref_dim, int dtype, int padding, unsigned flags,
                         void* workspace, size_t workspace_bytes, void* stream);
 int msda_module_backward(const void* value, const int64_t* spatial_shapes,
                          const int64_t* level_start_index, const void* offsets, const void* logits,
-                         const void* ref, const void* grad_output, void* grad_value,
+                         const void* ref, const unsigned char* padding_mask,
+                         const void* grad_output, void* grad_value,
                          void* grad_offsets, void* grad_logits, float* grad_ref,
                          int64_t N, int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq, int64_t P,
                          int ref_dim, int dtype, int padding, unsigned flags,

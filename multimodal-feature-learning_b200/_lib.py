@@ -104,9 +104,9 @@ def _declare(lib):
     lib.msda_module_supported.restype = c.c_int
     lib.msda_module_supported.argtypes = [i64] * 7 + [c.c_int, c.c_int, u32]
     lib.msda_module_forward.restype = c.c_int
-    lib.msda_module_forward.argtypes = ([vp] * 7 + [i64] * 7 + [c.c_int, c.c_int, c.c_int, u32, vp, c.c_size_t, vp])
+    lib.msda_module_forward.argtypes = ([vp] * 8 + [i64] * 7 + [c.c_int, c.c_int, c.c_int, u32, vp, c.c_size_t, vp])
     lib.msda_module_backward.restype = c.c_int
-    lib.msda_module_backward.argtypes = ([vp] * 11 + [i64] * 7 + [c.c_int, c.c_int, c.c_int, u32, vp, c.c_size_t,
+    lib.msda_module_backward.argtypes = ([vp] * 12 + [i64] * 7 + [c.c_int, c.c_int, c.c_int, u32, vp, c.c_size_t,
                                                                  vp, vp])
     lib.msda_frontend_forward.restype = c.c_int
     lib.msda_frontend_forward.argtypes = [vp] * 6 + [i64] * 5 + [c.c_int, c.c_int, vp]

@@ -987,10 +987,10 @@ int msda_dam_scatter(const void* loc, const void* aw, const int64_t* level_sizes
 namespace {
 template <typename T>
 TileFront<T> make_front(const void* off, const void* logits, const void* ref, void* g_off, void* g_logits,
-                        float* g_ref, int ref_dim) {
+                        float* g_ref, int ref_dim, const unsigned char* mask) {
   TileFront<T> f;
   f.off = (const T*)off; f.logits = (const T*)logits; f.ref = (const T*)ref;
-  f.g_off = (T*)g_off; f.g_logits = (T*)g_logits; f.g_ref = g_ref; f.ref_dim = ref_dim;
+  f.g_off = (T*)g_off; f.g_logits = (T*)g_logits; f.g_ref = g_ref; f.ref_dim = ref_dim; f.mask = mask;
   return f;
 }
 inline bool module_supported(const Dims& d, int64_t S, int64_t M, int64_t D, int64_t L, int dtype, int ref_dim,
@@ -1014,7 +1014,8 @@ int msda_module_supported(int64_t N, int64_t S, int64_t M, int64_t D, int64_t L,
 }
 
 int msda_module_forward(const void* value, const int64_t* spatial_shapes, const int64_t* level_start_index,
-                        const void* offsets, const void* logits, const void* ref, void* output, int64_t N,
+                        const void* offsets, const void* logits, const void* ref,
+                        const unsigned char* padding_mask, void* output, int64_t N,
                         int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq, int64_t P, int ref_dim,
                         int dtype, int padding, unsigned flags, void* workspace, size_t workspace_bytes,
                         void* stream) {
@@ -1038,11 +1039,12 @@ int msda_module_forward(const void* value, const int64_t* spatial_shapes, const 
     r = launch_fwd_tile<__nv_bfloat16, 1, true>(value, spatial_shapes, level_start_index, nullptr, nullptr, perm,
                                                 output, d, dtype, st, true,
                                                 make_front<__nv_bfloat16>(offsets, logits, ref, nullptr, nullptr,
-                                                                          nullptr, ref_dim));
+                                                                          nullptr, ref_dim, padding_mask));
   } else {
     const SortSrc<float> src = {nullptr, (const float*)offsets, (const float*)ref, spatial_shapes, ref_dim};
     if ((r = launch_sort<float>(src, perm, d, st)) != MSDA_OK) return r;
-    const TileFront<float> f = make_front<float>(offsets, logits, ref, nullptr, nullptr, nullptr, ref_dim);
+    const TileFront<float> f = make_front<float>(offsets, logits, ref, nullptr, nullptr, nullptr, ref_dim,
+                                                 padding_mask);
     r = D == 64 ? launch_fwd_tile<float, 2, true>(value, spatial_shapes, level_start_index, nullptr, nullptr, perm,
                                                   output, d, dtype, st, true, f)
                 : launch_fwd_tile<float, 1, true>(value, spatial_shapes, level_start_index, nullptr, nullptr, perm,
@@ -1052,8 +1054,8 @@ int msda_module_forward(const void* value, const int64_t* spatial_shapes, const 
 }
 
 int msda_module_backward(const void* value, const int64_t* spatial_shapes, const int64_t* level_start_index,
-                         const void* offsets, const void* logits, const void* ref, const void* grad_output,
-                         void* grad_value, void* grad_offsets, void* grad_logits, float* grad_ref, int64_t N,
+                         const void* offsets, const void* logits, const void* ref,
+                         const unsigned char* padding_mask, const void* grad_output, void* grad_value, void* grad_offsets, void* grad_logits, float* grad_ref, int64_t N,
                          int64_t S, int64_t M, int64_t D, int64_t L, int64_t Lq, int64_t P, int ref_dim,
                          int dtype, int padding, unsigned flags, void* workspace, size_t workspace_bytes,
                          const void* plan, void* stream) {
@@ -1086,9 +1088,10 @@ int msda_module_backward(const void* value, const int64_t* spatial_shapes, const
     r = launch_bwd_tile<__nv_bfloat16, 2, float, UnitBf16x4, true>(
         value, spatial_shapes, level_start_index, nullptr, nullptr, grad_output, perm, (float*)acc, nullptr,
         nullptr, d, dtype, st, nullptr, false,
-        make_front<__nv_bfloat16>(offsets, logits, ref, grad_offsets, grad_logits, grad_ref, ref_dim));
+        make_front<__nv_bfloat16>(offsets, logits, ref, grad_offsets, grad_logits, grad_ref, ref_dim, padding_mask));
   } else {
-    const TileFront<float> f = make_front<float>(offsets, logits, ref, grad_offsets, grad_logits, grad_ref, ref_dim);
+    const TileFront<float> f = make_front<float>(offsets, logits, ref, grad_offsets, grad_logits, grad_ref, ref_dim,
+                                                 padding_mask);
     r = D == 64 ? launch_bwd_tile<float, 2, float, Unit<float>, true>(
                       value, spatial_shapes, level_start_index, nullptr, nullptr, grad_output, perm, (float*)acc,
                       nullptr, nullptr, d, dtype, st, nullptr, false, f)

@@ -295,7 +295,8 @@ __device__ __forceinline__ void owner_point(const T* __restrict__ loc_g, const T
                                             int pt, int LP, int P, int MD, bool border,
                                             const int* s_lvl, TapMeta<NT>& tm, float (&cw)[NT],
                                             float (&cx)[NT], float (&cy)[NT],
-                                            const float* lpts = nullptr) {
+                                            const float* lpts = nullptr,
+                                            const unsigned char* mrow = nullptr) {
 #pragma unroll
   for (int k = 0; k < NT; ++k) { tm.off[k] = -1; tm.w[k] = 0.f; cw[k] = cx[k] = cy[k] = 0.f; }
   if (pt >= LP) return;
@@ -317,8 +318,11 @@ __device__ __forceinline__ void owner_point(const T* __restrict__ loc_g, const T
     const int k2 = (k + 2) & 3;
     const int row = alt ? g.off[k2] : g.off[k];
     const float wk = alt ? g.w[k2] : g.w[k];
-    tm.off[k] = row >= 0 ? row * MD : -1;
-    tm.w[k] = row >= 0 ? wk * a : 0.f;
+    // mrow: padding mask of the batch item (fused module op): a masked row counts as zeros, i.e. is
+    // neither read nor given a gradient (value.masked_fill(mask, 0), ms_deform_attn.py:96-97)
+    const bool ok = row >= 0 && !(mrow && mrow[row >= 0 ? row : 0]);
+    tm.off[k] = ok ? row * MD : -1;
+    tm.w[k] = ok ? wk * a : 0.f;
     if (BWD) {
       cw[k] = wk;
       cx[k] = (alt ? dx[k2] : dx[k]) * g.sx * a;
@@ -333,7 +337,8 @@ __device__ __forceinline__ void fwd_body(const T* __restrict__ value, const T* _
                                          const T* __restrict__ aw, T* __restrict__ out,
                                          const Dims& d, int b, int m, int q_first, int q_end,
                                          int q_step, const int* s_lvl, TapMeta<NT>* s_meta,
-                                         const int* qlist = nullptr, const float* lpts = nullptr) {
+                                         const int* qlist = nullptr, const float* lpts = nullptr,
+                                         const unsigned char* mrow = nullptr) {
   // the group handles queries q_first, q_first + q_step, ... < q_end of (b, m) -- or, with a
   // query list (the time-sorted tiles of msda_tile.cuh), the queries qlist[q_first], ...,
   // negative entries skipped; s_meta = G entries private to the group
@@ -362,7 +367,7 @@ __device__ __forceinline__ void fwd_body(const T* __restrict__ value, const T* _
         TapMeta<NT> tm;
         float cw[NT], cx[NT], cy[NT];
         owner_point<T, NT, false>(loc_g, aw_g, base + j, LP, d.P, MD, d.border != 0, s_lvl, tm, cw,
-                                  cx, cy, lpts ? lpts + (size_t)qq * LP * 3 : nullptr);
+                                  cx, cy, lpts ? lpts + (size_t)qq * LP * 3 : nullptr, mrow);
         s_meta[j] = tm;
       }
       __syncwarp(mask);
@@ -436,7 +441,7 @@ __device__ __forceinline__ void bwd_body(const T* __restrict__ value, const T* _
                                          int q_first, int q_end, int q_step, const int* s_lvl,
                                          TapMeta<NT>* s_meta, float gv_scale = 1.f,
                                          const int* qlist = nullptr, const float* lpts = nullptr,
-                                         float* lgrad = nullptr) {
+                                         float* lgrad = nullptr, const unsigned char* mrow = nullptr) {
   constexpr int E = U::E;
   const int lane = threadIdx.x & 31;
   const int j = threadIdx.x % G;
@@ -463,7 +468,7 @@ __device__ __forceinline__ void bwd_body(const T* __restrict__ value, const T* _
       {
         TapMeta<NT> tm;
         owner_point<T, NT, true>(loc_g, aw_g, pt, LP, d.P, MD, d.border != 0, s_lvl, tm, cw, cx, cy,
-                                 lpts ? lpts + (size_t)qq * LP * 3 : nullptr);
+                                 lpts ? lpts + (size_t)qq * LP * 3 : nullptr, mrow);
         s_meta[j] = tm;
       }
       __syncwarp(mask);

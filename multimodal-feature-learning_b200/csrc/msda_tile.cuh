@@ -418,8 +418,33 @@ struct TileFront {
   T* g_off;            // backward outputs
   T* g_logits;
   float* g_ref;        // [N, Lq, L, ref_dim] fp32, zeroed by the host side (nullptr: not wanted)
+  const unsigned char* mask;   // [N, S] bool, true = padding row of value (nullptr: none): the row counts
+                               // as zeros and gets no gradient (value.masked_fill, ms_deform_attn.py:96-97)
   int ref_dim;
 };
+
+// Padding mask on the value tile: flag the tile's rows, zero the masked ones (after the boxes have
+// landed).  All threads; ends with a barrier.
+template <int ROW_BYTES>
+__device__ __forceinline__ void tile_apply_mask(const unsigned char* mrow, int S, const int (&tlo)[kWinMaxL],
+                                                const int (&tbase)[kWinMaxL], int total, char* vtile,
+                                                unsigned char* s_rowmask) {
+  for (int t = threadIdx.x; t < total; t += kTileThreads) {
+    int l = 0;
+#pragma unroll
+    for (int k = 1; k < kWinMaxL; ++k)
+      if (t >= tbase[k]) l = k;
+    const int slab = tlo[l] + (t - tbase[l]);
+    const bool mk = slab >= 0 && slab < S && mrow[slab] != 0;
+    s_rowmask[t] = mk ? 1 : 0;
+    if (mk) {
+      uint4* r = reinterpret_cast<uint4*>(vtile + (size_t)t * ROW_BYTES);
+#pragma unroll
+      for (int k = 0; k < ROW_BYTES / 16; ++k) r[k] = make_uint4(0, 0, 0, 0);
+    }
+  }
+  __syncthreads();
+}
 
 template <typename T> struct Front4;       // 4 consecutive elements <-> 4 floats
 template <> struct Front4<float> {
@@ -713,21 +738,22 @@ __device__ __forceinline__ void tile_prefetch_ahead(const int* __restrict__ perm
 template <typename T, int NU, int NT>
 __device__ __noinline__ void tile_fallback_fwd(const T* value, const T* loc, const T* aw, T* out, Dims d,
                                                int b, int m, const int* s_lvl, char* scratch,
-                                               const int* s_q, const float* lpts = nullptr) {
+                                               const int* s_q, const float* lpts = nullptr,
+                                               const unsigned char* mrow = nullptr) {
   const int g = threadIdx.x >> 3;
   fwd_body<T, NU, 8, NT>(value, loc, aw, out, d, b, m, g, kTileQ, kTileBlocks, s_lvl,
-                         reinterpret_cast<TapMeta<NT>*>(scratch) + g * 8, s_q, lpts);
+                         reinterpret_cast<TapMeta<NT>*>(scratch) + g * 8, s_q, lpts, mrow);
 }
 template <typename T, int NU, int NT, typename GV, typename U>
 __device__ __noinline__ void tile_fallback_bwd(const T* value, const T* loc, const T* aw, const T* gout,
                                                GV* gvalue, T* gloc, T* gaw, Dims d, int b, int m,
                                                const int* s_lvl, char* scratch, float gv_scale,
                                                const int* s_q, const float* lpts = nullptr,
-                                               float* lgrad = nullptr) {
+                                               float* lgrad = nullptr, const unsigned char* mrow = nullptr) {
   const int g = threadIdx.x >> 3;
   bwd_body<T, NU, 8, NT, GV, U>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, g, kTileQ, kTileBlocks,
                                 s_lvl, reinterpret_cast<TapMeta<NT>*>(scratch) + g * 8, gv_scale, s_q, lpts,
-                                lgrad);
+                                lgrad, mrow);
 }
 
 // Fused front-end, tile without a plan: the thread's points (x, y, weight) as floats into shared
@@ -845,7 +871,8 @@ msda_fwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
     if (FUSED) {
       float* lp = reinterpret_cast<float*>(vtile);
       tile_front_stash<T>(front, d, b, m, s_q[g * kWinQ + (j & 3)], s_lvl, lp);
-      tile_fallback_fwd<T, NU, 2>(value, loc, aw, out, d, b, m, s_lvl, s_plan + SM::kPlanBytes - 4096, s_q, lp);
+      tile_fallback_fwd<T, NU, 2>(value, loc, aw, out, d, b, m, s_lvl, s_plan + SM::kPlanBytes - 4096, s_q, lp,
+                                  front.mask ? front.mask + (size_t)b * d.S : nullptr);
     } else {
       tile_fallback_fwd<T, NU, 2>(value, loc, aw, out, d, b, m, s_lvl, s_plan, s_q);
     }
@@ -854,6 +881,10 @@ msda_fwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
   tile_stamp(4);
   if (pl.total > 0) tile_mbar_wait(&s_mbar, 0);
   tile_stamp(5);
+  if (FUSED && front.mask) {
+    __shared__ unsigned char s_rowmask[kTileCapRows];
+    tile_apply_mask<RB>(front.mask + (size_t)b * d.S, d.S, pl.tlo, pl.tbase, pl.total, vtile, s_rowmask);
+  }
 
   float2 acc[kWinQ][NU][E / 2];
 #pragma unroll
@@ -981,7 +1012,8 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
       float* lg = lp + kTileQ * LPf * 3;
       tile_front_stash<T>(front, d, b, m, my_q, s_lvl, lp);
       tile_fallback_bwd<T, NU, 2, GV, U>(value, loc, aw, gout, gvalue, gloc, gaw, d, b, m, s_lvl,
-                                         s_plan + kTileBlocks * kTileBlkRows * 16 - 4096, gv_scale, s_q, lp, lg);
+                                         s_plan + kTileBlocks * kTileBlkRows * 16 - 4096, gv_scale, s_q, lp, lg,
+                                         front.mask ? front.mask + (size_t)b * d.S : nullptr);
       __syncthreads();
       float x[2][4], y[2][4], a[2][4], off[2][4], sc[2], gxx[2][4], gaa[2][4];
       const int qs = my_q >= 0 ? my_q : 0;
@@ -1014,6 +1046,10 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
       for (int c = 0; c < E / 2; ++c) go[q][uu][c] = make_float2(t[2 * c], t[2 * c + 1]);
     }
   if (pl.total > 0) tile_mbar_wait(&s_mbar, 0);
+  __shared__ unsigned char s_rowmask[FUSED ? kTileCapRows : 1];
+  const bool has_mask = FUSED && front.mask != nullptr;
+  if (has_mask)
+    tile_apply_mask<RB>(front.mask + (size_t)b * d.S, d.S, pl.tlo, pl.tbase, pl.total, vtile, s_rowmask);
 
   const int MD = d.M * d.D;
   GV* gvb = gvalue + ((size_t)b * d.S * d.M + m) * d.D + j * E;
@@ -1032,7 +1068,7 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
       for (int r = 0; r < 2; ++r) {
         const float4 w = wl[i + r];
         const float wq[kWinQ] = {w.x, w.y, w.z, w.w};
-        const bool real = i + r < nb;
+        const bool real = i + r < nb && !(has_mask && s_rowmask[pl.trow[l] + i + r]);
         float2 s[kWinQ];
 #pragma unroll
         for (int u = 0; u < NU; ++u) {

@@ -31,13 +31,17 @@ def supported(value, offsets, reference_points, flags=0):
 
 class MSDeformModuleFunction(Function):
     @staticmethod
-    def forward(ctx, value, shapes_hw, lsi, offsets, logits, ref, padding_mode):
+    def forward(ctx, value, shapes_hw, lsi, offsets, logits, ref, padding_mode, mask=None):
         N, S, M, D = value.shape
         _, Lq, _, L, P = offsets.shape
         rd = ref.shape[-1]
         dt = _DTYPES[value.dtype]
         value, offsets, logits = value.contiguous(), offsets.contiguous(), logits.contiguous()
         ref_c = ref.to(value.dtype).contiguous()
+        if mask is not None:
+            if mask.dtype != torch.bool or tuple(mask.shape) != (N, S):
+                raise RuntimeError("padding mask must be a bool [N, S] tensor")
+            mask = mask.contiguous()
         lib = _lib.load()
         ctx.msda_gv = None
         with torch.cuda.device_of(value):
@@ -57,16 +61,19 @@ class MSDeformModuleFunction(Function):
             plan = torch.empty(max(ws_bytes // 4, 1), dtype=torch.int32, device=value.device)
             _lib.check(lib.msda_module_forward(
                 value.data_ptr(), shapes_hw.data_ptr(), lsi.data_ptr(), offsets.data_ptr(), logits.data_ptr(),
-                ref_c.data_ptr(), out.data_ptr(), N, S, M, D, L, Lq, P, rd, dt,
+                ref_c.data_ptr(), mask.data_ptr() if mask is not None else None, out.data_ptr(),
+                N, S, M, D, L, Lq, P, rd, dt,
                 _lib.PADDING_MODES[padding_mode], 0, plan.data_ptr(), ws_bytes, _stream(value)))
-        ctx.save_for_backward(value, shapes_hw, lsi, offsets, logits, ref_c, plan)
+        ctx.save_for_backward(value, shapes_hw, lsi, offsets, logits, ref_c, plan,
+                              mask if mask is not None else plan.new_empty(0))
+        ctx.has_mask = mask is not None
         ctx.padding_mode, ctx.logits_shape, ctx.ref_dtype = padding_mode, logits.shape, ref.dtype
         return out
 
     @staticmethod
     @once_differentiable
     def backward(ctx, grad_out):
-        value, shapes_hw, lsi, offsets, logits, ref, plan = ctx.saved_tensors
+        value, shapes_hw, lsi, offsets, logits, ref, plan, mask = ctx.saved_tensors
         N, S, M, D = value.shape
         _, Lq, _, L, P = offsets.shape
         rd = ref.shape[-1]
@@ -91,7 +98,8 @@ class MSDeformModuleFunction(Function):
                 ws = torch.empty(ws_bytes // 4, dtype=torch.float32, device=value.device)
             _lib.check(lib.msda_module_backward(
                 value.data_ptr(), shapes_hw.data_ptr(), lsi.data_ptr(), offsets.data_ptr(), logits.data_ptr(),
-                ref.data_ptr(), grad_out.contiguous().data_ptr(), gv.data_ptr(), g_off.data_ptr(), g_lg.data_ptr(),
+                ref.data_ptr(), mask.data_ptr() if ctx.has_mask else None, grad_out.contiguous().data_ptr(),
+                gv.data_ptr(), g_off.data_ptr(), g_lg.data_ptr(),
                 g_ref.data_ptr() if g_ref is not None else None, N, S, M, D, L, Lq, P, rd, dt,
                 _lib.PADDING_MODES[ctx.padding_mode], flags, ws.data_ptr() if ws is not None else None, ws_bytes,
                 plan.data_ptr(), _stream(value)))
@@ -99,10 +107,12 @@ class MSDeformModuleFunction(Function):
                 ws.record_stream(torch.cuda.current_stream(value.device))
         if g_ref is not None:
             g_ref = g_ref.to(ctx.ref_dtype)
-        return gv, None, None, g_off, g_lg.view(ctx.logits_shape), g_ref, None
+        return gv, None, None, g_off, g_lg.view(ctx.logits_shape), g_ref, None, None
 
 
 def msdeform_module(value, shapes_hw, level_start_index, sampling_offsets, attention_logits, reference_points,
-                    padding_mode="zeros"):
+                    padding_mode="zeros", padding_mask=None):
+    """padding_mask [N, S] bool (True = padding): value.masked_fill(mask[..., None], 0) of
+    ms_deform_attn.py:96-97, applied inside the kernels (pass the UNMASKED value)."""
     return MSDeformModuleFunction.apply(value, shapes_hw, level_start_index, sampling_offsets, attention_logits,
-                                        reference_points, padding_mode)
+                                        reference_points, padding_mode, padding_mask)

@@ -142,10 +142,7 @@ class MSDeformAttn(nn.Module):
             self._check_lengths(input_spatial_shapes, Len_in)
         M, L, P = self.n_heads, self.n_levels, self.n_points
 
-        value = self.value_proj(input_flatten)
-        if input_padding_mask is not None:
-            value = value.masked_fill(input_padding_mask[..., None], float(0))
-        value = value.view(N, Len_in, M, self.d_model // M)
+        value = self.value_proj(input_flatten).view(N, Len_in, M, self.d_model // M)
         sampling_offsets = self.sampling_offsets(query).view(N, Len_q, M, L, P)
         logits = self.attention_weights(query).view(N, Len_q, M, L * P)
         if reference_points.shape[-1] not in (1, 2):
@@ -154,10 +151,13 @@ class MSDeformAttn(nn.Module):
         if (self.fused_frontend and self.fused_op and not is_sparse
                 and module_func.supported(value, sampling_offsets, reference_points)):
             # softmax + sampling locations inside the tile kernels: no loc / aw in memory
+            # (the padding mask too: masked rows are zeroed in the kernels' value tile)
             output = module_func.msdeform_module(value, self._shapes_hw(input_spatial_shapes),
                                                  input_level_start_index, sampling_offsets, logits,
-                                                 reference_points, self.padding_mode)
+                                                 reference_points, self.padding_mode, input_padding_mask)
             return self.output_proj(output)
+        if input_padding_mask is not None:
+            value = value.masked_fill(input_padding_mask[..., None, None], float(0))
         if self.fused_frontend:
             loc_xy, attention_weights = msdeform_frontend(sampling_offsets, logits, reference_points,
                                                           input_spatial_shapes)

@@ -84,6 +84,29 @@ def test_fused_module_op_bf16(padding):
         assert rel(g_, w_) <= 2e-2, nm
 
 
+@pytest.mark.parametrize("spread", [0.5, 40.0], ids=["tiles", "per_tap_fallback"])
+def test_fused_module_op_padding_mask(spread):
+    """The padding mask inside the kernels == value.masked_fill(mask, 0) in front of the two-kernel path,
+    including the (zero) gradient of the masked value rows."""
+    c = make(2, [160, 80, 40, 20], 8, 64, torch.float32, 1, seed=35, spread=spread)
+    mask = torch.zeros(2, 300, dtype=torch.bool, device=DEV)
+    mask[0, 120:160] = True
+    mask[1, 20:60] = True
+    mask[1, 290:] = True
+    v, off, lg, ref = (c[k].detach().clone().requires_grad_(True) for k in ("value", "off", "logits", "ref"))
+    out = module_func.msdeform_module(v, c["shapes"], c["lsi"], off, lg, ref, "zeros", mask)
+    out.backward(c["gout"])
+    v2, off2, lg2, ref2 = (c[k].detach().clone().requires_grad_(True) for k in ("value", "off", "logits", "ref"))
+    loc, aw = msdeform_frontend(off2, lg2, ref2, c["T"])
+    want = ms_deform_attn(v2.masked_fill(mask[..., None, None], 0.0), c["shapes"], c["lsi"], loc, aw, 64, "zeros")
+    want.backward(c["gout"])
+    assert float((out - want).abs().max()) <= 2e-5 * float(want.abs().max())
+    assert float(v.grad[mask].abs().max()) == 0.0
+    for g_, w_, nm in ((v.grad, v2.grad, "grad_value"), (off.grad, off2.grad, "grad_offsets"),
+                       (lg.grad, lg2.grad, "grad_logits"), (ref.grad, ref2.grad, "grad_ref")):
+        assert rel(g_, w_) <= 2e-4, nm
+
+
 def test_not_supported_shapes_are_reported():
     c = make(2, [40, 20], 4, 64, torch.float32, 1, seed=33, Lq=37)          # decoder-like: short query list
     assert not module_func.supported(c["value"], c["off"], c["ref"])
