@@ -894,7 +894,9 @@ msda_fwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
 #pragma unroll
       for (int c = 0; c < E / 2; ++c) acc[q][uu][c] = make_float2(0.f, 0.f);
 
-  // warp-uniform row loops: a block past its own rows re-reads its last row against zero weights
+  // warp-uniform row loops: a block past its own rows re-reads its last row against zero weights.
+  // (A hand-pipelined form -- weights and row of step i + 1 requested before the FFMA2 of step i --
+  // measured 2 us slower at ENC: DESIGN.md section 6.)
 #pragma unroll
   for (int l = 0; l < kWinMaxL; ++l) {
     const char* vr = vtile + pl.trow[l] * RB + j * 16;
