@@ -205,3 +205,22 @@ def test_window_default_heuristic_and_determinism():
     o2 = MSDA.ms_deform_attn_forward(*a, 64, flags=_lib.MSDA_FLAG_NO_WINDOW)
     assert torch.equal(o0, o1)
     assert float((o0 - o2).abs().max()) <= 2e-6 and not torch.equal(o0, o2)
+
+
+def test_long_query_list_uses_single_cta_sort():
+    """Lq > 4096: the query order comes from msda_sort_kernel (one CTA per batch item, histogram with
+    atomics) instead of the cluster sort; same results as the per-tap kernels."""
+    T = [2048, 1024, 512, 256]
+    inp = synthetic.make_inputs(1, 5000, 2, 64, 4, [(1, t) for t in T], torch.float32, DEV, seed=23, dist="model",
+                                value="small", enc_ref=False)
+    # reference points monotone in the (shuffled) query index would be too easy: make_inputs draws them at random
+    a = run_cuda(inp, "zeros", WIN)
+    b = run_cuda(inp, "zeros", _lib.MSDA_FLAG_NO_WINDOW)
+    assert np.abs(a[0] - b[0]).max() <= 2e-6
+    m = smooth_mask(inp)
+    for x, y, nm in ((a[1], b[1], "gv"), (a[2] * m, b[2] * m, "gl"), (a[3], b[3], "ga")):
+        assert rel_err(x, y) <= 2e-5, nm
+    out, plan = MSDA.ms_deform_attn_forward(*[inp[k] for k in ("value", "shapes", "lsi", "loc", "aw")], 64, flags=WIN,
+                                            return_plan=True)
+    srt = plan[:5000].sort()[0]
+    assert torch.equal(srt, torch.arange(5000, device=DEV, dtype=torch.int32))

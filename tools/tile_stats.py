@@ -42,6 +42,7 @@ def main():
     key = loc[:, :, :hk, 0, :, 0].mean(axis=(2, 3))
     bins = np.clip(np.floor(key * args.bins), 0, args.bins - 1).astype(np.int64)
     blk_rows, tile_rows, over_tile, over_blk, tiles = [], [], 0, 0, 0
+    warp_rows, warp_rows_even, over_bwd = [], [], 0
     per_level = np.zeros(L)
     for b in range(N):
         perm = np.arange(Lq) if args.nosort else np.argsort(bins[b], kind="stable")
@@ -56,12 +57,24 @@ def main():
             hi = np.minimum(hi, W[None, :] - 1)
             for t0 in range(0, Lq, args.tileq):
                 tiles += 1
+                bad_bwd_warp = False
                 tl, th = lo[t0:t0 + args.tileq], hi[t0:t0 + args.tileq]
                 tlo, thi = tl.min(0), th.max(0)
                 rows = np.where(thi >= tlo, thi - tlo + 1, 0)
                 total = (np.ceil(rows / args.box) * args.box).sum()
                 tile_rows.append(rows.sum())
                 bad = total > args.cap
+                # the kernels lay a warp's 4 blocks out with the warp's largest row count per level
+                # (backward: rounded up to even): that sum is what must fit the block plan
+                for w0 in range(0, len(tl), 16):
+                    wr = np.zeros(L)
+                    for q0 in range(w0, min(w0 + 16, len(tl)), 4):
+                        bl, bh = tl[q0:q0 + 4].min(0), th[q0:q0 + 4].max(0)
+                        wr = np.maximum(wr, np.where(bh >= bl, bh - bl + 1, 0))
+                    warp_rows.append(wr.sum())
+                    warp_rows_even.append((np.ceil(wr / 2) * 2).sum())
+                    if (np.ceil(wr / 2) * 2).sum() > args.blkcap:
+                        bad_bwd_warp = True
                 for q0 in range(0, len(tl), 4):
                     bl, bh = tl[q0:q0 + 4].min(0), th[q0:q0 + 4].max(0)
                     br = np.where(bh >= bl, bh - bl + 1, 0)
@@ -70,6 +83,8 @@ def main():
                     if br.sum() > args.blkcap:
                         bad = True
                         over_blk += 1
+                if bad_bwd_warp or total > args.cap:
+                    over_bwd += 1
                 if bad:
                     over_tile += 1
                     if over_tile <= 6:
@@ -80,6 +95,11 @@ def main():
     print("rows per block: mean %.1f p50 %d p90 %d p99 %d max %d; per level %s" % (
         blk_rows.mean(), np.percentile(blk_rows, 50), np.percentile(blk_rows, 90), np.percentile(blk_rows, 99),
         blk_rows.max(), (per_level / len(blk_rows)).round(1).tolist()))
+    wr, we = np.array(warp_rows), np.array(warp_rows_even)
+    print("plan rows per warp (sum over levels of the largest block): fwd mean %.1f p99 %d max %d; bwd (even) mean %.1f "
+          "p99 %d max %d; tiles the backward sends to the per-tap body: %d (%.1f%%)" % (
+              wr.mean(), np.percentile(wr, 99), wr.max(), we.mean(), np.percentile(we, 99), we.max(), over_bwd,
+              100.0 * over_bwd / tiles))
     print("rows per tile: mean %.1f p90 %d p99 %d max %d" % (tile_rows.mean(), np.percentile(tile_rows, 90),
                                                               np.percentile(tile_rows, 99), tile_rows.max()))
 
