@@ -70,6 +70,9 @@ typedef enum {
   MSDA_ERR_MISALIGNED = -8,     /* a data pointer is not 16-byte aligned */
   MSDA_ERR_UNSUPPORTED = -10,   /* msda_module_*: the call is outside the fused path (nothing was
                                    enqueued); use msda_frontend_* + msda_forward_ex / msda_backward_ex */
+  MSDA_ERR_SCRATCH_LIMIT = -11, /* msda_forward_static: the call needs more scratch than the
+                                   library's built-in MSDA_STATIC_SCRATCH_BYTES (nothing was
+                                   enqueued); use msda_forward_ex with a caller workspace */
   MSDA_ERR_NO_TMA = -9          /* internal: the TMA descriptor could not be encoded; the
                                    entry points fall back to the row-window kernels and
                                    never return it */
@@ -164,6 +167,35 @@ int msda_forward_ex(const void* value, const int64_t* spatial_shapes,
                     int64_t Lq, int64_t P,
                     int dtype, int padding, unsigned flags,
                     void* workspace, size_t workspace_bytes, void* stream);
+
+/*
+ * msda_forward_ex for callers that cannot allocate (code under CUDA graph capture,
+ * serving loops, harnesses that forbid cudaMalloc).  NO counterpart in the reference.
+ * The plan of the CTA-tile kernels (the
+ * time order of the queries, int32 [N][Lq]) goes to a scratch array built into the
+ * library (a file-scope __device__ array of MSDA_STATIC_SCRATCH_BYTES, resident on
+ * every GPU that loads the library until the process exits) instead of a caller
+ * workspace; the call itself allocates nothing (no cudaMalloc / cudaFree, no
+ * allocating library routine).  Same kernels, same results as msda_forward_ex with a
+ * workspace of msda_forward_workspace_bytes().
+ *   - msda_forward_workspace_bytes(..., flags without MSDA_FLAG_PLAN) >
+ *     MSDA_STATIC_SCRATCH_BYTES (N * Lq > 262,144 queries) -> MSDA_ERR_SCRATCH_LIMIT,
+ *     nothing enqueued.  MSDA_FLAG_PLAN is ignored (its plan is 13 KB per tile).
+ *   - a shape class that needs no scratch (per-tap / row-window / any-D kernels) runs
+ *     as msda_forward, which never allocated.
+ *   - ALL calls on a device share the array: two calls that overlap on the GPU
+ *     (different streams, or different host threads on different streams) race on it.
+ *     Calls on one stream are ordered and safe.  The array keeps the last call's
+ *     plan; every call overwrites the [N][Lq] entries it reads before reading them,
+ *     so nothing in it has to start at zero.
+ */
+#define MSDA_STATIC_SCRATCH_BYTES (1u << 20)
+int msda_forward_static(const void* value, const int64_t* spatial_shapes,
+                        const int64_t* level_start_index, const void* sampling_loc,
+                        const void* attn_weight, void* output,
+                        int64_t N, int64_t S, int64_t M, int64_t D, int64_t L,
+                        int64_t Lq, int64_t P,
+                        int dtype, int padding, unsigned flags, void* stream);
 
 /* Bytes of scratch msda_backward takes.  REQUIRED part: nothing for f32/f64, an fp32
  * accumulation image of grad_value for bf16 (the deterministic variant: see the

@@ -39,6 +39,7 @@ EXPORTED_SYMBOLS = (
     "msda_forward",
     "msda_forward_workspace_bytes",
     "msda_forward_ex",
+    "msda_forward_static",
     "msda_backward_workspace_bytes",
     "msda_backward_workspace_bytes_flags",
     "msda_backward",
@@ -89,6 +90,8 @@ def _declare(lib):
     lib.msda_forward_ex.restype = c.c_int
     lib.msda_forward_ex.argtypes = ([vp, vp, vp, vp, vp, vp] + [i64] * 7 +
                                     [c.c_int, c.c_int, u32, vp, c.c_size_t, vp])
+    lib.msda_forward_static.restype = c.c_int
+    lib.msda_forward_static.argtypes = [vp, vp, vp, vp, vp, vp] + [i64] * 7 + [c.c_int, c.c_int, u32, vp]
     lib.msda_backward_ex.restype = c.c_int
     lib.msda_backward_ex.argtypes = (
         [vp] * 9 + [i64] * 7 + [c.c_int, c.c_int, u32, vp, c.c_size_t, vp, vp]

@@ -562,6 +562,7 @@ const char* msda_error_string(int status) {
     case MSDA_ERR_CUDA: return "CUDA runtime error (see msda_last_cuda_error_string)";
     case MSDA_ERR_MISALIGNED: return "data pointer not aligned to its element size";
     case MSDA_ERR_UNSUPPORTED: return "shape / dtype / flags outside the fused module path (use msda_frontend_* + msda_forward/backward)";
+    case MSDA_ERR_SCRATCH_LIMIT: return "msda_forward_static: the call needs more than the built-in MSDA_STATIC_SCRATCH_BYTES of scratch (N * Lq > 262144); use msda_forward_ex with a workspace";
     case MSDA_ERR_NO_TMA: return "TMA tensor map could not be encoded (driver entry point missing or rejected)";
     default: return "unknown msda status";
   }
@@ -693,6 +694,57 @@ int msda_forward(const void* value, const int64_t* spatial_shapes, const int64_t
 }
 
 }  // extern "C"
+
+// ---- msda_forward_static: the plan workspace as a built-in device array -------------
+// No counterpart in the reference (added for callers
+// that cannot allocate).  One array per GPU that loads the library, shared by every call on
+// that GPU; it keeps the last call's plan.  Nothing in it has to start at zero: the sort
+// kernel writes all N * Lq entries of the plan before the tile kernel reads them.
+static __device__ __align__(256) unsigned char g_msda_static_scratch[MSDA_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kStaticMaxDevices = 64;
+std::atomic<void*> g_static_scratch_ptr[kStaticMaxDevices];
+
+// Device address of the array on the CURRENT device.  In host code the array's name is a
+// host-side stand-in, not a device address: resolved once per device with
+// cudaGetSymbolAddress (while that device is current) and cached.
+int static_scratch(void** out) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_fail(e);
+  if (dev < 0 || dev >= kStaticMaxDevices) return MSDA_ERR_SCRATCH_LIMIT;
+  void* p = g_static_scratch_ptr[dev].load(std::memory_order_acquire);
+  if (!p) {
+    e = cudaGetSymbolAddress(&p, g_msda_static_scratch);
+    if (e != cudaSuccess) return cuda_fail(e);
+    if (!p) return MSDA_ERR_CUDA;
+    g_static_scratch_ptr[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return MSDA_OK;
+}
+}  // namespace
+
+extern "C" int msda_forward_static(const void* value, const int64_t* spatial_shapes,
+                                   const int64_t* level_start_index, const void* sampling_loc,
+                                   const void* attn_weight, void* output, int64_t N, int64_t S, int64_t M,
+                                   int64_t D, int64_t L, int64_t Lq, int64_t P, int dtype, int padding,
+                                   unsigned flags, void* stream) {
+  flags &= ~MSDA_FLAG_PLAN;   // the plan / apply split keeps 13 KB per tile: not from this array
+  const int rc = check_common(N, S, M, D, L, Lq, P, dtype, padding);
+  if (rc != MSDA_OK) return rc;
+  const size_t need = msda_forward_workspace_bytes(N, S, M, D, L, Lq, P, dtype, flags);
+  if (need > (size_t)MSDA_STATIC_SCRATCH_BYTES) return MSDA_ERR_SCRATCH_LIMIT;
+  void* scratch = nullptr;
+  if (need > 0) {
+    const int r = static_scratch(&scratch);
+    if (r != MSDA_OK) return r;
+  }
+  return msda_forward_ex(value, spatial_shapes, level_start_index, sampling_loc, attn_weight, output, N, S,
+                         M, D, L, Lq, P, dtype, padding, flags, scratch,
+                         need > 0 ? (size_t)MSDA_STATIC_SCRATCH_BYTES : 0, stream);
+}
 
 namespace {
 // the part of the backward workspace that is REQUIRED: the fp32 accumulation image of a bf16
