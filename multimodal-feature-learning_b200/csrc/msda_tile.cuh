@@ -46,6 +46,9 @@ namespace msda {
 #ifndef MSDA_TILE_BLK
 #define MSDA_TILE_BLK 56
 #endif
+#ifndef MSDA_TILE_WT_INTERLEAVE
+#define MSDA_TILE_WT_INTERLEAVE 1   // 1: the 4 blocks of a warp interleave their weight rows (below)
+#endif
 #ifndef MSDA_TILE_FWD_CTAS
 #define MSDA_TILE_FWD_CTAS 4
 #endif
@@ -59,6 +62,16 @@ constexpr int kTileQ = kTileBlocks * kWinQ;          // queries per tile (64 wit
 constexpr int kTileBoxRows = 8;                      // value rows per TMA box
 constexpr int kTileCapRows = MSDA_TILE_CAP;          // value rows per tile (multiple of the box)
 constexpr int kTileBlkRows = MSDA_TILE_BLK;          // packed rows per block (plan capacity)
+// Layout of the merged weight matrices in shared memory.  Row t of block g (packed plan row; the
+// packing is warp-uniform) is one float4 (one weight per query of the block):
+//   interleaved: warp region [t][g & 3][qi] -- the 4 blocks of a warp sit in 4 different bank
+//                groups, so the scatter's read-modify-writes and the backward's dot stores of a
+//                warp conflict at most 2-way (levels h / h + 1 of one block);
+//   private:     [g][t][qi], blocks 896 B apart = the same banks (4-5-way conflicts measured).
+constexpr int kTileWtStride = MSDA_TILE_WT_INTERLEAVE ? 4 : 1;   // float4 units between rows t, t + 1
+__device__ __forceinline__ int tile_wt_base(int g) {             // float4 index of (block g, row 0)
+  return MSDA_TILE_WT_INTERLEAVE ? (g >> 2) * 4 * kTileBlkRows + (g & 3) : g * kTileBlkRows;
+}
 constexpr int kSortBins = 4096;
 constexpr int kSortThreads = 1024;
 constexpr int kTileBig = 0x3fffffff;
@@ -660,7 +673,8 @@ __device__ __forceinline__ void tile_prologue(const CUtensorMap* vmap, const T* 
   }
 
   // the block's weight matrix: zero, then every lane scatters its own columns (level, qi)
-  for (int t = j; t < rt; t += 8) Wt[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+  constexpr int WS = kTileWtStride;
+  for (int t = j; t < rt; t += 8) Wt[t * WS] = make_float4(0.f, 0.f, 0.f, 0.f);
   __syncwarp();
   float* Wf = reinterpret_cast<float*>(Wt);
   int tb[2];
@@ -672,14 +686,14 @@ __device__ __forceinline__ void tile_prologue(const CUtensorMap* vmap, const T* 
     int t0[2];
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
-      t0[i] = (r0[i][p] + tb[i]) * 4 + qi;
+      t0[i] = (r0[i][p] + tb[i]) * (4 * WS) + qi;
       c0[i] = w0[i][p] != 0.f ? Wf[t0[i]] : 0.f;
-      c1[i] = w1[i][p] != 0.f ? Wf[t0[i] + 4] : 0.f;
+      c1[i] = w1[i][p] != 0.f ? Wf[t0[i] + 4 * WS] : 0.f;
     }
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
       if (w0[i][p] != 0.f) Wf[t0[i]] = c0[i] + w0[i][p];
-      if (w1[i][p] != 0.f) Wf[t0[i] + 4] = c1[i] + w1[i][p];
+      if (w1[i][p] != 0.f) Wf[t0[i] + 4 * WS] = c1[i] + w1[i][p];
     }
   }
   __syncwarp();
@@ -863,7 +877,7 @@ msda_fwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
     tile_fallback_fwd<T, NU, 4>(value, loc, aw, out, d, b, m, s_lvl, s_plan, s_q);
     return;
   }
-  float4* Wt = reinterpret_cast<float4*>(s_plan) + g * kTileBlkRows;
+  float4* Wt = reinterpret_cast<float4*>(s_plan) + tile_wt_base(g);
   TilePlan pl;
   tile_prologue<T, false, true, FUSED>(&vmap, loc, aw, d, b, m, s_q[g * kWinQ + (j & 3)], s_lvl, s_win, vtile,
                                        RB, Wt, &s_mbar, pl, &front);
@@ -900,11 +914,11 @@ msda_fwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
 #pragma unroll
   for (int l = 0; l < kWinMaxL; ++l) {
     const char* vr = vtile + pl.trow[l] * RB + j * 16;
-    const float4* wl = Wt + pl.bpoff[l];
+    const float4* wl = Wt + pl.bpoff[l] * kTileWtStride;
     const int n = pl.wrows[l], nb = pl.brows[l];
 #pragma unroll 2
     for (int i = 0; i < n; ++i) {
-      const float4 wv = wl[i];
+      const float4 wv = wl[i * kTileWtStride];
       const float wq[kWinQ] = {wv.x, wv.y, wv.z, wv.w};
 #pragma unroll
       for (int uu = 0; uu < NU; ++uu) {
@@ -1000,7 +1014,7 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
     }
   }
   const int my_q = s_q[g * kWinQ + qi];
-  float4* Wt = reinterpret_cast<float4*>(s_plan) + g * kTileBlkRows;
+  float4* Wt = reinterpret_cast<float4*>(s_plan) + tile_wt_base(g);
   float* Gs = reinterpret_cast<float*>(Wt);   // the dots G[t][qi] overwrite Wt[t][qi] pair by pair
   TilePlan pl;
   tile_prologue<T, true, true, FUSED>(&vmap, loc, aw, d, b, m, my_q, s_lvl, s_win, vtile, RB, Wt, &s_mbar, pl,
@@ -1060,15 +1074,15 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
 #pragma unroll
   for (int l = 0; l < kWinMaxL; ++l) {
     const char* vr = vtile + pl.trow[l] * RB + j * U::BYTES;
-    const float4* wl = Wt + pl.bpoff[l];
-    float* gl = Gs + pl.bpoff[l] * 4 + j;
+    const float4* wl = Wt + pl.bpoff[l] * kTileWtStride;
+    float* gl = Gs + (pl.bpoff[l] + (j >> 2)) * (4 * kTileWtStride) + (j & 3);
     GV* gp = gvb + (size_t)pl.blo[l] * MD;
     const int n = pl.wrows[l], nb = pl.brows[l];
     for (int i = 0; i < n; i += 2) {
       float x[2 * kWinQ];
 #pragma unroll
       for (int r = 0; r < 2; ++r) {
-        const float4 w = wl[i + r];
+        const float4 w = wl[(i + r) * kTileWtStride];
         const float wq[kWinQ] = {w.x, w.y, w.z, w.w};
         const bool real = i + r < nb && !(has_mask && s_rowmask[pl.trow[l] + i + r]);
         float2 s[kWinQ];
@@ -1106,7 +1120,7 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
         if (i + r + 1 < nb) vr += RB;
       }
       const float tot = transpose_reduce<8>(x, j, 0xffffffffu);
-      gl[i * 4] = tot;   // (row i + (j >> 2), query j & 3)
+      gl[i * (4 * kTileWtStride)] = tot;   // (row i + (j >> 2), query j & 3)
     }
   }
   __syncwarp();
@@ -1141,9 +1155,9 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
       bool live, v0, v1;
       WinCoef c;
       win_point<true>(x[p], y[p], a[p], W, start, d.border != 0, active, r0, w0, w1, live, v0, v1, c);
-      const int t0 = (r0 + tb) * 4 + qi;
+      const int t0 = (r0 + tb) * (4 * kTileWtStride) + qi;
       const float g0 = v0 ? Gs[t0] : 0.f;
-      const float g1 = v1 ? Gs[t0 + 4] : 0.f;
+      const float g1 = v1 ? Gs[t0 + 4 * kTileWtStride] : 0.f;
       ga[p] = fmaf(c.k0, g0, c.k1 * g1);
       gx[p] = c.fx * (g1 - g0);
       gy[p] = fmaf(c.cy0, g0, c.cy1 * g1);
