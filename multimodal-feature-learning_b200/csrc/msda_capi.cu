@@ -326,7 +326,7 @@ int launch_bwd_tile(const void* value, const int64_t* shapes, const int64_t* lsi
   CUtensorMap map;
   if (!tile_value_map(&map, value, dtype, d)) return MSDA_ERR_NO_TMA;
   auto kern = msda_bwd_tile_kernel<T, NU, GV, U, FUSED>;
-  constexpr size_t smem = (size_t)kTileCapRows * NU * 8 * U::BYTES + (size_t)kTileBlocks * kTileBlkRows * 16 + 128;
+  constexpr size_t smem = tile_bwd_smem<T, NU, GV, U>();
   const int rc = tile_smem_attr(kern, smem, attr_done);
   if (rc != MSDA_OK) return rc;
   const int nchunks = (d.Lq + kTileQ - 1) / kTileQ;

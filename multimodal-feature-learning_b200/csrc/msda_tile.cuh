@@ -49,6 +49,13 @@ namespace msda {
 #ifndef MSDA_TILE_WT_INTERLEAVE
 #define MSDA_TILE_WT_INTERLEAVE 1   // 1: the 4 blocks of a warp interleave their weight rows (below)
 #endif
+#ifndef MSDA_TILE_BULK_RED
+#define MSDA_TILE_BULK_RED 0        // 1: backward hands grad_value rows to the TMA unit (cp.reduce.async.bulk);
+                                   // measured SLOWER (127 vs 96 us at ENC, profiles/r2c_sass_bulk_red.txt): off
+#endif
+#ifndef MSDA_TILE_RED_GROUP
+#define MSDA_TILE_RED_GROUP 1       // 1: backward issues the reds of a row (all units) under ONE branch
+#endif
 #ifndef MSDA_TILE_FWD_CTAS
 #define MSDA_TILE_FWD_CTAS 4
 #endif
@@ -399,6 +406,23 @@ __device__ __forceinline__ void tile_tma_load(void* smem_dst, const CUtensorMap*
 }
 
 // a unit of a value row from the shared-memory tile
+// grad_value rows through the TMA unit: `bytes` of fp32 at `ssrc` (shared memory, written by generic
+// stores + fence.proxy.async) are ADDED to global memory at `gdst` (both 16-byte aligned); the
+// operation belongs to the issuing thread's current bulk group.  SASS: UBLKRED.
+__device__ __forceinline__ void tile_bulk_red_f32(float* gdst, const void* ssrc, unsigned bytes) {
+  asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(gdst),
+               "r"(tile_smem_u32(ssrc)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void tile_bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void tile_bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void tile_fence_async_smem() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
 template <typename U>
 __device__ __forceinline__ void tile_lds(const char* p, typename U::Raw (&buf)[U::RW]) {
   using Raw = typename U::Raw;
@@ -842,6 +866,16 @@ struct TileSmem {
   static constexpr int kBytes = kValueBytes + kPlanBytes + 128 + MSDA_TILE_SMEM_PAD;
 };
 
+// Backward: + the staging rows of the bulk reductions, [2 slots][block][2 rows][one head's row of
+// grad_value], when grad_value accumulates as fp32 (not the fixed-point image of the deterministic form)
+template <typename GV>
+struct TileBulkRed { static constexpr bool value = MSDA_TILE_BULK_RED != 0 && std::is_same<GV, float>::value; };
+template <typename T, int NU, typename GV, typename U>
+constexpr size_t tile_bwd_smem() {
+  return (size_t)kTileCapRows * NU * 8 * U::BYTES + (size_t)kTileBlocks * kTileBlkRows * 16 + 128 +
+         (TileBulkRed<GV>::value ? (size_t)2 * kTileBlocks * 2 * NU * 8 * U::E * 4 : 0) + MSDA_TILE_SMEM_PAD;
+}
+
 // ------------------------------- forward ------------------------------------
 template <typename T, int NU, bool FUSED = false>
 __global__ void __launch_bounds__(kTileThreads, MSDA_TILE_FWD_CTAS)
@@ -1068,6 +1102,10 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
     tile_apply_mask<RB>(front.mask + (size_t)b * d.S, d.S, pl.tlo, pl.tbase, pl.total, vtile, s_rowmask);
 
   const int MD = d.M * d.D;
+  constexpr bool BULK = TileBulkRed<GV>::value;
+  constexpr int GRB = NU * G * E * 4;   // bytes of one head's grad_value row
+  char* s_stage = s_plan + kTileBlocks * kTileBlkRows * 16;
+  int it = 0;                           // row pairs done (warp-uniform): the staging slot alternates
   GV* gvb = gvalue + ((size_t)b * d.S * d.M + m) * d.D + j * E;
   // warp-uniform row loops over pairs of rows: a block past its own rows re-reads its last row
   // against zero weights and issues no reds
@@ -1080,27 +1118,64 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
     const int n = pl.wrows[l], nb = pl.brows[l];
     for (int i = 0; i < n; i += 2) {
       float x[2 * kWinQ];
+      float* stg = nullptr;
+      bool realr[2] = {false, false};
+      GV* gp0 = gp;
+      if (BULK) {
+        // the slot was handed to the TMA unit two pairs ago: that group must have read it
+        if (j == 0) tile_bulk_wait_read<1>();
+        __syncwarp();
+        stg = reinterpret_cast<float*>(s_stage + (size_t)(((it & 1) * kTileBlocks + g) * 2) * GRB) + j * E;
+      }
 #pragma unroll
       for (int r = 0; r < 2; ++r) {
         const float4 w = wl[(i + r) * kTileWtStride];
         const float wq[kWinQ] = {w.x, w.y, w.z, w.w};
+#ifdef MSDA_TILE_DBG_NORED
+        const bool real = gv_scale == 12345.f;   // experiment: no reds
+#else
         const bool real = i + r < nb && !(has_mask && s_rowmask[pl.trow[l] + i + r]);
+#endif
         float2 s[kWinQ];
+        // grad_value row: sum_q Wt[t][q] * grad_out[q]
+        float2 dv[NU][E / 2];
 #pragma unroll
-        for (int u = 0; u < NU; ++u) {
-          // grad_value row: sum_q Wt[t][q] * grad_out[q]
-          float2 dv[E / 2];
+        for (int u = 0; u < NU; ++u)
 #pragma unroll
           for (int q = 0; q < kWinQ; ++q) {
             const float2 w2 = make_float2(wq[q], wq[q]);
 #pragma unroll
             for (int c = 0; c < E / 2; ++c)
-              dv[c] = q == 0 ? __fmul2_rn(w2, go[q][u][c]) : __ffma2_rn(w2, go[q][u][c], dv[c]);
+              dv[u][c] = q == 0 ? __fmul2_rn(w2, go[q][u][c]) : __ffma2_rn(w2, go[q][u][c], dv[u][c]);
           }
+        if (BULK) {
 #pragma unroll
-          for (int c = 0; c < E / 2; c += 2)
-            GvRed<GV>::add4(gp + u * (G * E) + 2 * c, real, dv[c].x, dv[c].y, dv[c + 1].x, dv[c + 1].y,
-                            gv_scale);
+          for (int u = 0; u < NU; ++u)
+#pragma unroll
+            for (int c = 0; c < E / 2; c += 2)
+              *reinterpret_cast<float4*>(stg + r * (GRB / 4) + u * (G * E) + 2 * c) =
+                  make_float4(dv[u][c].x, dv[u][c].y, dv[u][c + 1].x, dv[u][c + 1].y);
+        } else if (MSDA_TILE_RED_GROUP) {
+          // one branch around the row's reds (ptxas turns every predicated red into its own
+          // BSSY / BRA / BSYNC region)
+          if (real) {
+#pragma unroll
+            for (int u = 0; u < NU; ++u)
+#pragma unroll
+              for (int c = 0; c < E / 2; c += 2)
+                GvRed<GV>::add4(gp + u * (G * E) + 2 * c, true, dv[u][c].x, dv[u][c].y, dv[u][c + 1].x,
+                                dv[u][c + 1].y, gv_scale);
+          }
+        } else {
+#pragma unroll
+          for (int u = 0; u < NU; ++u)
+#pragma unroll
+            for (int c = 0; c < E / 2; c += 2)
+              GvRed<GV>::add4(gp + u * (G * E) + 2 * c, real, dv[u][c].x, dv[u][c].y, dv[u][c + 1].x,
+                              dv[u][c + 1].y, gv_scale);
+        }
+#pragma unroll
+        for (int u = 0; u < NU; ++u) {
           // this lane's share of <grad_out[q], value row>
           Raw raw[U::RW];
           tile_lds<U>(vr + u * (G * U::BYTES), raw);
@@ -1116,13 +1191,29 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
         }
 #pragma unroll
         for (int q = 0; q < kWinQ; ++q) x[r * kWinQ + q] = s[q].x + s[q].y;
+        realr[r] = real;
         gp += MD;
         if (i + r + 1 < nb) vr += RB;
       }
       const float tot = transpose_reduce<8>(x, j, 0xffffffffu);
       gl[i * (4 * kTileWtStride)] = tot;   // (row i + (j >> 2), query j & 3)
+      if (BULK) {
+        // the block's two rows, complete in shared memory -> one bulk reduction each, issued by
+        // the block's first lane
+        tile_fence_async_smem();
+        __syncwarp();
+        if (j == 0) {
+          float* grow = reinterpret_cast<float*>(gp0);
+#pragma unroll
+          for (int r = 0; r < 2; ++r)
+            if (realr[r]) tile_bulk_red_f32(grow + (size_t)r * MD, stg + r * (GRB / 4), GRB);
+          tile_bulk_commit();
+        }
+        ++it;
+      }
     }
   }
+  if (BULK && j == 0) tile_bulk_wait_read<0>();   // shared memory must outlive the reads
   __syncwarp();
 
   // per-point gradients: the points again, the geometry again, the dots
