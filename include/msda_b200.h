@@ -111,6 +111,17 @@ typedef enum {
                                       msda_plan.cuh.  Measured slower than the one-kernel
                                       form on B200: kept as an
                                       experiment, off by default */
+#define MSDA_FLAG_SAVE_PLAN 128u    /* msda_forward_ex + msda_backward_ex, CTA-tile shape class: the
+                                      forward also SAVES every tile's plan (windows + merged
+                                      weights, ~14.6 KB reserved / ~7 KB written per 64 queries
+                                      and head) behind the query order in its workspace
+                                      (msda_forward_workspace_bytes with this flag reports the
+                                      size; 128-byte aligned); msda_backward_ex given that
+                                      workspace as `plan` AND this flag starts every tile from
+                                      the saved plan instead of the sampling points.  Set it on
+                                      both calls or on neither; a forward workspace too small for
+                                      the plans just keeps the query order (then do not set the
+                                      flag on the backward).  Same results */
 /* bits 8..19: queries-per-tile multiplier override for the vectorised kernels
  * (0 = heuristic); a tuning knob, results do not depend on it. */
 #define MSDA_FLAG_QTILE(k) (((unsigned)(k) & 0xfffu) << 8)

@@ -57,18 +57,31 @@ def _stream(t):
     return torch.cuda.current_stream(t.device).cuda_stream
 
 
+# True: the plan a forward returns for its backward also holds every tile's windows and merged
+# weights (MSDA_FLAG_SAVE_PLAN, ~1.8 KB per query at M = 8) and the backward starts from them instead
+# of the sampling points.  Same results; measured on B200 it does not pay (forward + 2 us for the
+# stores, backward unchanged: DESIGN.md section 6), so only the query order (4 B per query) is kept.
+SAVE_PLAN = False
+
+
 def ms_deform_attn_forward(value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
-                           im2col_step, padding_mode="zeros", flags=0, return_plan=False):
+                           im2col_step, padding_mode="zeros", flags=0, return_plan=False, save_plan=None):
     """value[N,S,M,D] ... -> output[N,Lq,M*D]  (cuda.cu:20-80).
     return_plan=True also returns the plan workspace of msda_forward_ex (the time order of the
     queries; None when the shape does not use the CTA-tile kernels), which
-    ms_deform_attn_backward(plan=...) reuses instead of sorting again."""
+    ms_deform_attn_backward(plan=...) reuses instead of sorting again.  save_plan (default: the
+    module switch SAVE_PLAN, when a plan is returned): the plan also carries the tiles' saved plans
+    (plan.msda_saved is True then)"""
     N, S, M, D, L, Lq, P = _check_inputs(
         [("value", value), ("spatial_shapes", spatial_shapes),
          ("level_start_index", level_start_index), ("sampling_loc", sampling_loc),
          ("attn_weight", attn_weight)], im2col_step)
     lib = _lib.load()
     dt = _DTYPES[value.dtype]
+    if save_plan is None:
+        save_plan = SAVE_PLAN and return_plan
+    if save_plan and not (flags & _lib.MSDA_FLAG_PLAN):
+        flags |= _lib.MSDA_FLAG_SAVE_PLAN
     with torch.cuda.device_of(value):
         out = torch.empty((N, Lq, M * D), dtype=value.dtype, device=value.device)
         ws_bytes = lib.msda_forward_workspace_bytes(N, S, M, D, L, Lq, P, dt, flags)
@@ -80,6 +93,7 @@ def ms_deform_attn_forward(value, spatial_shapes, level_start_index, sampling_lo
             flags, ws.data_ptr() if ws is not None else None, ws_bytes, _stream(value)))
         if ws is not None:
             ws.record_stream(torch.cuda.current_stream(value.device))
+            ws.msda_saved = bool(flags & _lib.MSDA_FLAG_SAVE_PLAN)
     return (out, ws) if return_plan else out
 
 
@@ -100,6 +114,9 @@ def ms_deform_attn_backward(value, spatial_shapes, level_start_index, sampling_l
         raise RuntimeError("grad_output must have N*Lq*M*D elements")
     lib = _lib.load()
     dt = _DTYPES[value.dtype]
+    flags &= ~_lib.MSDA_FLAG_SAVE_PLAN
+    if plan is not None and getattr(plan, "msda_saved", False):
+        flags |= _lib.MSDA_FLAG_SAVE_PLAN      # the plan carries the forward's tile plans
     with torch.cuda.device_of(value):
         if grad_value is None:
             grad_value = torch.empty_like(value)

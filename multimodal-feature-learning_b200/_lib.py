@@ -22,6 +22,7 @@ MSDA_FLAG_FORCE_WINDOW = 8
 MSDA_FLAG_DETERMINISTIC = 16
 MSDA_FLAG_NO_TILE = 32
 MSDA_FLAG_PLAN = 64
+MSDA_FLAG_SAVE_PLAN = 128
 ABI_VERSION = 2
 
 

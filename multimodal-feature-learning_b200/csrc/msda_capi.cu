@@ -302,7 +302,8 @@ int launch_pdl(void (*kern)(KArgs...), unsigned grid, unsigned block, size_t sme
 template <typename T, int NU, bool FUSED = false>
 int launch_fwd_tile(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
                     const void* aw, const int* perm, void* out, const Dims& d, int dtype,
-                    cudaStream_t st, bool after_sort, TileFront<T> front = TileFront<T>()) {
+                    cudaStream_t st, bool after_sort, TileFront<T> front = TileFront<T>(),
+                    char* save = nullptr) {
   static std::atomic<unsigned long long> attr_done{0};
   CUtensorMap map;
   if (!tile_value_map(&map, value, dtype, d)) return MSDA_ERR_NO_TMA;
@@ -313,7 +314,7 @@ int launch_fwd_tile(const void* value, const int64_t* shapes, const int64_t* lsi
   const int nchunks = (d.Lq + kTileQ - 1) / kTileQ;
   const unsigned grid = (unsigned)((int64_t)d.N * d.M * nchunks);
   return launch_pdl(kern, grid, kTileThreads, smem, st, after_sort, map, (const T*)value, shapes, lsi,
-                    (const T*)loc, (const T*)aw, perm, (T*)out, d, nchunks, front);
+                    (const T*)loc, (const T*)aw, perm, (T*)out, d, nchunks, front, save);
 }
 
 template <typename T, int NU, typename GV = float, typename U = Unit<T>, bool FUSED = false>
@@ -321,7 +322,7 @@ int launch_bwd_tile(const void* value, const int64_t* shapes, const int64_t* lsi
                     const void* aw, const void* gout, const int* perm, GV* gvalue, void* gloc,
                     void* gaw, const Dims& d, int dtype, cudaStream_t st,
                     const DetHeader* det = nullptr, bool after_sort = false,
-                    TileFront<T> front = TileFront<T>()) {
+                    TileFront<T> front = TileFront<T>(), const char* saved = nullptr) {
   static std::atomic<unsigned long long> attr_done{0};
   CUtensorMap map;
   if (!tile_value_map(&map, value, dtype, d)) return MSDA_ERR_NO_TMA;
@@ -333,7 +334,7 @@ int launch_bwd_tile(const void* value, const int64_t* shapes, const int64_t* lsi
   const unsigned grid = (unsigned)((int64_t)d.N * d.M * nchunks);
   return launch_pdl(kern, grid, kTileThreads, smem, st, after_sort, map, (const T*)value, shapes, lsi,
                     (const T*)loc, (const T*)aw, (const T*)gout, perm, gvalue, (T*)gloc, (T*)gaw, d,
-                    nchunks, det, front);
+                    nchunks, det, front, saved);
 }
 
 // ---- plan / apply split (msda_plan.cuh) ---------------------------------------------
@@ -343,6 +344,13 @@ inline size_t plan_tiles(int64_t N, int64_t M, int64_t Lq) {
 }
 inline size_t plan_ws_bytes(int64_t N, int64_t M, int64_t Lq) {
   return tile_plan_bytes(N, Lq) + plan_tiles(N, M, Lq) * kPlanStride;
+}
+// workspace with SAVED plans (MSDA_FLAG_SAVE_PLAN): [query order][tiles * kSaveStride]
+inline size_t save_ws_bytes(int64_t N, int64_t M, int64_t Lq) {
+  return tile_plan_bytes(N, Lq) + plan_tiles(N, M, Lq) * (size_t)kSaveStride;
+}
+inline bool save_applies(unsigned flags) {
+  return MSDA_TILE_WT_INTERLEAVE != 0 && (flags & MSDA_FLAG_SAVE_PLAN) && !(flags & MSDA_FLAG_PLAN);
 }
 inline char* plan_of(void* workspace, int64_t N, int64_t Lq) {
   return (char*)workspace + tile_plan_bytes(N, Lq);
@@ -601,7 +609,8 @@ size_t msda_forward_workspace_bytes(int64_t N, int64_t S, int64_t M, int64_t D, 
   if (check_common(N, S, M, D, L, Lq, P, dtype, MSDA_PAD_ZEROS) != MSDA_OK || N == 0 || Lq == 0) return 0;
   const bool fast = S * M * D < (int64_t(1) << 31) && fast_applies(D, L, dtype, flags);
   if (!fast || !tile_applies(make_dims(N, S, M, D, L, Lq, P, MSDA_PAD_ZEROS), dtype, flags)) return 0;
-  return (flags & MSDA_FLAG_PLAN) ? plan_ws_bytes(N, M, Lq) : tile_plan_bytes(N, Lq);
+  if (flags & MSDA_FLAG_PLAN) return plan_ws_bytes(N, M, Lq);
+  return save_applies(flags) ? save_ws_bytes(N, M, Lq) : tile_plan_bytes(N, Lq);
 }
 
 int msda_forward_ex(const void* value, const int64_t* spatial_shapes, const int64_t* level_start_index,
@@ -645,15 +654,21 @@ int msda_forward_ex(const void* value, const int64_t* spatial_shapes, const int6
                                        plan, output, d, dtype, st, true);
       if (r != MSDA_ERR_NO_TMA) return r;
     }
+    // MSDA_FLAG_SAVE_PLAN: the tiles' plans go behind the query order, for msda_backward_ex
+    char* save = save_applies(flags) && workspace_bytes >= save_ws_bytes(N, M, Lq) &&
+                         (reinterpret_cast<uintptr_t>(workspace) & 127u) == 0
+                     ? (char*)workspace + tile_plan_bytes(N, Lq)
+                     : nullptr;
     if (dtype == MSDA_BF16)
       r = launch_fwd_tile<__nv_bfloat16, 1>(value, spatial_shapes, level_start_index, sampling_loc,
-                                            attn_weight, perm, output, d, dtype, st, true);
+                                            attn_weight, perm, output, d, dtype, st, true,
+                                            TileFront<__nv_bfloat16>(), save);
     else if (D == 64)
       r = launch_fwd_tile<float, 2>(value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
-                                    perm, output, d, dtype, st, true);
+                                    perm, output, d, dtype, st, true, TileFront<float>(), save);
     else
       r = launch_fwd_tile<float, 1>(value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
-                                    perm, output, d, dtype, st, true);
+                                    perm, output, d, dtype, st, true, TileFront<float>(), save);
     if (r != MSDA_ERR_NO_TMA) return r;   // descriptor rejected: the row-window kernels take over
   }
   if (fast && win_applies(d, dtype, flags)) {
@@ -731,7 +746,8 @@ extern "C" int msda_forward_static(const void* value, const int64_t* spatial_sha
                                    const void* attn_weight, void* output, int64_t N, int64_t S, int64_t M,
                                    int64_t D, int64_t L, int64_t Lq, int64_t P, int dtype, int padding,
                                    unsigned flags, void* stream) {
-  flags &= ~MSDA_FLAG_PLAN;   // the plan / apply split keeps 13 KB per tile: not from this array
+  // the plan / apply split and saved plans keep ~14 KB per tile: not from this array
+  flags &= ~(MSDA_FLAG_PLAN | MSDA_FLAG_SAVE_PLAN);
   const int rc = check_common(N, S, M, D, L, Lq, P, dtype, padding);
   if (rc != MSDA_OK) return rc;
   const size_t need = msda_forward_workspace_bytes(N, S, M, D, L, Lq, P, dtype, flags);
@@ -764,7 +780,8 @@ size_t msda_backward_workspace_bytes_flags(int64_t N, int64_t S, int64_t M, int6
                                            int64_t Lq, int64_t P, int dtype, unsigned flags) {
   const size_t main_bytes = ws_main_bytes(N, S, M, D, dtype, flags);
   // + the plan of the CTA-tile kernels (optional: without it the row-window kernels run)
-  const size_t plan = msda_forward_workspace_bytes(N, S, M, D, L, Lq, P, dtype, flags & ~MSDA_FLAG_PLAN);
+  const size_t plan = msda_forward_workspace_bytes(N, S, M, D, L, Lq, P, dtype,
+                                                   flags & ~(MSDA_FLAG_PLAN | MSDA_FLAG_SAVE_PLAN));
   return plan ? round256(main_bytes) + plan : main_bytes;
 }
 
@@ -799,10 +816,13 @@ int msda_backward_ex(const void* value, const int64_t* spatial_shapes, const int
                        aligned16(grad_sampling_loc) && aligned16(grad_attn_weight);
   const bool fast = fits32 && fast_applies(D, L, dtype, flags) && aligned;
   const int* perm = nullptr;
+  const char* saved = nullptr;   // the forward's saved tile plans behind the query order
   bool need_sort = false;
   if (N > 0 && Lq > 0 && fast && tile_applies(d, dtype, flags) && tile_encoder()) {
     if (plan && aligned16(plan)) {
       perm = (const int*)plan;
+      if (save_applies(flags) && (reinterpret_cast<uintptr_t>(plan) & 127u) == 0)
+        saved = (const char*)plan + tile_plan_bytes(N, Lq);
     } else if (workspace && aligned16(workspace) &&
                workspace_bytes >= round256(ws_need) + tile_plan_bytes(N, Lq)) {
       perm = (const int*)((char*)workspace + round256(ws_need));
@@ -871,15 +891,16 @@ int msda_backward_ex(const void* value, const int64_t* spatial_shapes, const int
       // two 8-byte units per lane: dense 128-byte reds into the fp32 image (msda_fast.cuh)
       r = launch_bwd_tile<__nv_bfloat16, 2, float, UnitBf16x4>(
           value, spatial_shapes, level_start_index, sampling_loc, attn_weight, grad_output, perm,
-          (float*)acc, grad_sampling_loc, grad_attn_weight, d, dtype, st, nullptr, need_sort);
+          (float*)acc, grad_sampling_loc, grad_attn_weight, d, dtype, st, nullptr, need_sort,
+          TileFront<__nv_bfloat16>(), saved);
     else if (D == 64)
       r = launch_bwd_tile<float, 2>(value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
                                     grad_output, perm, (float*)acc, grad_sampling_loc, grad_attn_weight,
-                                    d, dtype, st, nullptr, need_sort);
+                                    d, dtype, st, nullptr, need_sort, TileFront<float>(), saved);
     else
       r = launch_bwd_tile<float, 1>(value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
                                     grad_output, perm, (float*)acc, grad_sampling_loc, grad_attn_weight,
-                                    d, dtype, st, nullptr, need_sort);
+                                    d, dtype, st, nullptr, need_sort, TileFront<float>(), saved);
   }
   if (r != MSDA_ERR_NO_TMA) {
     // done by the tile kernels (or failed)
@@ -1083,6 +1104,10 @@ int msda_module_forward(const void* value, const int64_t* spatial_shapes, const 
     return MSDA_ERR_UNSUPPORTED;
   cudaStream_t st = (cudaStream_t)stream;
   int* perm = (int*)workspace;
+  char* save = save_applies(flags) && workspace_bytes >= save_ws_bytes(N, M, Lq) &&
+                       (reinterpret_cast<uintptr_t>(workspace) & 127u) == 0
+                   ? (char*)workspace + tile_plan_bytes(N, Lq)
+                   : nullptr;
   int r;
   if (dtype == MSDA_BF16) {
     const SortSrc<__nv_bfloat16> src = {nullptr, (const __nv_bfloat16*)offsets, (const __nv_bfloat16*)ref,
@@ -1091,16 +1116,17 @@ int msda_module_forward(const void* value, const int64_t* spatial_shapes, const 
     r = launch_fwd_tile<__nv_bfloat16, 1, true>(value, spatial_shapes, level_start_index, nullptr, nullptr, perm,
                                                 output, d, dtype, st, true,
                                                 make_front<__nv_bfloat16>(offsets, logits, ref, nullptr, nullptr,
-                                                                          nullptr, ref_dim, padding_mask));
+                                                                          nullptr, ref_dim, padding_mask),
+                                                save);
   } else {
     const SortSrc<float> src = {nullptr, (const float*)offsets, (const float*)ref, spatial_shapes, ref_dim};
     if ((r = launch_sort<float>(src, perm, d, st)) != MSDA_OK) return r;
     const TileFront<float> f = make_front<float>(offsets, logits, ref, nullptr, nullptr, nullptr, ref_dim,
                                                  padding_mask);
     r = D == 64 ? launch_fwd_tile<float, 2, true>(value, spatial_shapes, level_start_index, nullptr, nullptr, perm,
-                                                  output, d, dtype, st, true, f)
+                                                  output, d, dtype, st, true, f, save)
                 : launch_fwd_tile<float, 1, true>(value, spatial_shapes, level_start_index, nullptr, nullptr, perm,
-                                                  output, d, dtype, st, true, f);
+                                                  output, d, dtype, st, true, f, save);
   }
   return r == MSDA_ERR_NO_TMA ? MSDA_ERR_UNSUPPORTED : r;
 }
@@ -1135,21 +1161,25 @@ int msda_module_backward(const void* value, const int64_t* spatial_shapes, const
     e = cudaMemsetAsync(grad_ref, 0, (size_t)N * Lq * L * ref_dim * sizeof(float), st);
   if (e != cudaSuccess) return cuda_fail(e);
   const int* perm = (const int*)plan;
+  const char* saved = save_applies(flags) && (reinterpret_cast<uintptr_t>(plan) & 127u) == 0
+                          ? (const char*)plan + tile_plan_bytes(N, Lq)
+                          : nullptr;
   int r;
   if (dtype == MSDA_BF16) {
     r = launch_bwd_tile<__nv_bfloat16, 2, float, UnitBf16x4, true>(
         value, spatial_shapes, level_start_index, nullptr, nullptr, grad_output, perm, (float*)acc, nullptr,
         nullptr, d, dtype, st, nullptr, false,
-        make_front<__nv_bfloat16>(offsets, logits, ref, grad_offsets, grad_logits, grad_ref, ref_dim, padding_mask));
+        make_front<__nv_bfloat16>(offsets, logits, ref, grad_offsets, grad_logits, grad_ref, ref_dim, padding_mask),
+        saved);
   } else {
     const TileFront<float> f = make_front<float>(offsets, logits, ref, grad_offsets, grad_logits, grad_ref, ref_dim,
                                                  padding_mask);
     r = D == 64 ? launch_bwd_tile<float, 2, float, Unit<float>, true>(
                       value, spatial_shapes, level_start_index, nullptr, nullptr, grad_output, perm, (float*)acc,
-                      nullptr, nullptr, d, dtype, st, nullptr, false, f)
+                      nullptr, nullptr, d, dtype, st, nullptr, false, f, saved)
                 : launch_bwd_tile<float, 1, float, Unit<float>, true>(
                       value, spatial_shapes, level_start_index, nullptr, nullptr, grad_output, perm, (float*)acc,
-                      nullptr, nullptr, d, dtype, st, nullptr, false, f);
+                      nullptr, nullptr, d, dtype, st, nullptr, false, f, saved);
   }
   if (r == MSDA_ERR_NO_TMA) return MSDA_ERR_UNSUPPORTED;
   if (r != MSDA_OK) return r;

@@ -223,15 +223,6 @@ struct ApplySmem {
 static_assert(kTileCapRows <= 255, "tile rows are stored in a byte");
 static_assert(kPlanMetaBytes % 128 == 0 && kPlanWtBytes % 128 == 0, "stage sections stay 128-byte aligned");
 
-// bulk copy global -> shared (1-D), completion on an mbarrier
-__device__ __forceinline__ void tile_bulk_load(void* smem_dst, const void* gsrc, unsigned bytes,
-                                               unsigned long long* mbar) {
-  asm volatile(
-      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-          tile_smem_u32(smem_dst)),
-      "l"(gsrc), "r"(bytes), "r"(tile_smem_u32(mbar))
-      : "memory");
-}
 __device__ __forceinline__ void tile_mbar_arrive(unsigned long long* mbar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tile_smem_u32(mbar)) : "memory");
 }

@@ -79,6 +79,21 @@ constexpr int kTileWtStride = MSDA_TILE_WT_INTERLEAVE ? 4 : 1;   // float4 units
 __device__ __forceinline__ int tile_wt_base(int g) {             // float4 index of (block g, row 0)
   return MSDA_TILE_WT_INTERLEAVE ? (g >> 2) * 4 * kTileBlkRows + (g & 3) : g * kTileBlkRows;
 }
+// A SAVED plan (MSDA_FLAG_SAVE_PLAN): what the forward's prologue worked out for a tile, kept in
+// the workspace behind the query order so that the backward starts from it instead of the points.
+// Per tile (index = blockIdx.x) kSaveStride bytes:
+//   int [0..3]  first slab row of the tile's window per level   (s_win lo)
+//   int [4..7]  last slab row                                    (s_win hi)
+//   int [8..11] packed plan rows of warp 0..3 (rt; 64 B each in the weight region)
+//   int [12]    1: the tile has a plan, 0: it runs the per-tap body (nothing else is valid)
+//   +128 + 32 g: block g: int blo[4], int brows[4]
+//   +kSaveHdrBytes: the warps' weight regions as they sit in shared memory (interleaved layout),
+//                   rt * 64 bytes used of each
+constexpr int kSaveHdrBytes = 128 + kTileBlocks * 32;
+constexpr int kSaveWarpBytes = 4 * kTileBlkRows * 16;
+constexpr int kSaveStride = kSaveHdrBytes + kTileBlocks * kTileBlkRows * 16;
+static_assert(kSaveHdrBytes % 128 == 0 && kSaveStride % 128 == 0, "saved plans stay 128-byte aligned");
+static_assert(kTileWarps == 4 || !MSDA_TILE_WT_INTERLEAVE, "header holds 4 warps");
 constexpr int kSortBins = 4096;
 constexpr int kSortThreads = 1024;
 constexpr int kTileBig = 0x3fffffff;
@@ -414,6 +429,21 @@ __device__ __forceinline__ void tile_bulk_red_f32(float* gdst, const void* ssrc,
                "r"(tile_smem_u32(ssrc)), "r"(bytes)
                : "memory");
 }
+// bulk copy global -> shared (1-D), completion on an mbarrier
+__device__ __forceinline__ void tile_bulk_load(void* smem_dst, const void* gsrc, unsigned bytes,
+                                               unsigned long long* mbar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+          tile_smem_u32(smem_dst)),
+      "l"(gsrc), "r"(bytes), "r"(tile_smem_u32(mbar))
+      : "memory");
+}
+// bulk copy shared -> global (1-D) in the issuing thread's current bulk group
+__device__ __forceinline__ void tile_bulk_store(void* gdst, const void* ssrc, unsigned bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst),
+               "r"(tile_smem_u32(ssrc)), "r"(bytes)
+               : "memory");
+}
 __device__ __forceinline__ void tile_bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void tile_bulk_wait_read() {
@@ -576,6 +606,21 @@ struct TilePlan {
   bool ok;               // false: the tile runs the per-tap body
 };
 
+// One thread: the value boxes of a tile (level l: rows tlo[l].. in boxes of kTileBoxRows, landing at
+// tile row tbase[l]) -> TMA loads completing on mbar (whose expect_tx the caller has set)
+__device__ __forceinline__ void tile_issue_boxes(const CUtensorMap* vmap, const Dims& d, int b, int m,
+                                                 const int (&tlo)[kWinMaxL], const int (&tbase)[kWinMaxL],
+                                                 int total, char* vtile, unsigned row_bytes,
+                                                 unsigned long long* mbar) {
+#pragma unroll
+  for (int l = 0; l < kWinMaxL; ++l) {
+    const int nb = ((l + 1 < kWinMaxL ? tbase[l + 1] : total) - tbase[l]) / kTileBoxRows;
+    for (int k = 0; k < nb; ++k)
+      tile_tma_load(vtile + (size_t)(tbase[l] + k * kTileBoxRows) * row_bytes, vmap, m * d.D,
+                    b * d.S + tlo[l] + k * kTileBoxRows, mbar);
+  }
+}
+
 // Geometry of the thread's points, block and tile windows, TMA issue, weight scatter.
 // PAIR: row loops run over pairs of rows (backward): every level of a plan is padded to an even
 // row count.
@@ -687,13 +732,7 @@ __device__ __forceinline__ void tile_prologue(const CUtensorMap* vmap, const T* 
 
   if (ISSUE && tid == 0 && total > 0) {
     tile_mbar_expect_tx(mbar, (unsigned)total * row_bytes);
-#pragma unroll
-    for (int l = 0; l < kWinMaxL; ++l) {
-      const int nb = ((l + 1 < kWinMaxL ? tbase[l + 1] : total) - tbase[l]) / kTileBoxRows;
-      for (int k = 0; k < nb; ++k)
-        tile_tma_load(vtile + (size_t)(tbase[l] + k * kTileBoxRows) * row_bytes, vmap, m * d.D,
-                      b * d.S + tlo[l] + k * kTileBoxRows, mbar);
-    }
+    tile_issue_boxes(vmap, d, b, m, tlo, tbase, total, vtile, row_bytes, mbar);
   }
 
   // the block's weight matrix: zero, then every lane scatters its own columns (level, qi)
@@ -769,6 +808,23 @@ __device__ __forceinline__ void tile_prefetch_ahead(const int* __restrict__ perm
   const T* p1 = front && front->off ? front->logits + grp * LP : aw + grp * LP;
   asm volatile("prefetch.global.L2 [%0];" ::"l"(p0));
   asm volatile("prefetch.global.L2 [%0];" ::"l"(p1));
+}
+
+// The same for a SAVED plan: header and the first 2 KB of every warp's weight region of the tile
+// that runs ~2 waves later (one 128-byte line per thread).
+__device__ __forceinline__ void tile_prefetch_saved(const char* saved) {
+  if (MSDA_TILE_AHEAD <= 0) return;
+  const long long ft = (long long)blockIdx.x + MSDA_TILE_AHEAD;
+  if (ft >= (long long)gridDim.x) return;
+  const int t = threadIdx.x;
+  const char* ts = saved + (size_t)ft * kSaveStride;
+  const char* p;
+  if (t < kSaveHdrBytes / 128) p = ts + t * 128;
+  else if (t < kSaveHdrBytes / 128 + 4 * 16) {
+    const int u = t - kSaveHdrBytes / 128;
+    p = ts + kSaveHdrBytes + (u >> 4) * kSaveWarpBytes + (u & 15) * 128;
+  } else return;
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
 }
 
 // The per-tap bodies as out-of-line functions: they are the rare path and must not shape the
@@ -855,6 +911,85 @@ __device__ __forceinline__ void tile_front_backward(const TileFront<T>& f, const
   }
 }
 
+// Forward, after the prologue: the tile's plan -> its slot `ts` of the workspace (layout at
+// kSaveStride).  All threads; the warps' weight regions leave as bulk copies (the caller waits for
+// their reads before the CTA exits).
+__device__ __forceinline__ void tile_save_plan(char* ts, const TilePlan& pl, const int* s_win, char* s_plan) {
+  const int tid = threadIdx.x, g = tid >> 3, j = tid & 7, warp = tid >> 5;
+  if (j == 0) {
+    int4* hb = reinterpret_cast<int4*>(ts + 128 + g * 32);
+    hb[0] = make_int4(pl.blo[0], pl.blo[1], pl.blo[2], pl.blo[3]);
+    hb[1] = make_int4(pl.brows[0], pl.brows[1], pl.brows[2], pl.brows[3]);
+  }
+  const int rt = pl.ok ? pl.rt : 0;
+  if ((tid & 31) == 0) reinterpret_cast<int*>(ts)[8 + warp] = rt;
+  if (tid == 0) {
+    int4* h = reinterpret_cast<int4*>(ts);
+    h[0] = make_int4(s_win[0], s_win[1], s_win[2], s_win[3]);
+    h[1] = make_int4(s_win[4], s_win[5], s_win[6], s_win[7]);
+    reinterpret_cast<int*>(ts)[12] = pl.ok ? 1 : 0;
+  }
+  if (rt > 0) {
+    tile_fence_async_smem();   // the scatter's generic-proxy writes -> visible to the bulk copy
+    __syncwarp();
+    if ((tid & 31) == 0) {
+      tile_bulk_store(ts + kSaveHdrBytes + warp * kSaveWarpBytes, s_plan + warp * kSaveWarpBytes,
+                      (unsigned)rt * 64u);
+      tile_bulk_commit();
+    }
+  }
+}
+
+// Backward from a saved plan: the header -> TilePlan (as tile_prologue<PAIR = true> leaves it);
+// thread 0 requests the value boxes and the warps' weight regions on mbar.
+__device__ __forceinline__ void tile_load_plan(const char* ts, const CUtensorMap* vmap, const Dims& d, int b,
+                                               int m, char* vtile, unsigned row_bytes, char* s_plan,
+                                               unsigned long long* mbar, TilePlan& pl) {
+  constexpr unsigned FULL = 0xffffffffu;
+  const int tid = threadIdx.x, g = tid >> 3;
+  const int4* hb = reinterpret_cast<const int4*>(ts + 128 + g * 32);
+  const int4 b0 = __ldg(hb), b1 = __ldg(hb + 1);
+  const int4 lo4 = __ldg(reinterpret_cast<const int4*>(ts)), hi4 = __ldg(reinterpret_cast<const int4*>(ts) + 1);
+  const int blo[kWinMaxL] = {b0.x, b0.y, b0.z, b0.w}, brows[kWinMaxL] = {b1.x, b1.y, b1.z, b1.w};
+  const int lo[kWinMaxL] = {lo4.x, lo4.y, lo4.z, lo4.w}, hi[kWinMaxL] = {hi4.x, hi4.y, hi4.z, hi4.w};
+  int rt = 0, total = 0;
+  int tlo[kWinMaxL], tbase[kWinMaxL];
+#pragma unroll
+  for (int l = 0; l < kWinMaxL; ++l) {
+    const int wmax = __reduce_max_sync(FULL, brows[l]);
+    pl.blo[l] = blo[l];
+    pl.brows[l] = brows[l];
+    pl.wmax[l] = wmax;
+    pl.wrows[l] = (wmax + 1) & ~1;
+    pl.bpoff[l] = rt;
+    rt += pl.wrows[l];
+    const int rows = hi[l] >= lo[l] ? hi[l] - lo[l] + 1 : 0;
+    tlo[l] = lo[l];
+    tbase[l] = total;
+    total += (rows + kTileBoxRows - 1) / kTileBoxRows * kTileBoxRows;
+  }
+#pragma unroll
+  for (int l = 0; l < kWinMaxL; ++l) {
+    pl.tlo[l] = tlo[l];
+    pl.tbase[l] = tbase[l];
+    pl.trow[l] = brows[l] > 0 ? tbase[l] + blo[l] - tlo[l] : 0;
+  }
+  pl.rt = rt;
+  pl.total = total;
+  pl.ok = true;
+  if (tid == 0 && total > 0) {
+    const int4 r4 = __ldg(reinterpret_cast<const int4*>(ts) + 2);
+    const int rts[4] = {r4.x, r4.y, r4.z, r4.w};
+    tile_mbar_expect_tx(mbar, (unsigned)total * row_bytes + (unsigned)(rts[0] + rts[1] + rts[2] + rts[3]) * 64u);
+    tile_issue_boxes(vmap, d, b, m, tlo, tbase, total, vtile, row_bytes, mbar);
+#pragma unroll
+    for (int w = 0; w < 4; ++w)
+      if (rts[w] > 0)
+        tile_bulk_load(s_plan + w * kSaveWarpBytes, ts + kSaveHdrBytes + w * kSaveWarpBytes,
+                       (unsigned)rts[w] * 64u, mbar);
+  }
+}
+
 template <typename T, int NU>
 struct TileSmem {
   static constexpr int kRowBytes = NU * 8 * 16;                        // D * sizeof(T)
@@ -883,7 +1018,7 @@ msda_fwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
                      const int64_t* __restrict__ shapes, const int64_t* __restrict__ lsi,
                      const T* __restrict__ loc, const T* __restrict__ aw,
                      const int* __restrict__ perm, T* __restrict__ out, Dims d, int nchunks,
-                     TileFront<T> front) {
+                     TileFront<T> front, char* save) {
   using U = Unit<T>;
   using Raw = typename U::Raw;
   using SM = TileSmem<T, NU>;
@@ -913,8 +1048,11 @@ msda_fwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
   }
   float4* Wt = reinterpret_cast<float4*>(s_plan) + tile_wt_base(g);
   TilePlan pl;
-  tile_prologue<T, false, true, FUSED>(&vmap, loc, aw, d, b, m, s_q[g * kWinQ + (j & 3)], s_lvl, s_win, vtile,
-                                       RB, Wt, &s_mbar, pl, &front);
+  // the plan is laid out as the backward wants it (levels padded to even row counts), so that a
+  // saved plan serves both; this kernel's loops stop at wmax
+  tile_prologue<T, true, true, FUSED>(&vmap, loc, aw, d, b, m, s_q[g * kWinQ + (j & 3)], s_lvl, s_win, vtile,
+                                      RB, Wt, &s_mbar, pl, &front);
+  if (save) tile_save_plan(save + (size_t)blockIdx.x * kSaveStride, pl, s_win, s_plan);
   if (!pl.ok) {
     if (FUSED) {
       float* lp = reinterpret_cast<float*>(vtile);
@@ -949,7 +1087,7 @@ msda_fwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
   for (int l = 0; l < kWinMaxL; ++l) {
     const char* vr = vtile + pl.trow[l] * RB + j * 16;
     const float4* wl = Wt + pl.bpoff[l] * kTileWtStride;
-    const int n = pl.wrows[l], nb = pl.brows[l];
+    const int n = pl.wmax[l], nb = pl.brows[l];
 #pragma unroll 2
     for (int i = 0; i < n; ++i) {
       const float4 wv = wl[i * kTileWtStride];
@@ -987,6 +1125,7 @@ msda_fwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
     }
   }
   tile_stamp(7);
+  if (save && (tid & 31) == 0) tile_bulk_wait_read<0>();   // shared memory must outlive the bulk copy's reads
 }
 
 // ------------------------------- backward -----------------------------------
@@ -1001,7 +1140,8 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
                      const T* __restrict__ loc, const T* __restrict__ aw,
                      const T* __restrict__ gout, const int* __restrict__ perm,
                      GV* __restrict__ gvalue, T* __restrict__ gloc, T* __restrict__ gaw, Dims d,
-                     int nchunks, const DetHeader* __restrict__ det, TileFront<T> front) {
+                     int nchunks, const DetHeader* __restrict__ det, TileFront<T> front,
+                     const char* __restrict__ saved) {
   const float gv_scale = det ? (float)det->scale : 1.f;
   using Raw = typename U::Raw;
   constexpr int G = 8;
@@ -1051,8 +1191,15 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
   float4* Wt = reinterpret_cast<float4*>(s_plan) + tile_wt_base(g);
   float* Gs = reinterpret_cast<float*>(Wt);   // the dots G[t][qi] overwrite Wt[t][qi] pair by pair
   TilePlan pl;
-  tile_prologue<T, true, true, FUSED>(&vmap, loc, aw, d, b, m, my_q, s_lvl, s_win, vtile, RB, Wt, &s_mbar, pl,
-                                      &front);
+  // the forward's saved plan of this tile (same sampling points), if there is one and the tile has a
+  // plan at all: windows and merged weights come from the workspace, not from the points
+  const char* ts = saved ? saved + (size_t)blockIdx.x * kSaveStride : nullptr;
+  if (saved) tile_prefetch_saved(saved);
+  if (ts && __ldg(reinterpret_cast<const int*>(ts) + 12) != 0)
+    tile_load_plan(ts, &vmap, d, b, m, vtile, RB, s_plan, &s_mbar, pl);
+  else
+    tile_prologue<T, true, true, FUSED>(&vmap, loc, aw, d, b, m, my_q, s_lvl, s_win, vtile, RB, Wt, &s_mbar, pl,
+                                        &front);
   if (!pl.ok) {
     if (FUSED) {
       // points to shared memory, per-tap body with its per-point gradients to shared memory, then

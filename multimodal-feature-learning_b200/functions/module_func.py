@@ -14,6 +14,7 @@ from torch.autograd import Function
 from torch.autograd.function import once_differentiable
 
 from .. import _lib
+from .. import MultiScaleDeformableAttention as MSDA
 from ..MultiScaleDeformableAttention import _DTYPES, _stream
 from . import ms_deform_attn_func as _f
 
@@ -57,13 +58,16 @@ class MSDeformModuleFunction(Function):
                 ev.record(side)
                 ctx.msda_gv = (gv, ev)
             out = torch.empty((N, Lq, M * D), dtype=value.dtype, device=value.device)
-            ws_bytes = lib.msda_forward_workspace_bytes(N, S, M, D, L, Lq, P, dt, 0)
+            # the tiles' plans travel to the backward with the query order when there will be one
+            fflags = _lib.MSDA_FLAG_SAVE_PLAN if (MSDA.SAVE_PLAN and any(ctx.needs_input_grad)) else 0
+            ctx.msda_fflags = fflags
+            ws_bytes = lib.msda_forward_workspace_bytes(N, S, M, D, L, Lq, P, dt, fflags)
             plan = torch.empty(max(ws_bytes // 4, 1), dtype=torch.int32, device=value.device)
             _lib.check(lib.msda_module_forward(
                 value.data_ptr(), shapes_hw.data_ptr(), lsi.data_ptr(), offsets.data_ptr(), logits.data_ptr(),
                 ref_c.data_ptr(), mask.data_ptr() if mask is not None else None, out.data_ptr(),
                 N, S, M, D, L, Lq, P, rd, dt,
-                _lib.PADDING_MODES[padding_mode], 0, plan.data_ptr(), ws_bytes, _stream(value)))
+                _lib.PADDING_MODES[padding_mode], fflags, plan.data_ptr(), ws_bytes, _stream(value)))
         ctx.save_for_backward(value, shapes_hw, lsi, offsets, logits, ref_c, plan,
                               mask if mask is not None else plan.new_empty(0))
         ctx.has_mask = mask is not None
@@ -79,7 +83,7 @@ class MSDeformModuleFunction(Function):
         rd = ref.shape[-1]
         dt = _DTYPES[value.dtype]
         lib = _lib.load()
-        flags = 0
+        flags = ctx.msda_fflags
         with torch.cuda.device_of(value):
             gv = None
             if ctx.msda_gv is not None:

@@ -55,10 +55,11 @@ class _MSDeformAttnBase(Function):
             ctx.msda_gv = (gv, ev)
         output, plan = MSDA.ms_deform_attn_forward(
             value, value_spatial_shapes, value_level_start_index, sampling_locations,
-            attention_weights, ctx.im2col_step, padding_mode=cls.padding_mode, return_plan=True)
+            attention_weights, ctx.im2col_step, padding_mode=cls.padding_mode, return_plan=True,
+            save_plan=MSDA.SAVE_PLAN and any(ctx.needs_input_grad))
         ctx.save_for_backward(value, value_spatial_shapes, value_level_start_index,
                               sampling_locations, attention_weights)
-        ctx.msda_plan = plan     # time order of the queries (6 KB per batch item at the encoder shape)
+        ctx.msda_plan = plan     # time order of the queries (+ the tiles' saved plans when a backward follows)
         return output
 
     @classmethod

@@ -141,3 +141,23 @@ def test_module_with_and_without_fused_op():
         torch.testing.assert_close(a, b, rtol=2e-3, atol=2e-4 * float(b.abs().max()))
     import pickle
     pickle.loads(pickle.dumps(m.cpu()))          # the caches do not travel
+
+
+@pytest.mark.parametrize("spread", [0.5, 6.0], ids=["tiles", "some_fallback"])
+def test_fused_module_op_saved_plan_on_and_off(spread):
+    """The backward of the fused op from the forward's saved tile plans
+    (MultiScaleDeformableAttention.SAVE_PLAN on) against the same op with it off: grad_offsets / grad_logits bitwise (same
+    merged weights, same dots), grad_value / grad_ref up to the order of their atomics."""
+    from mfl_b200 import MultiScaleDeformableAttention as MSDA
+    c = make(2, [160, 80, 40, 20], 8, 64, torch.float32, 2, seed=41, spread=spread, Lq=277)
+    keep = MSDA.SAVE_PLAN
+    try:
+        MSDA.SAVE_PLAN = True
+        a = run(True, c, "zeros")
+        MSDA.SAVE_PLAN = False
+        b = run(True, c, "zeros")
+    finally:
+        MSDA.SAVE_PLAN = keep
+    assert torch.equal(a[0], b[0])
+    assert torch.equal(a[2], b[2]) and torch.equal(a[3], b[3])
+    assert rel(a[1], b[1]) <= 1e-5 and rel(a[4], b[4]) <= 1e-5

@@ -30,10 +30,12 @@ GRAD_REL_F32 = 1e-4
 BF16_FWD_REL = 2.0 ** -7
 BF16_GRAD_REL = 2e-2
 WIN = _lib.MSDA_FLAG_FORCE_WINDOW
-FAMILY_FLAGS = {"tile": WIN, "window": WIN | _lib.MSDA_FLAG_NO_TILE, "plan": WIN | _lib.MSDA_FLAG_PLAN}
+SAVE = _lib.MSDA_FLAG_SAVE_PLAN
+FAMILY_FLAGS = {"tile": WIN, "window": WIN | _lib.MSDA_FLAG_NO_TILE, "plan": WIN | _lib.MSDA_FLAG_PLAN,
+                "saved": WIN | SAVE}   # saved: the backward starts from the tile plans the forward saved
 
 
-@pytest.fixture(params=["tile", "window", "plan"])
+@pytest.fixture(params=["tile", "window", "plan", "saved"])
 def fam(request):
     return FAMILY_FLAGS[request.param]
 
@@ -46,8 +48,15 @@ def rel_err(a, b):
 
 def run_cuda(inp, padding, flags):
     v, s, l, loc, aw, go = (inp[k] for k in ("value", "shapes", "lsi", "loc", "aw", "grad_out"))
-    out = MSDA.ms_deform_attn_forward(v, s, l, loc, aw, 64, padding_mode=padding, flags=flags)
-    gv, gl, ga = MSDA.ms_deform_attn_backward(v, s, l, loc, aw, go, 64, padding_mode=padding, flags=flags)
+    if flags & SAVE:
+        out, plan = MSDA.ms_deform_attn_forward(v, s, l, loc, aw, 64, padding_mode=padding, flags=flags & ~SAVE,
+                                                return_plan=True, save_plan=True)
+        assert plan is None or plan.msda_saved
+        gv, gl, ga = MSDA.ms_deform_attn_backward(v, s, l, loc, aw, go, 64, padding_mode=padding,
+                                                  flags=flags & ~SAVE, plan=plan)
+    else:
+        out = MSDA.ms_deform_attn_forward(v, s, l, loc, aw, 64, padding_mode=padding, flags=flags)
+        gv, gl, ga = MSDA.ms_deform_attn_backward(v, s, l, loc, aw, go, 64, padding_mode=padding, flags=flags)
     torch.cuda.synchronize()
     return [t.float().cpu().numpy() for t in (out, gv, gl, ga)]
 
@@ -224,3 +233,45 @@ def test_long_query_list_uses_single_cta_sort():
                                             return_plan=True)
     srt = plan[:5000].sort()[0]
     assert torch.equal(srt, torch.arange(5000, device=DEV, dtype=torch.int32))
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("sigma", [0.5, 3.0])
+def test_saved_plan_backward_equals_recomputed_plan(dtype, sigma):
+    """MSDA_FLAG_SAVE_PLAN: the backward that starts from the forward's saved tile plans gives the
+    gradients of the backward that rebuilds them from the points -- grad_sampling_loc and
+    grad_attn_weight bitwise (same weights, same dots), grad_value up to the order of its atomics.
+    sigma = 3 rows: part of the tiles have no plan (per-tap body) and say so in their header.
+    Ragged query count (last tile 37 queries), plan buffer pre-filled with garbage."""
+    T = [256, 128, 64, 32]
+    inp = synthetic.make_inputs(2, 421, 8, 64, 4, [(1, t) for t in T], dtype, DEV, seed=31, dist="model",
+                                value="normal", sigma=sigma)
+    v, s, l, loc, aw, go = (inp[k] for k in ("value", "shapes", "lsi", "loc", "aw", "grad_out"))
+    junk = torch.full((1 << 22,), -1, dtype=torch.int32, device=DEV)   # whatever the allocator hands out next
+    del junk
+    o_s, plan_s = MSDA.ms_deform_attn_forward(v, s, l, loc, aw, 64, return_plan=True, save_plan=True)
+    o_n, plan_n = MSDA.ms_deform_attn_forward(v, s, l, loc, aw, 64, return_plan=True, save_plan=False)
+    assert plan_s.msda_saved and not plan_n.msda_saved and plan_s.numel() > plan_n.numel()
+    assert torch.equal(o_s, o_n)
+    nq = loc.shape[0] * loc.shape[1]
+    assert torch.equal(plan_s[:nq], plan_n[:nq])
+    g_s = MSDA.ms_deform_attn_backward(v, s, l, loc, aw, go, 64, plan=plan_s)
+    g_n = MSDA.ms_deform_attn_backward(v, s, l, loc, aw, go, 64, plan=plan_n)
+    assert torch.equal(g_s[1], g_n[1]) and torch.equal(g_s[2], g_n[2])
+    tol = 1e-5 if dtype == torch.float32 else BF16_GRAD_REL
+    assert rel_err(g_s[0].float().cpu().numpy(), g_n[0].float().cpu().numpy()) <= tol
+    # and once more from the same plan (the backward leaves it untouched)
+    g_r = MSDA.ms_deform_attn_backward(v, s, l, loc, aw, go, 64, plan=plan_s)
+    assert torch.equal(g_r[1], g_s[1]) and torch.equal(g_r[2], g_s[2])
+    # the saved plans are what the backward used: with every tile's weights zeroed (headers kept) the
+    # planned tiles contribute nothing to grad_value
+    if sigma > 1:
+        return
+    tiles = 2 * 8 * ((421 + 63) // 64)
+    stride, hdr = 14976 // 4, 640 // 4
+    base = (nq * 4 + 255) // 256 * 64
+    broken = plan_s.clone()
+    broken.msda_saved = True
+    broken[base:base + tiles * stride].view(tiles, stride)[:, hdr:] = 0
+    g_b = MSDA.ms_deform_attn_backward(v, s, l, loc, aw, go, 64, plan=broken)
+    assert float(g_b[0].float().abs().sum()) < 0.9 * float(g_s[0].float().abs().sum())
