@@ -1160,7 +1160,9 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
   const int m = blockIdx.x % d.M;
   const int t2 = blockIdx.x / d.M;
   const int chunk = t2 % nchunks, b = t2 / nchunks;
+  tile_stamp(0);
   const bool one_d = tile_setup(shapes, lsi, perm, d, b, chunk, s_lvl, s_win, s_q, &s_mbar);
+  tile_stamp(1);
   tile_prefetch_ahead<T>(perm, loc, aw, FUSED ? &front : nullptr, d, nchunks);
   if (!one_d) {
     if (FUSED) __trap();
@@ -1195,9 +1197,11 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
   // plan at all: windows and merged weights come from the workspace, not from the points
   const char* ts = saved ? saved + (size_t)blockIdx.x * kSaveStride : nullptr;
   if (saved) tile_prefetch_saved(saved);
-  if (ts && __ldg(reinterpret_cast<const int*>(ts) + 12) != 0)
+  if (ts && __ldg(reinterpret_cast<const int*>(ts) + 12) != 0) {
+    tile_stamp(2);
     tile_load_plan(ts, &vmap, d, b, m, vtile, RB, s_plan, &s_mbar, pl);
-  else
+    tile_stamp(3);
+  } else
     tile_prologue<T, true, true, FUSED>(&vmap, loc, aw, d, b, m, my_q, s_lvl, s_win, vtile, RB, Wt, &s_mbar, pl,
                                         &front);
   if (!pl.ok) {
@@ -1242,7 +1246,9 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
 #pragma unroll
       for (int c = 0; c < E / 2; ++c) go[q][uu][c] = make_float2(t[2 * c], t[2 * c + 1]);
     }
+  tile_stamp(4);
   if (pl.total > 0) tile_mbar_wait(&s_mbar, 0);
+  tile_stamp(5);
   __shared__ unsigned char s_rowmask[FUSED ? kTileCapRows : 1];
   const bool has_mask = FUSED && front.mask != nullptr;
   if (has_mask)
@@ -1321,6 +1327,11 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
               GvRed<GV>::add4(gp + u * (G * E) + 2 * c, real, dv[u][c].x, dv[u][c].y, dv[u][c + 1].x,
                               dv[u][c + 1].y, gv_scale);
         }
+#ifdef MSDA_TILE_DBG_NODOTS
+#pragma unroll
+        for (int q = 0; q < kWinQ; ++q) s[q] = make_float2(wq[q], 0.f);   // experiment: no value rows, no dots
+        if (false)
+#endif
 #pragma unroll
         for (int u = 0; u < NU; ++u) {
           // this lane's share of <grad_out[q], value row>
@@ -1342,7 +1353,11 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
         gp += MD;
         if (i + r + 1 < nb) vr += RB;
       }
+#ifdef MSDA_TILE_DBG_NOTR
+      const float tot = x[0] + x[1] + x[2] + x[3] + x[4] + x[5] + x[6] + x[7];   // experiment: no shuffles
+#else
       const float tot = transpose_reduce<8>(x, j, 0xffffffffu);
+#endif
       gl[i * (4 * kTileWtStride)] = tot;   // (row i + (j >> 2), query j & 3)
       if (BULK) {
         // the block's two rows, complete in shared memory -> one bulk reduction each, issued by
@@ -1362,6 +1377,7 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
   }
   if (BULK && j == 0) tile_bulk_wait_read<0>();   // shared memory must outlive the reads
   __syncwarp();
+  tile_stamp(6);
 
   // per-point gradients: the points again, the geometry again, the dots
   const bool have_q = my_q >= 0;
@@ -1405,6 +1421,7 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
       WinPts<T>::st(gloc + (grp_me * LP + l * kWinP) * 2, gaw + grp_me * LP + l * kWinP, gx, gy, ga);
   }
   if (FUSED) tile_front_backward<T>(front, d, b, m, my_q, h, fa, foff, fsc, fgx, fga);
+  tile_stamp(7);
 }
 
 }  // namespace msda

@@ -1,6 +1,7 @@
 #!/usr/bin/env python
-"""Phase timeline of the forward tile kernel from a -DMSDA_TILE_TIMING build (variants/timing.so):
-globaltimer stamps of thread 0 of every CTA.  Dev aid."""
+"""Phase timeline of the forward tile kernel (or, with --bwd [--flags 128], of the backward) from a
+-DMSDA_TILE_TIMING build (variants/timing.so, or --lib): globaltimer stamps of thread 0 of every CTA.
+Dev aid."""
 import ctypes
 import os
 import sys
@@ -12,7 +13,13 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from mfl_b200 import _lib  # noqa: E402
 
-_lib.LIB_PATH = os.path.join(ROOT, "variants", "timing.so")
+import argparse
+ap = argparse.ArgumentParser()
+ap.add_argument("--bwd", action="store_true")
+ap.add_argument("--flags", type=int, default=0)
+ap.add_argument("--lib", default=os.path.join(ROOT, "variants", "timing.so"))
+args = ap.parse_args()
+_lib.LIB_PATH = os.path.abspath(args.lib)
 import bench  # noqa: E402
 from mfl_b200 import synthetic  # noqa: E402
 
@@ -20,8 +27,13 @@ dev = torch.device("cuda", 0)
 ring = [synthetic.make_workload("ENC", torch.float32, dev, seed=1234 + r, dist="model", value="normal") for r in range(4)]
 bufs = [bench.OpBuffers(i, "zeros", 0) for i in ring]
 st = torch.cuda.current_stream().cuda_stream
+for b_ in bufs:
+    b_.set_flags(args.flags)
 for i in range(9):
     bufs[i % 4].fwd(st)
+    if args.bwd:
+        bufs[i % 4].zero()
+        bufs[i % 4].bwd(st)
 torch.cuda.synchronize()
 lib = _lib.load()
 n = 3072
@@ -30,6 +42,9 @@ lib.msda_debug_tile_times.argtypes = [ctypes.c_void_p, ctypes.c_int]
 assert lib.msda_debug_tile_times(host, 8 * n) == 0
 t = np.array(host, dtype=np.float64).reshape(n, 8)
 t0 = t[:, 0].min()
+if args.bwd:
+    print("BACKWARD kernel, flags", args.flags, "(phases: setup | grad_out requested, points+geometry or saved header | "
+          "barrier / issue | scatter or nothing | wait for boxes | row loops | epilogue)")
 names = ["start->setup(perm)", "setup->geometry done", "geometry->barrier", "barrier->plan built(TMA issued)",
          "plan->V landed", "V->rows done", "rows->stored"]
 d = np.diff(t, axis=1)
