@@ -492,7 +492,9 @@ def secondary_records(args, dev, hbm_peak, dist_sync, ring_enc):
     rec("ENC_f32_no_tile(row windows, round 1 default)", ring_enc, _lib.MSDA_FLAG_NO_TILE)
     rec("ENC_f32_per_tap", ring_enc, _lib.MSDA_FLAG_NO_WINDOW)
     rec("ENC_f32_plan_apply_split", ring_enc, _lib.MSDA_FLAG_PLAN)
-    rec("ENC_f32_saved_plan(backward starts from the forward's tile plans)", ring_enc, _lib.MSDA_FLAG_SAVE_PLAN)
+    from mfl_b200 import MultiScaleDeformableAttention as MSDA
+    if MSDA.saved_plans_supported():      # only in a -DMSDA_TILE_SAVED_PLANS=1 build (an experiment)
+        rec("ENC_f32_saved_plan(backward starts from the forward's tile plans)", ring_enc, _lib.MSDA_FLAG_SAVE_PLAN)
     rec("ENC_f32_zero_fill_serial", ring_enc, 0, overlap_zero=False)
     out["kernel_to_beat"] = time_kernel_to_beat(ring_enc, 5, 2)
     del ring_enc

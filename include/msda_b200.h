@@ -121,7 +121,11 @@ typedef enum {
                                       the saved plan instead of the sampling points.  Set it on
                                       both calls or on neither; a forward workspace too small for
                                       the plans just keeps the query order (then do not set the
-                                      flag on the backward).  Same results */
+                                      flag on the backward).  Same results.  An EXPERIMENT
+                                      (measured: no gain): honoured only by a
+                                      library built with -DMSDA_TILE_SAVED_PLANS=1; the default build
+                                      ignores the flag on both calls (msda_forward_workspace_bytes
+                                      then reports the same size with and without it) */
 /* bits 8..19: queries-per-tile multiplier override for the vectorised kernels
  * (0 = heuristic); a tuning knob, results do not depend on it. */
 #define MSDA_FLAG_QTILE(k) (((unsigned)(k) & 0xfffu) << 8)

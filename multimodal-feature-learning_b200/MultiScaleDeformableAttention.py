@@ -60,8 +60,16 @@ def _stream(t):
 # True: the plan a forward returns for its backward also holds every tile's windows and merged
 # weights (MSDA_FLAG_SAVE_PLAN, ~1.8 KB per query at M = 8) and the backward starts from them instead
 # of the sampling points.  Same results; measured on B200 it does not pay (forward + 2 us for the
-# stores, backward unchanged: DESIGN.md section 6), so only the query order (4 B per query) is kept.
+# stores, backward unchanged: DESIGN.md section 6), so only the query order (4 B per query) is kept;
+# the default build of the library ignores the flag altogether (-DMSDA_TILE_SAVED_PLANS=1 enables it).
 SAVE_PLAN = False
+
+
+def saved_plans_supported():
+    """Whether libmsda_b200.so was built with -DMSDA_TILE_SAVED_PLANS=1."""
+    lib = _lib.load()
+    a = lib.msda_forward_workspace_bytes(2, 1500, 8, 64, 4, 1500, 4, 0, _lib.MSDA_FLAG_SAVE_PLAN)
+    return a != lib.msda_forward_workspace_bytes(2, 1500, 8, 64, 4, 1500, 4, 0, 0)
 
 
 def ms_deform_attn_forward(value, spatial_shapes, level_start_index, sampling_loc, attn_weight,
@@ -85,6 +93,9 @@ def ms_deform_attn_forward(value, spatial_shapes, level_start_index, sampling_lo
     with torch.cuda.device_of(value):
         out = torch.empty((N, Lq, M * D), dtype=value.dtype, device=value.device)
         ws_bytes = lib.msda_forward_workspace_bytes(N, S, M, D, L, Lq, P, dt, flags)
+        if (flags & _lib.MSDA_FLAG_SAVE_PLAN) and ws_bytes == lib.msda_forward_workspace_bytes(
+                N, S, M, D, L, Lq, P, dt, flags & ~_lib.MSDA_FLAG_SAVE_PLAN):
+            flags &= ~_lib.MSDA_FLAG_SAVE_PLAN     # this build of the library does not save plans
         ws = torch.empty(ws_bytes // 4, dtype=torch.int32, device=value.device) if ws_bytes else None
         _lib.check(lib.msda_forward_ex(
             value.data_ptr(), spatial_shapes.data_ptr(), level_start_index.data_ptr(),

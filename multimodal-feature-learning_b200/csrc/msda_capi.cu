@@ -350,7 +350,8 @@ inline size_t save_ws_bytes(int64_t N, int64_t M, int64_t Lq) {
   return tile_plan_bytes(N, Lq) + plan_tiles(N, M, Lq) * (size_t)kSaveStride;
 }
 inline bool save_applies(unsigned flags) {
-  return MSDA_TILE_WT_INTERLEAVE != 0 && (flags & MSDA_FLAG_SAVE_PLAN) && !(flags & MSDA_FLAG_PLAN);
+  return MSDA_TILE_SAVED_PLANS != 0 && MSDA_TILE_WT_INTERLEAVE != 0 && (flags & MSDA_FLAG_SAVE_PLAN) &&
+         !(flags & MSDA_FLAG_PLAN);
 }
 inline char* plan_of(void* workspace, int64_t N, int64_t Lq) {
   return (char*)workspace + tile_plan_bytes(N, Lq);

@@ -56,6 +56,11 @@ namespace msda {
 #ifndef MSDA_TILE_RED_GROUP
 #define MSDA_TILE_RED_GROUP 1       // 1: backward issues the reds of a row (all units) under ONE branch
 #endif
+#ifndef MSDA_TILE_SAVED_PLANS
+#define MSDA_TILE_SAVED_PLANS 0     // 1: MSDA_FLAG_SAVE_PLAN is honoured (forward saves the tiles' plans, backward
+                                   // starts from them).  Same results, no gain measured, and the extra branch
+                                   // in the backward kernel slows its per-tap body by 38 %: off
+#endif
 #ifndef MSDA_TILE_FWD_CTAS
 #define MSDA_TILE_FWD_CTAS 4
 #endif
@@ -1052,6 +1057,9 @@ msda_fwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
   // saved plan serves both; this kernel's loops stop at wmax
   tile_prologue<T, true, true, FUSED>(&vmap, loc, aw, d, b, m, s_q[g * kWinQ + (j & 3)], s_lvl, s_win, vtile,
                                       RB, Wt, &s_mbar, pl, &front);
+#if !MSDA_TILE_SAVED_PLANS
+  save = nullptr;
+#endif
   if (save) tile_save_plan(save + (size_t)blockIdx.x * kSaveStride, pl, s_win, s_plan);
   if (!pl.ok) {
     if (FUSED) {
@@ -1195,8 +1203,12 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
   TilePlan pl;
   // the forward's saved plan of this tile (same sampling points), if there is one and the tile has a
   // plan at all: windows and merged weights come from the workspace, not from the points
+#if MSDA_TILE_SAVED_PLANS
   const char* ts = saved ? saved + (size_t)blockIdx.x * kSaveStride : nullptr;
-  if (saved) tile_prefetch_saved(saved);
+#else
+  const char* ts = nullptr;
+#endif
+  if (ts) tile_prefetch_saved(saved);
   if (ts && __ldg(reinterpret_cast<const int*>(ts) + 12) != 0) {
     tile_stamp(2);
     tile_load_plan(ts, &vmap, d, b, m, vtile, RB, s_plan, &s_mbar, pl);

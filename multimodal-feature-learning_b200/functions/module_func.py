@@ -59,7 +59,8 @@ class MSDeformModuleFunction(Function):
                 ctx.msda_gv = (gv, ev)
             out = torch.empty((N, Lq, M * D), dtype=value.dtype, device=value.device)
             # the tiles' plans travel to the backward with the query order when there will be one
-            fflags = _lib.MSDA_FLAG_SAVE_PLAN if (MSDA.SAVE_PLAN and any(ctx.needs_input_grad)) else 0
+            fflags = _lib.MSDA_FLAG_SAVE_PLAN if (MSDA.SAVE_PLAN and any(ctx.needs_input_grad)
+                                                  and MSDA.saved_plans_supported()) else 0
             ctx.msda_fflags = fflags
             ws_bytes = lib.msda_forward_workspace_bytes(N, S, M, D, L, Lq, P, dt, fflags)
             plan = torch.empty(max(ws_bytes // 4, 1), dtype=torch.int32, device=value.device)

@@ -149,6 +149,8 @@ def test_fused_module_op_saved_plan_on_and_off(spread):
     (MultiScaleDeformableAttention.SAVE_PLAN on) against the same op with it off: grad_offsets / grad_logits bitwise (same
     merged weights, same dots), grad_value / grad_ref up to the order of their atomics."""
     from mfl_b200 import MultiScaleDeformableAttention as MSDA
+    if not MSDA.saved_plans_supported():
+        pytest.skip("libmsda_b200.so built without -DMSDA_TILE_SAVED_PLANS=1 (the default: DESIGN.md section 6, 5h)")
     c = make(2, [160, 80, 40, 20], 8, 64, torch.float32, 2, seed=41, spread=spread, Lq=277)
     keep = MSDA.SAVE_PLAN
     try:

@@ -37,6 +37,8 @@ FAMILY_FLAGS = {"tile": WIN, "window": WIN | _lib.MSDA_FLAG_NO_TILE, "plan": WIN
 
 @pytest.fixture(params=["tile", "window", "plan", "saved"])
 def fam(request):
+    if request.param == "saved" and not MSDA.saved_plans_supported():
+        pytest.skip("libmsda_b200.so built without -DMSDA_TILE_SAVED_PLANS=1 (the default: DESIGN.md section 6, 5h)")
     return FAMILY_FLAGS[request.param]
 
 
@@ -243,6 +245,8 @@ def test_saved_plan_backward_equals_recomputed_plan(dtype, sigma):
     grad_attn_weight bitwise (same weights, same dots), grad_value up to the order of its atomics.
     sigma = 3 rows: part of the tiles have no plan (per-tap body) and say so in their header.
     Ragged query count (last tile 37 queries), plan buffer pre-filled with garbage."""
+    if not MSDA.saved_plans_supported():
+        pytest.skip("libmsda_b200.so built without -DMSDA_TILE_SAVED_PLANS=1 (the default: DESIGN.md section 6, 5h)")
     T = [256, 128, 64, 32]
     inp = synthetic.make_inputs(2, 421, 8, 64, 4, [(1, t) for t in T], dtype, DEV, seed=31, dist="model",
                                 value="normal", sigma=sigma)
