@@ -41,7 +41,8 @@ namespace msda {
 #define MSDA_TILE_WARPS 4
 #endif
 #ifndef MSDA_TILE_CAP
-#define MSDA_TILE_CAP 152
+#define MSDA_TILE_CAP 128           // value rows per tile.  152 -> 128 (32 KB at fp32): 4 CTAs leave ~35 KB of L1
+                                   // for the global loads; forward 55.8 -> 53.8 us, backward (4 CTAs) 96.0 -> 90.0
 #endif
 #ifndef MSDA_TILE_BLK
 #define MSDA_TILE_BLK 56
@@ -65,7 +66,10 @@ namespace msda {
 #define MSDA_TILE_FWD_CTAS 4
 #endif
 #ifndef MSDA_TILE_BWD_CTAS
-#define MSDA_TILE_BWD_CTAS 3
+#define MSDA_TILE_BWD_CTAS 4
+#endif
+#ifndef MSDA_TILE_BWD_CTAS_BF16
+#define MSDA_TILE_BWD_CTAS_BF16 4
 #endif
 constexpr int kTileWarps = MSDA_TILE_WARPS;
 constexpr int kTileThreads = kTileWarps * 32;
@@ -1141,8 +1145,13 @@ msda_fwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
 // unit and lane of a block, 4.7 rows per query in time order); the dots <grad_out, value row>
 // are transpose-reduced over the 8 lanes for two rows at a time and stored over the weights;
 // the epilogue reads the points again (L2) and forms grad_attn_weight / grad_sampling_loc.
+// CTAs per SM the backward is compiled for (4 = 128 registers; with 152-row value tiles the fp32
+// kernel was faster at 3 -- no L1 left at 4 --, the bf16 one, whose tile is half the bytes, at 4)
+template <typename T>
+struct TileBwdCtas { static constexpr int value = std::is_same<T, __nv_bfloat16>::value ? MSDA_TILE_BWD_CTAS_BF16 : MSDA_TILE_BWD_CTAS; };
+
 template <typename T, int NU, typename GV = float, typename U = Unit<T>, bool FUSED = false>
-__global__ void __launch_bounds__(kTileThreads, MSDA_TILE_BWD_CTAS)
+__global__ void __launch_bounds__(kTileThreads, TileBwdCtas<T>::value)
 msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restrict__ value,
                      const int64_t* __restrict__ shapes, const int64_t* __restrict__ lsi,
                      const T* __restrict__ loc, const T* __restrict__ aw,
