@@ -65,6 +65,9 @@ namespace msda {
 #ifndef MSDA_TILE_FWD_CTAS
 #define MSDA_TILE_FWD_CTAS 4
 #endif
+#ifndef MSDA_TILE_FWD_CTAS_BF16
+#define MSDA_TILE_FWD_CTAS_BF16 5
+#endif
 #ifndef MSDA_TILE_BWD_CTAS
 #define MSDA_TILE_BWD_CTAS 4
 #endif
@@ -1021,8 +1024,13 @@ constexpr size_t tile_bwd_smem() {
 }
 
 // ------------------------------- forward ------------------------------------
+// CTAs per SM the forward is compiled for: 4 at fp32 (48 KB of shared memory each), 5 for bf16 rows (half
+// the tile bytes; 96 registers, no spills: ENC 49.6 -> 47.6 us, MM_AV 45.5 -> 35.2 us)
+template <typename T>
+struct TileFwdCtas { static constexpr int value = std::is_same<T, __nv_bfloat16>::value ? MSDA_TILE_FWD_CTAS_BF16 : MSDA_TILE_FWD_CTAS; };
+
 template <typename T, int NU, bool FUSED = false>
-__global__ void __launch_bounds__(kTileThreads, MSDA_TILE_FWD_CTAS)
+__global__ void __launch_bounds__(kTileThreads, TileFwdCtas<T>::value)
 msda_fwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restrict__ value,
                      const int64_t* __restrict__ shapes, const int64_t* __restrict__ lsi,
                      const T* __restrict__ loc, const T* __restrict__ aw,
