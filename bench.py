@@ -534,6 +534,10 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        if args.train_step:
+            # the training-step record also replays the step as a CUDA graph with the all-reduce inside:
+            # NCCL's watchdog polls events, which is illegal during a capture
+            os.environ["TORCH_NCCL_ASYNC_ERROR_HANDLING"] = "0"
         dist.init_process_group("nccl", device_id=dev)
 
     def dist_sync():

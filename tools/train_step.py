@@ -237,6 +237,60 @@ def bench_record(dev, world, rank, steps=10, warmup=3, batch=16, layers=6):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ar_ms = float(t)
     ms_step = float(ms) / steps
+    # the eager loss keeps its autograd graph alive, AccumulateGrad nodes bound to the stream of the eager
+    # steps included: they must be gone before a capture on another stream reuses the parameters
+    loss_val = float(loss.detach())
+    del loss
+
+    # the same step replayed as ONE CUDA graph (forward + backward + all-reduce + clip + AdamW): the eager
+    # step is bound by the host's launch rate (8 ranks share the box's cores), the replay is not
+    graph_ms = None
+    if os.environ.get("TORCH_NCCL_ASYNC_ERROR_HANDLING", "") == "0" or world == 1:
+        opt_g = torch.optim.AdamW(model.parameters(), lr=1e-4, weight_decay=1e-4, fused=True, capturable=True)
+
+        def body():
+            flat.zero_()
+            l_ = model(src, pos, enc_ref, T, lsi).float().pow(2).mean()
+            l_.backward()
+            if world > 1:
+                dist.all_reduce(flat, op=dist.ReduceOp.AVG)
+            torch.nn.utils.clip_grad_norm_(model.parameters(), 0.1, foreach=True)
+            opt_g.step()
+            return l_
+
+        side = torch.cuda.Stream()
+        torch.cuda.synchronize()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                body()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            body()
+        for _ in range(warmup):
+            graph.replay()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        for _ in range(steps):
+            graph.replay()
+        g1.record()
+        torch.cuda.synchronize()
+        gm = torch.tensor([g0.elapsed_time(g1)], device=dev)
+        if world > 1:
+            dist.all_reduce(gm, op=dist.ReduceOp.MAX)
+        graph_ms = float(gm) / steps
+        # the captured graph holds references into the communicator: drop it before the group goes away
+        torch.cuda.synchronize()
+        graph.reset()
+        del graph
+        if world > 1:
+            dist.barrier()
+    # (the profiled step comes last: a capture after a profiler session fails)
     share = op_share(step) if rank == 0 else (step(), None, None, None)[1:]
     rec = {"metric": "configs[4] training step (6+6-layer deformable transformer, 39.4 M parameters + query "
                      "embedding), eager, flat NCCL gradient all-reduce", "samples_per_s": batch * world / ms_step * 1e3,
@@ -244,7 +298,9 @@ def bench_record(dev, world, rank, steps=10, warmup=3, batch=16, layers=6):
            "allreduce_bytes": n_params * 4, "allreduce_ms": ar_ms,
            "allreduce_busbw_GBps": (2.0 * (world - 1) / world * n_params * 4 / (ar_ms * 1e-3) / 1e9) if ar_ms else None,
            "collective": "ncclAllReduce (avg) of one flat fp32 buffer over NVLink 5 / NVSwitch" if world > 1 else None,
-           "loss": float(loss.detach())}
+           "loss": loss_val,
+           "cuda_graph_ms_per_step": graph_ms,
+           "cuda_graph_samples_per_s": (batch * world / graph_ms * 1e3) if graph_ms else None}
     if rank == 0 and share and share[0] is not None:
         rec.update(op_share_of_gpu_time=share[0], op_us_per_step=share[1], gpu_us_per_step=share[2],
                    op_launches_per_step=share[3])
