@@ -237,6 +237,14 @@ inline bool tile_applies(const Dims& d, int dtype, unsigned flags) {
   if (!win_applies(d, dtype, flags)) return false;
   if ((int64_t)d.N * d.S >= (int64_t(1) << 31) || (int64_t)d.N * d.S < kTileBoxRows) return false;
   if ((int64_t)d.N * d.M * ((d.Lq + kTileQ - 1) / kTileQ) >= (int64_t(1) << 31)) return false;
+  // Queries much sparser in time than the value rows (audio tokens over the video memory of the
+  // multimodal encoder: 300 queries on 1200 rows): the 64 time-adjacent queries of a tile would
+  // span ~ 64 * S / Lq (+ ~6 per level) rows, beyond the tile, and every tile would run the per-tap
+  // body.  The row-window kernels, whose unit is the 4-query block, take such calls (measured at
+  // MM_AV: step 0.225 of the roofline against 0.166).  MSDA_FLAG_FORCE_WINDOW keeps the tiles.
+  if (!(flags & MSDA_FLAG_FORCE_WINDOW) &&
+      (int64_t)kTileQ * d.S > (int64_t)(kTileCapRows - 6 * d.L) * d.Lq)
+    return false;
   return true;
 }
 
