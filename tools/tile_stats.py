@@ -22,7 +22,7 @@ def main():
     ap.add_argument("--N", type=int, default=2)
     ap.add_argument("--tileq", type=int, default=64)
     ap.add_argument("--bins", type=int, default=4096)
-    ap.add_argument("--cap", type=int, default=152)
+    ap.add_argument("--cap", type=int, default=128)
     ap.add_argument("--blkcap", type=int, default=56)
     ap.add_argument("--box", type=int, default=8)
     ap.add_argument("--nosort", action="store_true")
