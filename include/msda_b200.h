@@ -126,6 +126,10 @@ typedef enum {
                                       library built with -DMSDA_TILE_SAVED_PLANS=1; the default build
                                       ignores the flag on both calls (msda_forward_workspace_bytes
                                       then reports the same size with and without it) */
+#define MSDA_FLAG_PERSIST (1u << 20) /* msda_forward_ex, fp32 CTA-tile shape class: the forward tile kernel
+                                      in its persistent form (one CTA per resident slot walks tiles and
+                                      holds the next tile's query list and points ahead of time).  Same
+                                      results; an experiment */
 /* bits 8..19: queries-per-tile multiplier override for the vectorised kernels
  * (0 = heuristic); a tuning knob, results do not depend on it. */
 #define MSDA_FLAG_QTILE(k) (((unsigned)(k) & 0xfffu) << 8)

@@ -23,6 +23,7 @@ MSDA_FLAG_DETERMINISTIC = 16
 MSDA_FLAG_NO_TILE = 32
 MSDA_FLAG_PLAN = 64
 MSDA_FLAG_SAVE_PLAN = 128
+MSDA_FLAG_PERSIST = 1 << 20   # (bits 8..19 are the QTILE override)
 ABI_VERSION = 2
 
 

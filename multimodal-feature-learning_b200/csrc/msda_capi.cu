@@ -374,6 +374,28 @@ int launch_plan(const int64_t* shapes, const int64_t* lsi, const void* loc, cons
                     (const T*)aw, perm, plan, d, nchunks);
 }
 
+// persistent form of the forward tile kernel (fp32): one CTA per resident slot, walking tiles
+template <int NU>
+int launch_fwd_tile_persist(const void* value, const int64_t* shapes, const int64_t* lsi, const void* loc,
+                            const void* aw, const int* perm, void* out, const Dims& d, int dtype,
+                            cudaStream_t st, bool after_sort) {
+  static std::atomic<unsigned long long> attr_done{0};
+  CUtensorMap map;
+  if (!tile_value_map(&map, value, dtype, d)) return MSDA_ERR_NO_TMA;
+  auto kern = msda_fwd_tile_persist_kernel<NU>;
+  constexpr size_t smem = TileSmem<float, NU>::kBytes;
+  const int rc = tile_smem_attr(kern, smem, attr_done);
+  if (rc != MSDA_OK) return rc;
+  const int nchunks = (d.Lq + kTileQ - 1) / kTileQ;
+  const long long tiles = (long long)d.N * d.M * nchunks;
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const long long slots = (long long)sms * MSDA_TILE_FWD_CTAS;
+  return launch_pdl(kern, (unsigned)(tiles < slots ? tiles : slots), kTileThreads, smem, st, after_sort, map,
+                    (const float*)value, shapes, lsi, (const float*)loc, (const float*)aw, perm, (float*)out, d,
+                    nchunks, (int)tiles);
+}
+
 // persistent apply kernels: two CTAs per SM
 inline int apply_grid(long long tiles) {
   int dev = 0, sms = 148;
@@ -668,7 +690,12 @@ int msda_forward_ex(const void* value, const int64_t* spatial_shapes, const int6
                          (reinterpret_cast<uintptr_t>(workspace) & 127u) == 0
                      ? (char*)workspace + tile_plan_bytes(N, Lq)
                      : nullptr;
-    if (dtype == MSDA_BF16)
+    if ((flags & MSDA_FLAG_PERSIST) && dtype == MSDA_F32 && !save)
+      r = D == 64 ? launch_fwd_tile_persist<2>(value, spatial_shapes, level_start_index, sampling_loc,
+                                               attn_weight, perm, output, d, dtype, st, true)
+                  : launch_fwd_tile_persist<1>(value, spatial_shapes, level_start_index, sampling_loc,
+                                               attn_weight, perm, output, d, dtype, st, true);
+    else if (dtype == MSDA_BF16)
       r = launch_fwd_tile<__nv_bfloat16, 1>(value, spatial_shapes, level_start_index, sampling_loc,
                                             attn_weight, perm, output, d, dtype, st, true,
                                             TileFront<__nv_bfloat16>(), save);

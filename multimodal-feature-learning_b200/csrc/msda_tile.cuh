@@ -637,13 +637,15 @@ __device__ __forceinline__ void tile_issue_boxes(const CUtensorMap* vmap, const 
 // PAIR: row loops run over pairs of rows (backward): every level of a plan is padded to an even
 // row count.
 // On return (plan.ok) the block's weights are in Wt, the value boxes are in flight on mbar.
-template <typename T, bool PAIR, bool ISSUE = true, bool FUSED = false>
+// PRE: the thread's points were loaded by the caller (persistent kernel: a tile ahead), pre[i] = (x, y, a).
+template <typename T, bool PAIR, bool ISSUE = true, bool FUSED = false, bool PRE = false>
 __device__ __forceinline__ void tile_prologue(const CUtensorMap* vmap, const T* __restrict__ loc,
                                               const T* __restrict__ aw, const Dims& d, int b, int m,
                                               int q, const int* s_lvl, int* s_win, char* vtile,
                                               unsigned row_bytes, float4* Wt,
                                               unsigned long long* mbar, TilePlan& pl,
-                                              const TileFront<T>* front = nullptr) {
+                                              const TileFront<T>* front = nullptr,
+                                              const float (*pre)[3][4] = nullptr) {
   constexpr unsigned FULL = 0xffffffffu;
   const int tid = threadIdx.x, j = tid & 7, qi = j & 3, h = j >> 2;
   const int gbase = (tid & 31) & ~7;
@@ -668,6 +670,9 @@ __device__ __forceinline__ void tile_prologue(const CUtensorMap* vmap, const T* 
     if (FUSED) {
 #pragma unroll
       for (int p = 0; p < 4; ++p) { x[p] = fx[i][p]; y[p] = fy[i][p]; a[p] = fa[i][p]; }
+    } else if (PRE) {
+#pragma unroll
+      for (int p = 0; p < 4; ++p) { x[p] = pre[i][0][p]; y[p] = pre[i][1][p]; a[p] = pre[i][2][p]; }
     } else {
       WinPts<T>::ld(loc + (grp * LP + ls * kWinP) * 2, aw + grp * LP + ls * kWinP, x, y, a);
     }
@@ -1146,6 +1151,162 @@ msda_fwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
   }
   tile_stamp(7);
   if (save && (tid & 31) == 0) tile_bulk_wait_read<0>();   // shared memory must outlive the bulk copy's reads
+}
+
+// ------------------------- forward, persistent form (experiment) --------------------------
+// One CTA walks tiles blockIdx.x, + gridDim.x, ...  While it works on a tile it already holds the
+// NEXT tile's query list (shared memory, double buffered) and, from the middle of the prologue on, the
+// next tile's sampling points in registers -- the two dependent global round trips at the head of a
+// tile (perm, then points) are off its critical path.  fp32, unfused front-end; same results as
+// msda_fwd_tile_kernel (same prologue, same row loops).  MSDA_FLAG_PERSIST.
+template <int NU>
+__global__ void __launch_bounds__(kTileThreads, MSDA_TILE_FWD_CTAS)
+msda_fwd_tile_persist_kernel(const __grid_constant__ CUtensorMap vmap, const float* __restrict__ value,
+                             const int64_t* __restrict__ shapes, const int64_t* __restrict__ lsi,
+                             const float* __restrict__ loc, const float* __restrict__ aw,
+                             const int* __restrict__ perm, float* __restrict__ out, Dims d, int nchunks,
+                             int ntiles) {
+  using T = float;
+  using U = Unit<T>;
+  using Raw = typename U::Raw;
+  using SM = TileSmem<T, NU>;
+  constexpr int G = 8;
+  constexpr int E = U::E;
+  constexpr int RB = SM::kRowBytes;
+  __shared__ int s_lvl[3 * kWinMaxL];
+  __shared__ int s_win2[2][2 * kWinMaxL];
+  __shared__ int s_q2[2][kTileQ];
+  __shared__ __align__(8) unsigned long long s_mbar;
+  extern __shared__ __align__(128) char s_raw[];
+  char* vtile = s_raw;
+  char* s_plan = vtile + SM::kValueBytes;
+
+  const int tid = threadIdx.x, g = tid >> 3, j = tid & 7, qi = j & 3, h = j >> 2;
+  const int LP = d.L * kWinP;
+  if (tid < 2 * kWinMaxL) {
+    s_win2[0][tid] = tid < kWinMaxL ? kTileBig : -kTileBig;
+    s_win2[1][tid] = tid < kWinMaxL ? kTileBig : -kTileBig;
+  }
+  if (tid == 0) tile_mbar_init(&s_mbar, 1);
+  tile_grid_wait();
+  auto tile_coords = [&](int tile, int& b, int& m, int& chunk) {
+    m = tile % d.M;
+    const int t2 = tile / d.M;
+    chunk = t2 % nchunks;
+    b = t2 / nchunks;
+  };
+  auto stage_queries = [&](int tile, int* sq) {   // threads 0..63: the tile's query list
+    if (tid < kTileQ) {
+      int b, m, chunk;
+      tile_coords(tile, b, m, chunk);
+      const int pos = chunk * kTileQ + tid;
+      sq[tid] = pos < d.Lq ? tile_ld_dep(perm + (size_t)b * d.Lq + pos) : -1;
+    }
+  };
+  // the thread's points of a tile: (x, y, a) of 4 points at levels h and h + 2
+  auto load_points = [&](int tile, int q, float (&pt)[2][3][4]) {
+    int b, m, chunk;
+    tile_coords(tile, b, m, chunk);
+    const size_t grp = ((size_t)b * d.Lq + (q >= 0 ? q : 0)) * d.M + m;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const int l = h + 2 * i, ls = l < d.L ? l : 0;
+      WinPts<T>::ld(loc + (grp * LP + ls * kWinP) * 2, aw + grp * LP + ls * kWinP, pt[i][0], pt[i][1], pt[i][2]);
+    }
+  };
+  int tile = blockIdx.x;
+  stage_queries(tile, s_q2[0]);
+  const bool one_d = win_stage_levels(shapes, lsi, d.L, s_lvl);   // barrier: s_q2[0], s_win2, mbar visible
+  if (!one_d) {
+    for (int it = 0; tile < ntiles; tile += gridDim.x, ++it) {
+      int b, m, chunk;
+      tile_coords(tile, b, m, chunk);
+      if (it > 0) { stage_queries(tile, s_q2[0]); __syncthreads(); }
+      tile_fallback_fwd<T, NU, 4>(value, loc, aw, out, d, b, m, s_lvl, s_plan, s_q2[0]);
+      __syncthreads();
+    }
+    return;
+  }
+  float pts[2][3][4];
+  load_points(tile, s_q2[0][g * kWinQ + qi], pts);
+  float4* Wt = reinterpret_cast<float4*>(s_plan) + tile_wt_base(g);
+  unsigned phase = 0;
+  for (int it = 0; tile < ntiles; ++it) {
+    const int cur = it & 1, next = tile + (int)gridDim.x;
+    int b, m, chunk;
+    tile_coords(tile, b, m, chunk);
+    int* s_q = s_q2[cur];
+    int* s_win = s_win2[cur];
+    if (next < ntiles) stage_queries(next, s_q2[cur ^ 1]);   // visible after the prologue's barrier
+    TilePlan pl;
+    tile_prologue<T, true, true, false, true>(&vmap, loc, aw, d, b, m, s_q[g * kWinQ + qi], s_lvl, s_win, vtile, RB,
+                                              Wt, &s_mbar, pl, nullptr, pts);
+    // the other window buffer is free again (its readers passed the previous tile's last barrier)
+    if (tid < 2 * kWinMaxL) s_win2[cur ^ 1][tid] = tid < kWinMaxL ? kTileBig : -kTileBig;
+    // next tile's points: requested now, used in the next iteration
+    float nxt[2][3][4];
+    if (next < ntiles) load_points(next, s_q2[cur ^ 1][g * kWinQ + qi], nxt);
+    if (!pl.ok) {
+      tile_fallback_fwd<T, NU, 2>(value, loc, aw, out, d, b, m, s_lvl, s_plan, s_q);
+    } else {
+      if (pl.total > 0) { tile_mbar_wait(&s_mbar, phase); phase ^= 1u; }
+      float2 acc[kWinQ][NU][E / 2];
+#pragma unroll
+      for (int q = 0; q < kWinQ; ++q)
+#pragma unroll
+        for (int uu = 0; uu < NU; ++uu)
+#pragma unroll
+          for (int c = 0; c < E / 2; ++c) acc[q][uu][c] = make_float2(0.f, 0.f);
+#pragma unroll
+      for (int l = 0; l < kWinMaxL; ++l) {
+        const char* vr = vtile + pl.trow[l] * RB + j * 16;
+        const float4* wl = Wt + pl.bpoff[l] * kTileWtStride;
+        const int n = pl.wmax[l], nb = pl.brows[l];
+#pragma unroll 2
+        for (int i = 0; i < n; ++i) {
+          const float4 wv = wl[i * kTileWtStride];
+          const float wq[kWinQ] = {wv.x, wv.y, wv.z, wv.w};
+#pragma unroll
+          for (int uu = 0; uu < NU; ++uu) {
+            Raw raw[U::RW];
+            tile_lds<U>(vr + uu * (G * 16), raw);
+            float v[E];
+            U::unpack_raw(raw, v);
+#pragma unroll
+            for (int q = 0; q < kWinQ; ++q) {
+              const float2 w2 = make_float2(wq[q], wq[q]);
+#pragma unroll
+              for (int c = 0; c < E / 2; ++c)
+                acc[q][uu][c] = __ffma2_rn(w2, make_float2(v[2 * c], v[2 * c + 1]), acc[q][uu][c]);
+            }
+          }
+          if (i + 1 < nb) vr += RB;
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < kWinQ; ++q) {
+        const int qq = s_q[g * kWinQ + q];
+        if (qq >= 0) {
+          T* og = out + (((size_t)b * d.Lq + qq) * d.M + m) * d.D + j * E;
+#pragma unroll
+          for (int uu = 0; uu < NU; ++uu) {
+            float o[E];
+#pragma unroll
+            for (int c = 0; c < E / 2; ++c) { o[2 * c] = acc[q][uu][c].x; o[2 * c + 1] = acc[q][uu][c].y; }
+            U::st_stream(og + uu * (G * E), o);
+          }
+        }
+      }
+    }
+    __syncthreads();   // the tile, the weights and this query list may be overwritten
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+      for (int k = 0; k < 3; ++k)
+#pragma unroll
+        for (int p = 0; p < 4; ++p) pts[i][k][p] = nxt[i][k][p];
+    tile = next;
+  }
 }
 
 // ------------------------------- backward -----------------------------------

@@ -32,10 +32,11 @@ BF16_GRAD_REL = 2e-2
 WIN = _lib.MSDA_FLAG_FORCE_WINDOW
 SAVE = _lib.MSDA_FLAG_SAVE_PLAN
 FAMILY_FLAGS = {"tile": WIN, "window": WIN | _lib.MSDA_FLAG_NO_TILE, "plan": WIN | _lib.MSDA_FLAG_PLAN,
-                "saved": WIN | SAVE}   # saved: the backward starts from the tile plans the forward saved
+                "saved": WIN | SAVE,   # saved: the backward starts from the tile plans the forward saved
+                "persist": WIN | _lib.MSDA_FLAG_PERSIST}   # the forward tile kernel in its persistent form
 
 
-@pytest.fixture(params=["tile", "window", "plan", "saved"])
+@pytest.fixture(params=["tile", "window", "plan", "saved", "persist"])
 def fam(request):
     if request.param == "saved" and not MSDA.saved_plans_supported():
         pytest.skip("libmsda_b200.so built without -DMSDA_TILE_SAVED_PLANS=1 (the default: DESIGN.md section 6, 5h)")
