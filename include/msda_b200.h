@@ -101,6 +101,12 @@ typedef enum {
                                       whole grad_value NaN.  Slower: an optional
                                       variant, as the sorted scatter of the design
                                       brief, without the sort */
+/* Semantics of the default kernels on NON-FINITE value rows (temporal maps, >= 256 queries: CTA-tile and
+ * row-window kernels): a block of 4 time-adjacent queries multiplies every row of its window by each of
+ * its queries' weights, so an Inf / NaN value row reaches the block's other queries as 0 * Inf = NaN,
+ * where the reference poisons only the queries that tap the row -- a superset of the reference's NaN
+ * outputs, never outside the tapping blocks; finite outputs are equal.  MSDA_FLAG_NO_WINDOW selects the
+ * per-tap kernels, which match the reference exactly. */
 #define MSDA_FLAG_NO_TILE 32u       /* never use the CTA-tile kernels (msda_tile.cuh:
                                       time-sorted query tiles, TMA-filled shared
                                       memory); the row-window kernels run instead */
