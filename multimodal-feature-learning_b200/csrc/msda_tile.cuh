@@ -62,6 +62,9 @@ namespace msda {
                                    // starts from them).  Same results, no gain measured, and the extra branch
                                    // in the backward kernel slows its per-tap body by 38 %: off
 #endif
+#ifndef MSDA_TILE_FWD_UNROLL
+#define MSDA_TILE_FWD_UNROLL 2
+#endif
 #ifndef MSDA_TILE_FWD_CTAS
 #define MSDA_TILE_FWD_CTAS 4
 #endif
@@ -78,7 +81,11 @@ constexpr int kTileWarps = MSDA_TILE_WARPS;
 constexpr int kTileThreads = kTileWarps * 32;
 constexpr int kTileBlocks = kTileThreads / 8;        // 4-query blocks per tile
 constexpr int kTileQ = kTileBlocks * kWinQ;          // queries per tile (64 with 4 warps)
-constexpr int kTileBoxRows = 8;                      // value rows per TMA box
+#ifndef MSDA_TILE_BOX
+#define MSDA_TILE_BOX 8
+#endif
+constexpr int kTileBoxRows = MSDA_TILE_BOX;          // value rows per TMA box
+constexpr int kTileFwdUnroll = MSDA_TILE_FWD_UNROLL; // unroll factor of the forward's row loops
 constexpr int kTileCapRows = MSDA_TILE_CAP;          // value rows per tile (multiple of the box)
 constexpr int kTileBlkRows = MSDA_TILE_BLK;          // packed rows per block (plan capacity)
 // Layout of the merged weight matrices in shared memory.  Row t of block g (packed plan row; the
@@ -803,7 +810,8 @@ __device__ __forceinline__ bool tile_setup(const int64_t* __restrict__ shapes,
 // HBM -- the two dependent HBM round trips at the head of every tile CTA's life.
 // Threads 64..127 of the CTA, after the grid-dependency wait (the permutation is final).
 #ifndef MSDA_TILE_AHEAD
-#define MSDA_TILE_AHEAD 1184
+#define MSDA_TILE_AHEAD 0     // 1184 = two waves ahead.  Neutral with the 152-row tiles; with
+                              // 128-row tiles and 4 CTAs both ways it costs: backward 90.0 vs 88.0 us.  Off
 #endif
 template <typename T>
 __device__ __forceinline__ void tile_prefetch_ahead(const int* __restrict__ perm, const T* loc, const T* aw,
@@ -1113,7 +1121,7 @@ msda_fwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
     const char* vr = vtile + pl.trow[l] * RB + j * 16;
     const float4* wl = Wt + pl.bpoff[l] * kTileWtStride;
     const int n = pl.wmax[l], nb = pl.brows[l];
-#pragma unroll 2
+#pragma unroll kTileFwdUnroll
     for (int i = 0; i < n; ++i) {
       const float4 wv = wl[i * kTileWtStride];
       const float wq[kWinQ] = {wv.x, wv.y, wv.z, wv.w};
@@ -1262,7 +1270,7 @@ msda_fwd_tile_persist_kernel(const __grid_constant__ CUtensorMap vmap, const flo
         const char* vr = vtile + pl.trow[l] * RB + j * 16;
         const float4* wl = Wt + pl.bpoff[l] * kTileWtStride;
         const int n = pl.wmax[l], nb = pl.brows[l];
-#pragma unroll 2
+#pragma unroll kTileFwdUnroll
         for (int i = 0; i < n; ++i) {
           const float4 wv = wl[i * kTileWtStride];
           const float wq[kWinQ] = {wv.x, wv.y, wv.z, wv.w};
