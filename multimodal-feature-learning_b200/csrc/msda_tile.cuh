@@ -112,7 +112,7 @@ constexpr int kSaveHdrBytes = 128 + kTileBlocks * 32;
 constexpr int kSaveWarpBytes = 4 * kTileBlkRows * 16;
 constexpr int kSaveStride = kSaveHdrBytes + kTileBlocks * kTileBlkRows * 16;
 static_assert(kSaveHdrBytes % 128 == 0 && kSaveStride % 128 == 0, "saved plans stay 128-byte aligned");
-static_assert(kTileWarps == 4 || !MSDA_TILE_WT_INTERLEAVE, "header holds 4 warps");
+static_assert(kTileWarps == 4 || !MSDA_TILE_SAVED_PLANS, "a saved plan's header holds 4 warps");
 constexpr int kSortBins = 4096;
 constexpr int kSortThreads = 1024;
 constexpr int kTileBig = 0x3fffffff;
