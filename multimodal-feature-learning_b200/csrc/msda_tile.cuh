@@ -69,13 +69,13 @@ namespace msda {
 #define MSDA_TILE_FWD_CTAS 4
 #endif
 #ifndef MSDA_TILE_FWD_CTAS_BF16
-#define MSDA_TILE_FWD_CTAS_BF16 5
+#define MSDA_TILE_FWD_CTAS_BF16 6
 #endif
 #ifndef MSDA_TILE_BWD_CTAS
 #define MSDA_TILE_BWD_CTAS 4
 #endif
 #ifndef MSDA_TILE_BWD_CTAS_BF16
-#define MSDA_TILE_BWD_CTAS_BF16 4
+#define MSDA_TILE_BWD_CTAS_BF16 5
 #endif
 constexpr int kTileWarps = MSDA_TILE_WARPS;
 constexpr int kTileThreads = kTileWarps * 32;
@@ -1037,8 +1037,8 @@ constexpr size_t tile_bwd_smem() {
 }
 
 // ------------------------------- forward ------------------------------------
-// CTAs per SM the forward is compiled for: 4 at fp32 (48 KB of shared memory each), 5 for bf16 rows (half
-// the tile bytes; 96 registers, no spills: ENC 49.6 -> 47.6 us, MM_AV 45.5 -> 35.2 us)
+// CTAs per SM the forward is compiled for: 4 at fp32 (48 KB of shared memory each), 6 for bf16 rows (half
+// the tile bytes; 80 registers: ENC 49.6 -> 47.6 (5 CTAs) -> 43.6 us (6), MM_VV 39.4 -> 37.4 us)
 template <typename T>
 struct TileFwdCtas { static constexpr int value = std::is_same<T, __nv_bfloat16>::value ? MSDA_TILE_FWD_CTAS_BF16 : MSDA_TILE_FWD_CTAS; };
 
@@ -1322,8 +1322,8 @@ msda_fwd_tile_persist_kernel(const __grid_constant__ CUtensorMap vmap, const flo
 // unit and lane of a block, 4.7 rows per query in time order); the dots <grad_out, value row>
 // are transpose-reduced over the 8 lanes for two rows at a time and stored over the weights;
 // the epilogue reads the points again (L2) and forms grad_attn_weight / grad_sampling_loc.
-// CTAs per SM the backward is compiled for (4 = 128 registers; with 152-row value tiles the fp32
-// kernel was faster at 3 -- no L1 left at 4 --, the bf16 one, whose tile is half the bytes, at 4)
+// CTAs per SM the backward is compiled for (fp32: 4 = 128 registers; with 152-row value tiles it was
+// faster at 3 -- no L1 left at 4; bf16, whose tile is half the bytes: 5 = 96 registers, ENC 89.1 -> 87.0 us)
 template <typename T>
 struct TileBwdCtas { static constexpr int value = std::is_same<T, __nv_bfloat16>::value ? MSDA_TILE_BWD_CTAS_BF16 : MSDA_TILE_BWD_CTAS; };
 
