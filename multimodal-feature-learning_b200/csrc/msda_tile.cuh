@@ -62,6 +62,10 @@ namespace msda {
                                    // starts from them).  Same results, no gain measured, and the extra branch
                                    // in the backward kernel slows its per-tap body by 38 %: off
 #endif
+#ifndef MSDA_TILE_ISSUE_SPLIT
+#define MSDA_TILE_ISSUE_SPLIT 0     // 1: the TMA boxes of a tile are requested by 4 lanes (one per warp and level)
+                                   // instead of thread 0.  Measured: no change at fp32, bf16 backward 83 -> 85 us
+#endif
 #ifndef MSDA_TILE_FWD_UNROLL
 #define MSDA_TILE_FWD_UNROLL 2
 #endif
@@ -627,13 +631,16 @@ struct TilePlan {
 
 // One thread: the value boxes of a tile (level l: rows tlo[l].. in boxes of kTileBoxRows, landing at
 // tile row tbase[l]) -> TMA loads completing on mbar (whose expect_tx the caller has set)
+// (levels l with l % nsplit == part: the warps of a CTA can share the issue, one elected lane each)
 __device__ __forceinline__ void tile_issue_boxes(const CUtensorMap* vmap, const Dims& d, int b, int m,
                                                  const int (&tlo)[kWinMaxL], const int (&tbase)[kWinMaxL],
                                                  int total, char* vtile, unsigned row_bytes,
-                                                 unsigned long long* mbar) {
+                                                 unsigned long long* mbar, int part = 0, int nsplit = 1) {
 #pragma unroll
   for (int l = 0; l < kWinMaxL; ++l) {
+    if (l % nsplit != part) continue;
     const int nb = ((l + 1 < kWinMaxL ? tbase[l + 1] : total) - tbase[l]) / kTileBoxRows;
+#pragma unroll 1   // one thread runs this: keep it out of the kernel's code size
     for (int k = 0; k < nb; ++k)
       tile_tma_load(vtile + (size_t)(tbase[l] + k * kTileBoxRows) * row_bytes, vmap, m * d.D,
                     b * d.S + tlo[l] + k * kTileBoxRows, mbar);
@@ -754,9 +761,13 @@ __device__ __forceinline__ void tile_prologue(const CUtensorMap* vmap, const T* 
 #pragma unroll
   for (int l = 0; l < kWinMaxL; ++l) pl.trow[l] = pl.brows[l] > 0 ? tbase[l] + pl.blo[l] - tlo[l] : 0;
 
-  if (ISSUE && tid == 0 && total > 0) {
-    tile_mbar_expect_tx(mbar, (unsigned)total * row_bytes);
-    tile_issue_boxes(vmap, d, b, m, tlo, tbase, total, vtile, row_bytes, mbar);
+  // thread 0 arrives with the byte count; the first lane of every warp requests the boxes of "its" levels
+  // (a complete_tx that lands before the expect_tx only drives the count negative for a moment: the phase
+  // cannot complete before thread 0's arrival)
+  if (ISSUE && total > 0) {
+    if (tid == 0) tile_mbar_expect_tx(mbar, (unsigned)total * row_bytes);
+    if ((tid & 31) == 0)
+      tile_issue_boxes(vmap, d, b, m, tlo, tbase, total, vtile, row_bytes, mbar, tid >> 5, MSDA_TILE_ISSUE_SPLIT ? kTileWarps : 1);
   }
 
   // the block's weight matrix: zero, then every lane scatters its own columns (level, qi)
