@@ -66,6 +66,10 @@ namespace msda {
 #define MSDA_TILE_ISSUE_SPLIT 0     // 1: the TMA boxes of a tile are requested by 4 lanes (one per warp and level)
                                    // instead of thread 0.  Measured: no change at fp32, bf16 backward 83 -> 85 us
 #endif
+#ifndef MSDA_TILE_LEVEL_LOOP
+#define MSDA_TILE_LEVEL_LOOP 0      // 1: the level loop around the row loops is a real loop (one copy of the body
+                                   // instead of four).  Measured: forward unchanged, backward 86.1 -> 88.1 us
+#endif
 #ifndef MSDA_TILE_FWD_UNROLL
 #define MSDA_TILE_FWD_UNROLL 2
 #endif
@@ -629,6 +633,13 @@ struct TilePlan {
   bool ok;               // false: the tile runs the per-tap body
 };
 
+// a[l] for a run-time l without making `a` addressable (it stays in registers): the level loops of the
+// row phases are NOT unrolled -- one copy of the loop body instead of four (code size, section 6 5p)
+__device__ __forceinline__ int tile_sel4(int l, const int (&a)[kWinMaxL]) {
+  static_assert(kWinMaxL == 4, "4 levels");
+  return l == 0 ? a[0] : l == 1 ? a[1] : l == 2 ? a[2] : a[3];
+}
+
 // One thread: the value boxes of a tile (level l: rows tlo[l].. in boxes of kTileBoxRows, landing at
 // tile row tbase[l]) -> TMA loads completing on mbar (whose expect_tx the caller has set)
 // (levels l with l % nsplit == part: the warps of a CTA can share the issue, one elected lane each)
@@ -764,11 +775,18 @@ __device__ __forceinline__ void tile_prologue(const CUtensorMap* vmap, const T* 
   // thread 0 arrives with the byte count; the first lane of every warp requests the boxes of "its" levels
   // (a complete_tx that lands before the expect_tx only drives the count negative for a moment: the phase
   // cannot complete before thread 0's arrival)
+#if MSDA_TILE_ISSUE_SPLIT
   if (ISSUE && total > 0) {
     if (tid == 0) tile_mbar_expect_tx(mbar, (unsigned)total * row_bytes);
     if ((tid & 31) == 0)
-      tile_issue_boxes(vmap, d, b, m, tlo, tbase, total, vtile, row_bytes, mbar, tid >> 5, MSDA_TILE_ISSUE_SPLIT ? kTileWarps : 1);
+      tile_issue_boxes(vmap, d, b, m, tlo, tbase, total, vtile, row_bytes, mbar, tid >> 5, kTileWarps);
   }
+#else
+  if (ISSUE && tid == 0 && total > 0) {
+    tile_mbar_expect_tx(mbar, (unsigned)total * row_bytes);
+    tile_issue_boxes(vmap, d, b, m, tlo, tbase, total, vtile, row_bytes, mbar);
+  }
+#endif
 
   // the block's weight matrix: zero, then every lane scatters its own columns (level, qi)
   constexpr int WS = kTileWtStride;
@@ -1127,11 +1145,15 @@ msda_fwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
   // warp-uniform row loops: a block past its own rows re-reads its last row against zero weights.
   // (A hand-pipelined form -- weights and row of step i + 1 requested before the FFMA2 of step i --
   // measured 2 us slower at ENC: DESIGN.md section 6.)
+#if MSDA_TILE_LEVEL_LOOP
+#pragma unroll 1
+#else
 #pragma unroll
+#endif
   for (int l = 0; l < kWinMaxL; ++l) {
-    const char* vr = vtile + pl.trow[l] * RB + j * 16;
-    const float4* wl = Wt + pl.bpoff[l] * kTileWtStride;
-    const int n = pl.wmax[l], nb = pl.brows[l];
+    const char* vr = vtile + tile_sel4(l, pl.trow) * RB + j * 16;
+    const float4* wl = Wt + tile_sel4(l, pl.bpoff) * kTileWtStride;
+    const int n = tile_sel4(l, pl.wmax), nb = tile_sel4(l, pl.brows);
 #pragma unroll kTileFwdUnroll
     for (int i = 0; i < n; ++i) {
       const float4 wv = wl[i * kTileWtStride];
@@ -1471,13 +1493,18 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
   GV* gvb = gvalue + ((size_t)b * d.S * d.M + m) * d.D + j * E;
   // warp-uniform row loops over pairs of rows: a block past its own rows re-reads its last row
   // against zero weights and issues no reds
+#if MSDA_TILE_LEVEL_LOOP
+#pragma unroll 1
+#else
 #pragma unroll
+#endif
   for (int l = 0; l < kWinMaxL; ++l) {
-    const char* vr = vtile + pl.trow[l] * RB + j * U::BYTES;
-    const float4* wl = Wt + pl.bpoff[l] * kTileWtStride;
-    float* gl = Gs + (pl.bpoff[l] + (j >> 2)) * (4 * kTileWtStride) + (j & 3);
-    GV* gp = gvb + (size_t)pl.blo[l] * MD;
-    const int n = pl.wrows[l], nb = pl.brows[l];
+    const int l_trow = tile_sel4(l, pl.trow), l_bpoff = tile_sel4(l, pl.bpoff);
+    const char* vr = vtile + l_trow * RB + j * U::BYTES;
+    const float4* wl = Wt + l_bpoff * kTileWtStride;
+    float* gl = Gs + (l_bpoff + (j >> 2)) * (4 * kTileWtStride) + (j & 3);
+    GV* gp = gvb + (size_t)tile_sel4(l, pl.blo) * MD;
+    const int n = tile_sel4(l, pl.wrows), nb = tile_sel4(l, pl.brows);
     for (int i = 0; i < n; i += 2) {
       float x[2 * kWinQ];
       float* stg = nullptr;
@@ -1496,7 +1523,7 @@ msda_bwd_tile_kernel(const __grid_constant__ CUtensorMap vmap, const T* __restri
 #ifdef MSDA_TILE_DBG_NORED
         const bool real = gv_scale == 12345.f;   // experiment: no reds
 #else
-        const bool real = i + r < nb && !(has_mask && s_rowmask[pl.trow[l] + i + r]);
+        const bool real = i + r < nb && !(has_mask && s_rowmask[l_trow + i + r]);
 #endif
         float2 s[kWinQ];
         // grad_value row: sum_q Wt[t][q] * grad_out[q]
