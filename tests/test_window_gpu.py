@@ -280,3 +280,26 @@ def test_saved_plan_backward_equals_recomputed_plan(dtype, sigma):
     broken[base:base + tiles * stride].view(tiles, stride)[:, hdr:] = 0
     g_b = MSDA.ms_deform_attn_backward(v, s, l, loc, aw, go, 64, plan=broken)
     assert float(g_b[0].float().abs().sum()) < 0.9 * float(g_s[0].float().abs().sum())
+
+
+def test_prezero_on_and_off_give_the_same_gradients():
+    """MSDeformAttnFunction with grad_value cleared ahead of the backward (PREZERO_GRAD_VALUE, default) and
+    with the clear inside the backward: grad_sampling_loc / grad_attn_weight bitwise, grad_value up to the
+    order of its atomics."""
+    from mfl_b200.functions import ms_deform_attn_func as F
+    inp = synthetic.make_inputs(2, 421, 8, 64, 4, [(1, 256), (1, 128), (1, 64), (1, 32)], torch.float32, DEV, seed=41,
+                                dist="model", value="normal")
+    grads = []
+    for pre in (True, False):
+        keep = F.PREZERO_GRAD_VALUE
+        F.PREZERO_GRAD_VALUE = pre
+        try:
+            v, loc, aw = (inp[k].detach().clone().requires_grad_(True) for k in ("value", "loc", "aw"))
+            F.ms_deform_attn(v, inp["shapes"], inp["lsi"], loc, aw, 64).backward(inp["grad_out"])
+            grads.append((v.grad, loc.grad, aw.grad))
+        finally:
+            F.PREZERO_GRAD_VALUE = keep
+    for k in (1, 2):
+        dlt = (grads[0][k] - grads[1][k]).abs()
+        assert torch.equal(grads[0][k], grads[1][k]), (k, float(dlt.max()), int((dlt > 0).sum()), dlt.numel())
+    assert rel_err(grads[0][0].cpu().numpy(), grads[1][0].cpu().numpy()) <= 1e-5
