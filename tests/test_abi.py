@@ -67,6 +67,14 @@ def test_argument_validation_without_gpu(lib):
     assert lib.msda_forward(z, z, z, z, z, z, 0, 1, 1, 4, 1, 1, 1, 0, 0, 0, z) == 0    # empty batch
     assert lib.msda_backward_workspace_bytes(2, 3, 4, 8, 1, 1, 1, _lib.MSDA_F32) == 0
     assert lib.msda_backward_workspace_bytes(2, 3, 4, 8, 1, 1, 1, _lib.MSDA_BF16) == 2 * 3 * 4 * 8 * 4
+    # msda_forward_static (no reference counterpart): the same validation, and a call whose plan
+    # does not fit the built-in 1 MiB array is refused on the host, before any CUDA call
+    assert lib.msda_forward_static(z, z, z, z, z, z, 1, 1, 0, 4, 1, 1, 1, 0, 0, 0, z) == -2
+    assert lib.msda_forward_static(z, z, z, z, z, z, 0, 1, 1, 4, 1, 1, 1, 0, 0, 0, z) == 0
+    big = (176, 1500, 8, 64, 4, 1500, 4)                      # 264,000 queries > 262,144
+    assert lib.msda_forward_workspace_bytes(*big, _lib.MSDA_F32, 0) > (1 << 20)
+    assert lib.msda_forward_static(z, z, z, z, z, z, *big, _lib.MSDA_F32, 0, 0, z) == -11
+    assert b"scratch" in lib.msda_error_string(-11).lower()
 
 
 def _cpu_inputs():
