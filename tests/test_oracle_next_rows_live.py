@@ -52,17 +52,7 @@ def test_reference_points_restatement_equals_reference_method(seed, N, T):
     """DeformableTransformerEncoder.get_reference_points
     (models/deformable/unimodal_deformable_transformer.py:259-276), imported through a stub `models`
     package as tests/golden/make_golden.py does (models/__init__.py needs packages this image lacks)."""
-    saved = sys.modules.get("models")
-    stub = types.ModuleType("models")
-    stub.__path__ = [os.path.join(REF, "models")]
-    sys.modules["models"] = stub
-    try:
-        udt = importlib.import_module("models.deformable.unimodal_deformable_transformer")
-    finally:
-        for k in [k for k in sys.modules if k == "models" or k.startswith("models.")]:
-            del sys.modules[k]
-        if saved is not None:
-            sys.modules["models"] = saved
+    udt = _ref_udt()
     torch.manual_seed(seed)
     T = torch.tensor(T, dtype=torch.long)
     vr = torch.rand(N, len(T)) * 0.6 + 0.4
@@ -70,3 +60,40 @@ def test_reference_points_restatement_equals_reference_method(seed, N, T):
     got = core_pytorch.reference_points_pytorch(T, vr)
     assert got.shape == want.shape
     torch.testing.assert_close(got, want, rtol=1e-6, atol=1e-7)
+
+
+def _ref_udt():
+    saved = sys.modules.get("models")
+    stub = types.ModuleType("models")
+    stub.__path__ = [os.path.join(REF, "models")]
+    sys.modules["models"] = stub
+    try:
+        return importlib.import_module("models.deformable.unimodal_deformable_transformer")
+    finally:
+        for k in [k for k in sys.modules if k == "models" or k.startswith("models.")]:
+            del sys.modules[k]
+        if saved is not None:
+            sys.modules["models"] = saved
+
+
+@pytest.mark.parametrize("sizes,C,B", [([300, 150, 75, 38], 64, 2), ([33, 7], 48, 3), ([5], 8, 1)])
+def test_prepare_encoder_inputs_checker_equals_reference_method(sizes, C, B):
+    """The checker the GPU test of msda_prepare_encoder_inputs compares with (ref_prepare in
+    tests/test_prepare_inputs_gpu.py) against DeformableTransformer.prepare_encoder_inputs itself
+    (models/deformable/unimodal_deformable_transformer.py:90-134), called unbound on a stand-in that
+    carries only what the method reads (level_embed, get_valid_ratio): all six results bit for bit."""
+    from test_prepare_inputs_gpu import ref_prepare
+    udt = _ref_udt()
+    cls = udt.DeformableTransformer
+    g = torch.Generator().manual_seed(5)
+    srcs = [torch.randn(B, C, t, generator=g) for t in sizes]
+    poss = [torch.randn(B, C, t, generator=g) for t in sizes]
+    masks = [torch.rand(B, t, generator=g) > 0.8 for t in sizes]
+    le = torch.randn(len(sizes), C, generator=g)
+    me = types.SimpleNamespace(level_embed=le)
+    me.get_valid_ratio = lambda m: cls.get_valid_ratio(me, m)
+    want = cls.prepare_encoder_inputs(me, srcs, masks, poss)
+    got = ref_prepare(srcs, masks, poss, le)
+    assert len(got) == len(want) == 6
+    for a, b in zip(got, want):
+        assert a.shape == b.shape and a.dtype == b.dtype and torch.equal(a, b)
