@@ -138,3 +138,28 @@ def test_reference_names_resolve():
     aw = torch.zeros(1, 3, 2, 1, 2)
     with pytest.raises(RuntimeError, match="Not implemented on the CPU"):
         ms_deform_attn_core_pytorch(v, [(2, 3)], loc, aw)
+
+
+def test_workspace_sizes_host_logic(lib):
+    """The workspace queries are pure host arithmetic (include/msda_b200.h): the plan is one int per
+    query, kernel families without a plan ask for nothing, the backward's required part (fp32 image
+    for bf16, fixed-point image + header for the deterministic variant) comes first, 256-byte rounded,
+    with the plan behind it -- and msda_forward_static's limit is exactly 262,144 queries."""
+    enc = (16, 1500, 8, 64, 4, 1500, 4)
+    dec = (64, 1500, 8, 64, 4, 100, 4)
+    fwd = lib.msda_forward_workspace_bytes
+    bwd = lib.msda_backward_workspace_bytes_flags
+    assert fwd(*enc, _lib.MSDA_F32, 0) == fwd(*enc, _lib.MSDA_BF16, 0) == 16 * 1500 * 4
+    assert fwd(*dec, _lib.MSDA_F32, 0) == 0 and fwd(*enc, _lib.MSDA_F64, 0) == 0      # per-tap / generic
+    assert fwd(*enc, _lib.MSDA_F32, _lib.MSDA_FLAG_NO_TILE) == 0
+    assert fwd(1, 1500, 8, 64, 4, 262144, 4, _lib.MSDA_F32, 0) == 1 << 20
+    assert fwd(1, 1500, 8, 64, 4, 262145, 4, _lib.MSDA_F32, 0) > 1 << 20
+    plan = 16 * 1500 * 4
+    nvalue = 16 * 1500 * 8 * 64
+    assert bwd(*enc, _lib.MSDA_F32, 0) == plan
+    assert bwd(*enc, _lib.MSDA_BF16, 0) == nvalue * 4 + plan                          # already a 256 multiple
+    det = bwd(*enc, _lib.MSDA_F32, _lib.MSDA_FLAG_DETERMINISTIC)
+    assert det > nvalue * 8 + plan and (det - plan) % 256 == 0 and det - plan - nvalue * 8 < 512
+    assert lib.msda_backward_workspace_bytes(*enc, _lib.MSDA_F32) == bwd(*enc, _lib.MSDA_F32, 0)
+    for bad in ((16, 1500, 0, 64, 4, 1500, 4), (16, 1500, 8, 64, 4, 1500, 0)):         # invalid shapes ask for nothing
+        assert fwd(*bad, _lib.MSDA_F32, 0) == 0
